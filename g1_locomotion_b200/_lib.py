@@ -1,0 +1,70 @@
+"""ctypes loader for the in-tree C-ABI library libg1mpc_b200.so (include/g1mpc_b200.h).
+
+No fallback of any kind: if the library is missing or no CUDA device is present the product raises.
+"""
+import ctypes as C
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libg1mpc_b200.so")
+_lib = None
+
+EXPORTS = ["g1mpc_create", "g1mpc_destroy", "g1mpc_solve_batch", "g1mpc_emit_qp_batch", "g1mpc_update_host",
+           "g1mpc_kernel_info", "g1mpc_fp64_peak_tflops", "g1mpc_last_error", "g1mpc_abi_version"]
+
+
+class G1mpcParams(C.Structure):
+    """Mirror of struct g1mpc_params (include/g1mpc_b200.h)."""
+    _fields_ = [("horizon", C.c_int32), ("num_contacts", C.c_int32), ("mu", C.c_double), ("fz_min", C.c_double),
+                ("fz_max", C.c_double), ("dt", C.c_double), ("mass", C.c_double), ("gravity", C.c_double),
+                ("inertia_body", C.c_double * 9), ("q_weights", C.c_double * 13), ("r_weight", C.c_double),
+                ("cost_scale", C.c_double), ("gap_tol", C.c_double), ("max_iter", C.c_int32), ("reserved", C.c_int32)]
+
+
+def build(force=False, extra=""):
+    """Compile csrc/g1mpc_kernels.cu for sm_100a into the package directory (nvcc cross-compiles without a GPU)."""
+    src = os.path.join(_HERE, "csrc", "g1mpc_kernels.cu")
+    hdr = os.path.join(_HERE, "..", "include", "g1mpc_b200.h")
+    stale = (not os.path.exists(LIB_PATH)) or os.path.getmtime(LIB_PATH) < max(os.path.getmtime(src), os.path.getmtime(hdr))
+    if force or stale:
+        cmd = ["make", "-C", os.path.join(_HERE, "csrc"), "-B", "../libg1mpc_b200.so"]
+        if extra:
+            cmd.append(f"EXTRA={extra}")
+        subprocess.check_call(cmd)
+    return LIB_PATH
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(g1_locomotion_b200 has no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    vp, i64, i32p, dp = C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p
+    lib.g1mpc_create.argtypes = [C.POINTER(G1mpcParams), C.c_int, C.POINTER(vp)]
+    lib.g1mpc_create.restype = C.c_int
+    lib.g1mpc_destroy.argtypes = [vp]
+    lib.g1mpc_destroy.restype = None
+    lib.g1mpc_solve_batch.argtypes = [vp, i64, dp, dp, dp, dp, dp, dp, C.c_int, dp, dp, i32p, i32p, dp, dp, vp]
+    lib.g1mpc_solve_batch.restype = C.c_int
+    lib.g1mpc_emit_qp_batch.argtypes = [vp, i64] + [dp] * 14 + [vp]
+    lib.g1mpc_emit_qp_batch.restype = C.c_int
+    lib.g1mpc_update_host.argtypes = [vp, i64, dp, dp, dp, dp, dp, dp, C.c_int, dp, dp, i32p, i32p, dp]
+    lib.g1mpc_update_host.restype = C.c_int
+    lib.g1mpc_kernel_info.argtypes = [vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    lib.g1mpc_kernel_info.restype = C.c_int
+    lib.g1mpc_fp64_peak_tflops.argtypes = [C.c_int, C.POINTER(C.c_double)]
+    lib.g1mpc_fp64_peak_tflops.restype = C.c_int
+    lib.g1mpc_last_error.restype = C.c_char_p
+    lib.g1mpc_abi_version.restype = C.c_int
+    _lib = lib
+    return lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = load().g1mpc_last_error().decode(errors="replace")
+        raise RuntimeError(f"{what} failed (g1mpc_error {rc}): {msg}")

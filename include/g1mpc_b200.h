@@ -1,0 +1,122 @@
+/*
+ * g1mpc_b200.h -- C ABI of the B200-native batched SRBD-MPC hot path.
+ *
+ * Drop-in boundary for g1_mpc::MPC::updateMPC (reference g1_mpc/include/mpc.hpp:77-82,
+ * g1_mpc/src/mpc.cpp:448-473) and the Python twin MPC.update (g1_mpc/scripts/mpc.py:360-377), extended
+ * from one problem to a batch of B independent problems.  Plain pointers and sizes only; no torch,
+ * Eigen or CUDA types in the signatures (`stream` is a cudaStream_t passed as void*, NULL = default).
+ *
+ * Layouts (all double, row-major, contiguous, problem-major):
+ *   x0        [B,13]        state  [roll,pitch,yaw, px,py,pz, wx,wy,wz, vx,vy,vz, g]   (mpc.py:30; setX0 mpc.hpp:91)
+ *   x_ref     [B,N,13]      reference trajectory                                       (setXRefHor mpc.hpp:95)
+ *   contact   [B,N,nc]      real-valued contact flags, multiply the fz bounds          (mpc.cpp:344,350)
+ *   c_horizon [B,N,3*nc]    world contact-point positions                              (mpc.cpp:229)
+ *   p_com     [B,N,3]       CoM used for the lever arms (independent input)            (mpc.cpp:230)
+ *   x_current [B,13]|NULL   row 0 of x_opt if given                                    (mpc.cpp:430-433)
+ *   u_opt     [B,N,3*nc]    ground-reaction forces, step-major decision vector         (mpc.cpp:417-420)
+ *   x_opt     [B,N,13]      in/out: rows that the reference leaves untouched are left untouched
+ *                           (row 0 without x_current; rows 2.. with one_rollout)       (mpc.cpp:427-446)
+ *
+ * Every entry point returns 0 on success or a negative g1mpc_error; numerical trouble inside one
+ * problem is reported per problem in `status`, never as a call failure (the reference ignores the
+ * solver status, mpc.cpp:405,414).  There is NO CPU fallback: without a CUDA device g1mpc_create fails.
+ */
+#ifndef G1MPC_B200_H
+#define G1MPC_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define G1MPC_NUM_STATES 13
+#define G1MPC_ABI_VERSION 1
+
+typedef enum g1mpc_error {
+    G1MPC_OK = 0,
+    G1MPC_ERR_INVALID_ARGUMENT = -1,
+    G1MPC_ERR_UNSUPPORTED_SHAPE = -2, /* (horizon, num_contacts) has no compiled kernel / exceeds shared memory */
+    G1MPC_ERR_CUDA = -3,              /* see g1mpc_last_error() */
+    G1MPC_ERR_NO_DEVICE = -4
+} g1mpc_error;
+
+/* per-problem status written by g1mpc_solve_batch */
+typedef enum g1mpc_status {
+    G1MPC_SOLVED = 0,          /* complementarity gap <= gap_tol                                        */
+    G1MPC_MAX_ITER = 1,        /* iteration limit hit; best iterate returned                            */
+    G1MPC_BAD_BOUNDS = 2,      /* some contact had fz_max*c < fz_min*c (negative flag); treated as swing */
+    G1MPC_NUMERICAL = 3        /* NaN/Inf in the inputs or a breakdown of the factorisation             */
+} g1mpc_status;
+
+/* Constants the reference hard-codes in its constructors (mpc.hpp:22,136; mpc.cpp:25-27,90-98;
+ * mpc.py:12-51) plus the interior-point settings of this implementation. */
+typedef struct g1mpc_params {
+    int32_t horizon;          /* N   (horizon_length_, mpc.hpp:19)            */
+    int32_t num_contacts;     /* nc  (num_contacts_, mpc.cpp:12)              */
+    double mu, fz_min, fz_max, dt;
+    double mass;              /* robot_mass_ (mpc.hpp:136)                    */
+    double gravity;           /* g_ (mpc.cpp:7); only used for the start point */
+    double inertia_body[9];   /* row-major (mpc.cpp:25-27 / mpc.py:24-28)     */
+    double q_weights[13];     /* diag(Q_weights_) (mpc.cpp:90-96)             */
+    double r_weight;          /* diag(R_weights_) entry (mpc.cpp:98)          */
+    double cost_scale;        /* 2: H=2(B'QB+R) (mpc.cpp:361,375); 1: Python (mpc.py:301,317) */
+    double gap_tol;           /* stop when mean complementarity s'lambda/m <= gap_tol  (<=0: default 1e-10) */
+    int32_t max_iter;         /* interior-point iteration limit               (<=0: default 40)     */
+    int32_t reserved;
+} g1mpc_params;
+
+typedef struct g1mpc_handle g1mpc_handle;
+
+/* Creates a solver context on CUDA device `device` (replaces MPC::MPC + initMatrices, mpc.cpp:10-151). */
+int g1mpc_create(const g1mpc_params *params, int device, g1mpc_handle **out);
+void g1mpc_destroy(g1mpc_handle *h);
+
+/*
+ * MPC::updateMPC over a batch, all pointers DEVICE memory (mpc.cpp:448-473): linearise + discretise,
+ * condensed build (in factored form), friction-cone/contact-schedule constraints, QP solve, rollout --
+ * one fused kernel launch, asynchronous on `stream`.
+ * Optional outputs (NULL to skip):
+ *   status [B] int32, iters [B] int32,
+ *   resid  [B,4]  {complementarity gap, ||H u + g + A'y||inf, max primal violation, objective 1/2u'Hu+g'u},
+ *   y_opt  [B,5*nc*N] multipliers of the reference's rows l <= Ac u <= u (OSQP sign convention).
+ */
+int g1mpc_solve_batch(g1mpc_handle *h, int64_t B, const double *x0, const double *x_ref,
+                      const double *contact, const double *c_horizon, const double *p_com,
+                      const double *x_current, int one_rollout, double *u_opt, double *x_opt,
+                      int32_t *status, int32_t *iters, double *resid, double *y_opt, void *stream);
+
+/*
+ * Materialises the reference's intermediate matrices for a batch (device pointers, any may be NULL):
+ *   A [B,13,13] (mpc.cpp:208-211)        Bd  [B,13N,3nc] (mpc.cpp:246-254)   Aqp [B,13N,13]  (mpc.cpp:256-270)
+ *   Bqp [B,13N,3ncN] (mpc.cpp:272-291)   H   [B,3ncN,3ncN] (mpc.cpp:359-364) g [B,3ncN]      (mpc.cpp:366-376)
+ *   Acon [B,5ncN,3ncN] dense (mpc.cpp:293-326)   l,u [B,5ncN] with IEEE +-inf (mpc.cpp:328-357)
+ */
+int g1mpc_emit_qp_batch(g1mpc_handle *h, int64_t B, const double *x0, const double *x_ref,
+                        const double *contact, const double *c_horizon, const double *p_com, double *A,
+                        double *Bd, double *Aqp, double *Bqp, double *H, double *g, double *Acon,
+                        double *l, double *u, void *stream);
+
+/*
+ * Same as g1mpc_solve_batch but every pointer is HOST memory: stages through pinned buffers owned by
+ * the handle, copies host->device, solves, copies device->host and synchronises.  x_opt is in/out.
+ * This is the call the reference-facing MPC.update()/updateMPC wrapper makes.
+ */
+int g1mpc_update_host(g1mpc_handle *h, int64_t B, const double *x0, const double *x_ref,
+                      const double *contact, const double *c_horizon, const double *p_com,
+                      const double *x_current, int one_rollout, double *u_opt, double *x_opt,
+                      int32_t *status, int32_t *iters, double *resid);
+
+/* Dynamic shared memory (bytes) and threads per CTA of the solve kernel for this handle's shape. */
+int g1mpc_kernel_info(const g1mpc_handle *h, int32_t *smem_bytes, int32_t *threads, int32_t *ctas_per_sm);
+
+/* FP64 FMA throughput microbenchmark (dependent-chain-free DFMA loop on every SM), TFLOP/s. */
+int g1mpc_fp64_peak_tflops(int device, double *tflops);
+
+const char *g1mpc_last_error(void);
+int g1mpc_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* G1MPC_B200_H */

