@@ -1,0 +1,327 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the batched SRBD-MPC hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One "step" = one pass of the hot path (MPC::updateMPC, mpc.cpp:448-473: build + QP solve + rollout) over
+one batch of 1,024 synthetic walking-gait problems (BASELINE.json configs[1]) per GPU, one fused kernel
+launch.  N>1: one rank per GPU under torchrun, every rank owns an independent batch (weak scaling), no
+data-path collective; one NCCL all_gather of the first-step results after the timed region is timed
+separately (`gather_ms`).  Prints ONE JSON line on rank 0.
+
+`--impl reference` times the CPU restatement of the reference path (oracle/srbd_mpc_oracle.c: build as
+coded + OSQP-style ADMM with the reference's default settings) on all host threads; the reference's own
+C++ (needs Eigen/OSQP/OsqpEigen) cannot be built on this image and /root/reference does not exist on
+the GPU box, so kind = "port".
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "batched MPC build+solve/sec (N=10, whole box, device-timed)"
+UNIT = "problems/s"
+BATCH = 1024
+WORKLOAD = "configs[1]: 1,024 independent G1 SRBD MPC problems per GPU (cpp_node preset, N=10, nc=4, walking gait schedule)"
+
+
+def algorithmic_flops(N, nc, iters_mean):
+    """FP64 flops (FMA = 2) of THIS implementation per problem; term by term in DESIGN.md section 4."""
+    ncn, n6 = nc * N, 6 * N
+    setup = 70 * ncn + 2 * 12 * N * (N + 1) / 2 * 6 + 2 * 12 * N ** 3 + 40 * N
+    it = (21 * ncn                      # w = W u
+          + 36 * N                      # X2, X0
+          + 4 * n6 * N                  # v = M w + h
+          + 120 * ncn                   # per-contact gradient, residual, 3x3 scaling blocks, t
+          + 21 * N * nc * 36            # S_k
+          + n6 * (n6 + 1) / 2           # Y assembly
+          + n6 ** 3 / 3                 # LDL'
+          + 2 * (2 * n6 * n6 + 21 * ncn + 60 * ncn)   # two Newton solves
+          + 30 * ncn)                   # step lengths, update
+    return setup + (iters_mean + 1) * (21 * ncn + 36 * N + 4 * n6 * N + 120 * ncn) + iters_mean * (it - (21 * ncn + 36 * N + 4 * n6 * N + 120 * ncn))
+
+
+def algorithmic_bytes(N, nc):
+    """Compulsory HBM bytes per problem: inputs + x_current in, u_opt/x_opt/status/iters/resid out."""
+    return 8 * (13 + 13 * N + nc * N + 3 * nc * N + 3 * N + 13) + 8 * (3 * nc * N + 13 * N) + 8 + 32
+
+
+class ClockSampler:
+    """Samples SM clock / throttle reasons of one GPU with NVML while the timed region runs."""
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz, self._stop = [], set(), None, threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            pass
+        self.t = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                mhz = self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)
+                try:
+                    r = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.samples.append(mhz)
+                for bit, name in self.REASONS.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.002)
+
+    def __enter__(self):
+        if self.ok:
+            self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self.ok:
+            self.t.join(timeout=1.0)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": 0}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+def cpu_reference_pass(preset, batch, nthreads):
+    """One pass of the CPU restatement over `batch` -> seconds."""
+    from oracle import oracle
+    p = oracle.params_from_dict(preset)
+    t0 = time.perf_counter()
+    oracle.update_batch(p, *batch, x_current=batch[0], nthreads=nthreads)
+    return time.perf_counter() - t0
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    from g1_locomotion_b200 import presets, inputs
+    from oracle import oracle
+    oracle.build_lib()
+    preset = presets.get_preset("cpp_node")
+    sample_B = 256
+    batch = [a[:sample_B] for a in inputs.walking_batch(preset, sample_B)]
+    cores = oracle.num_threads()
+    for _ in range(max(args.warmup, 1)):
+        cpu_reference_pass(preset, batch, cores)
+    times = [cpu_reference_pass(preset, batch, cores) for _ in range(args.steps)]
+    total = float(np.sum(times))
+    value = sample_B * args.steps / total
+    sample = f"{sample_B} of the 1,024 walking problems per step, {args.steps} steps, OpenMP over {cores} threads"
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "cpu_impl": "oracle/srbd_mpc_oracle.c (mpc.cpp restatement + OSQP-style ADMM, defaults eps 1e-3)"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the config-3 throughput and B=1 latency extras")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from g1_locomotion_b200 import BatchedMPC, presets, inputs, _lib
+
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    preset = presets.get_preset("cpp_node")
+    N, nc = preset["horizon"], preset["num_contacts"]
+    solver = BatchedMPC(preset, device=local_rank)
+    host_batch = inputs.walking_batch(preset, BATCH, seed0=1000 + 100000 * rank)
+    ins = [torch.as_tensor(a, dtype=torch.float64).to(dev) for a in host_batch]
+    u_opt = torch.empty(BATCH, N, 3 * nc, device=dev, dtype=torch.float64)
+    x_opt = torch.zeros(BATCH, N, 13, device=dev, dtype=torch.float64)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def step():
+        return solver.update_batch(*ins, x_current=ins[0], u_opt=u_opt, x_opt=x_opt)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    for _ in range(max(args.warmup, 3)):
+        _, _, info = step()
+    torch.cuda.synchronize()
+    assert int((info["status"] != 0).sum()) == 0, "unsolved problems in the bench batch"
+    iters_mean = float(info["iters"].double().mean())
+
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    with ClockSampler(local_rank) as clk:
+        barrier(); torch.cuda.synchronize()
+        t_wall0 = time.perf_counter()
+        for k in range(args.steps):
+            flush.fill_(k & 0xff)              # evict L2 between timed iterations (outside the event pair)
+            starts[k].record()
+            step()
+            ends[k].record()
+        torch.cuda.synchronize(); barrier()
+        t_wall = time.perf_counter() - t_wall0
+    dev_ms = float(sum(s.elapsed_time(e) for s, e in zip(starts, ends)))
+    per_launch_ms = dev_ms / args.steps
+
+    # end to end through the reference-facing host API (numpy buffers; H2D + kernel + D2H inside the call)
+    for _ in range(3):
+        solver.update_host(*host_batch, x_current=host_batch[0])
+    barrier(); torch.cuda.synchronize()
+    e2e_steps = min(args.steps, 50)
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        uh, xh, _ = solver.update_host(*host_batch, x_current=host_batch[0])
+    e2e_s = time.perf_counter() - t0
+    barrier()
+
+    # result collection over NCCL (first-step GRFs + x_opt[1], what the WBID layer consumes)
+    gather_ms = None
+    if world > 1:
+        payload = torch.cat([u_opt[:, 0, :], x_opt[:, 1, :]], dim=1).contiguous()
+        out = torch.empty(world * BATCH, payload.shape[1], device=dev, dtype=torch.float64)
+        dist.all_gather_into_tensor(out, payload)
+        torch.cuda.synchronize(); barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record(); dist.all_gather_into_tensor(out, payload); g1.record(); torch.cuda.synchronize()
+        gather_ms = float(g0.elapsed_time(g1))
+
+    tot = torch.tensor([dev_ms, e2e_s, gather_ms or 0.0], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tot, op=dist.ReduceOp.MAX)
+    dev_ms_max, e2e_s_max, gather_ms_max = [float(v) for v in tot.tolist()]
+    value = world * BATCH * args.steps / (dev_ms_max * 1e-3)
+    e2e_value = world * BATCH * e2e_steps / e2e_s_max
+
+    if rank == 0:
+        fl = algorithmic_flops(N, nc, iters_mean) * BATCH
+        peak_tf = _fp64_peak(local_rank)
+        ach_tf = fl / (per_launch_ms * 1e-3) / 1e12
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        by = algorithmic_bytes(N, nc) * BATCH
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+                "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic",
+                "config": {"workload": WORKLOAD, "batch_per_gpu": BATCH, "preset": "cpp_node", "l2": "flushed between timed steps (256 MiB fill)",
+                           "ipm_iters_mean": iters_mean, "kernel": solver.kernel_info()},
+                "roofline": {"bound": "fp64", "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach_tf / peak_tf if peak_tf else None,
+                             "traffic": None, "kernel": "srbd_mpc_solve_kernel<10,4>", "flops_per_problem": fl / BATCH,
+                             "peak_source": "g1mpc_fp64_peak_tflops DFMA microbenchmark, measured in this run (MEASURED_PEAKS.json has no FP64 entry)",
+                             "hbm": {"bound": "hbm", "achieved": by / (per_launch_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                                     "frac": by / (per_launch_ms * 1e-3) / 1e9 / hbm_peak, "bytes_per_problem": by / BATCH,
+                                     "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s"}},
+                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 8 * BATCH * (13 + 13 * N + nc * N + 3 * nc * N + 3 * N + 13 + 13 * N),
+                        "d2h_bytes_per_step": BATCH * (8 * (3 * nc * N + 13 * N + 4) + 8), "steps": e2e_steps,
+                        "api": "BatchedMPC.update_host -> g1mpc_update_host (numpy in/out)"},
+                "gpu_launches": args.steps, "clocks": clk.summary(), "wall_s_timed_region": t_wall,
+                "gather_ms": gather_ms_max if world > 1 else None}
+        if not args.no_extras:
+            line["extras"] = extras(solver, preset, dev)
+        if not args.no_cpu_baseline and world == 1:
+            line["cpu_baseline"] = cpu_baseline(preset, host_batch)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def _fp64_peak(index):
+    import ctypes as C
+    from g1_locomotion_b200 import _lib
+    v = C.c_double()
+    rc = _lib.load().g1mpc_fp64_peak_tflops(index, C.byref(v))
+    return float(v.value) if rc == 0 else None
+
+
+def extras(solver, preset, dev):
+    """Config-3 throughput regime (65,536 random problems) and single-problem latency (p50 over 500 B=1 launches)."""
+    import torch
+    from g1_locomotion_b200 import inputs
+    out = {}
+    ins = list(inputs.random_batch(preset, 65536, seed=7, device=dev))
+    for _ in range(2):
+        _, _, info = solver.update_batch(*ins, x_current=ins[0], want_resid=False)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(3):
+        solver.update_batch(*ins, x_current=ins[0], want_resid=False)
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 3
+    out["config3_65536_random"] = {"problems_per_s": 65536 / (ms * 1e-3), "ms_per_launch": ms, "unsolved": int((info["status"] != 0).sum()),
+                                   "ipm_iters_mean": float(info["iters"].double().mean())}
+    one = [t[:1].contiguous() for t in ins]
+    lat = []
+    for i in range(520):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); solver.update_batch(*one, x_current=one[0], want_resid=False); b.record(); b.synchronize()
+        if i >= 20:
+            lat.append(a.elapsed_time(b) * 1e3)
+    out["single_solve_us"] = {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)), "launches": len(lat),
+                              "timing": "CUDA events around one B=1 launch"}
+    return out
+
+
+def cpu_baseline(preset, host_batch):
+    from oracle import oracle
+    oracle.build_lib()
+    cores = oracle.num_threads()
+    sample = [a[:256] for a in host_batch]
+    cpu_reference_pass(preset, [a[:32] for a in host_batch], cores)
+    t1 = cpu_reference_pass(preset, [a[:32] for a in host_batch], 1) / 32
+    reps, t_all = 0, 0.0
+    while t_all < 2.0 and reps < 50:
+        t_all += cpu_reference_pass(preset, sample, cores)
+        reps += 1
+    return {"value": 256 * reps / t_all, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"first 256 of the 1,024 walking problems x {reps} passes, OpenMP over {cores} host threads "
+                      f"(oracle/srbd_mpc_oracle.c: mpc.cpp build as coded + OSQP-style ADMM, eps 1e-3, cold start)",
+            "single_core_ms_per_solve": 1e3 * t1}
+
+
+if __name__ == "__main__":
+    main()

@@ -174,7 +174,8 @@ struct Lay {
     static constexpr int oGf = oT + NV;                // [NV]   grad f(u)
     static constexpr int oDu = oGf + NV;               // [NV]
     static constexpr int oDbi = oDu + NV;              // [NCN*6] Dblk^-1 (symmetric 3x3: 00,01,02,11,12,22)
-    static constexpr int oLam = oDbi + NCN * 6;        // [MC]
+    static constexpr int oX = oDbi + NCN * 6;          // [NCN*18] x_i = Dblk^-1 c_i (6 rows per contact)
+    static constexpr int oLam = oX + NCN * 18;         // [MC]
     static constexpr int oS = oLam + MC;               // [MC]
     static constexpr int oDl = oS + MC;                // [MC]
     static constexpr int oDs = oDl + MC;               // [MC]
@@ -246,7 +247,7 @@ __global__ void __launch_bounds__(kThreads) srbd_mpc_solve_kernel(const DevParam
     double *Y = sm + L_::oY, *Minv = sm + L_::oMinv, *Us = sm + L_::oU, *S2 = sm + L_::oS2, *Bw = sm + L_::oBw;
     double *hv = sm + L_::oH, *wv = sm + L_::oW, *X2 = sm + L_::oX2, *X0 = sm + L_::oX0, *vv = sm + L_::oV;
     double *dinv = sm + L_::oDinv, *Sk = sm + L_::oSk, *u = sm + L_::oUv, *tv = sm + L_::oT, *gf = sm + L_::oGf;
-    double *du = sm + L_::oDu, *Dbi = sm + L_::oDbi, *lam = sm + L_::oLam, *sl = sm + L_::oS, *dl = sm + L_::oDl;
+    double *du = sm + L_::oDu, *Dbi = sm + L_::oDbi, *Xc = sm + L_::oX, *lam = sm + L_::oLam, *sl = sm + L_::oS, *dl = sm + L_::oDl;
     double *ds = sm + L_::oDs, *lo = sm + L_::oLo, *hi = sm + L_::oHi, *Cinv = sm + L_::oCinv, *Th = sm + L_::oTh;
     double *red = sm + L_::oRed;
     const int tid = threadIdx.x;
@@ -451,6 +452,22 @@ __global__ void __launch_bounds__(kThreads) srbd_mpc_solve_kernel(const DevParam
                     const double l20 = e / a, l21 = f / bq, id2 = 1.0 / d2;
                     D6[0] = 1.0 / a + l20 * l20 * id2; D6[1] = l20 * l21 * id2; D6[2] = -l20 * id2;
                     D6[3] = 1.0 / bq + l21 * l21 * id2; D6[4] = -l21 * id2; D6[5] = id2;
+                    // x_i = Dblk^-1 c_i in cancellation-free closed form: c_i' du must be accurate to << s_i near
+                    // the solution, which a 3x3 mat-vec in (fx,fy,fz) coordinates cannot deliver
+                    {
+                        double *X = Xc + 18 * c;
+                        const double ia = 1.0 / a, ib = 1.0 / bq, iad = ia * id2, ibd = ib * id2;
+                        double x2 = -mu * (sr + 2.0 * D[1]) * iad;
+                        X[0] = (1.0 - e * x2) * ia; X[1] = -f * x2 * ib; X[2] = x2;
+                        x2 = -mu * (sr + 2.0 * D[0]) * iad;
+                        X[3] = (-1.0 - e * x2) * ia; X[4] = -f * x2 * ib; X[5] = x2;
+                        x2 = -mu * (sr + 2.0 * D[3]) * ibd;
+                        X[6] = -e * x2 * ia; X[7] = (1.0 - f * x2) * ib; X[8] = x2;
+                        x2 = -mu * (sr + 2.0 * D[2]) * ibd;
+                        X[9] = -e * x2 * ia; X[10] = (-1.0 - f * x2) * ib; X[11] = x2;
+                        X[12] = -e * id2 * ia; X[13] = -f * id2 * ib; X[14] = id2;
+                        X[15] = -X[12]; X[16] = -X[13]; X[17] = -id2;
+                    }
                     // predictor rhs = -grad f ; t = Dblk^-1 rhs
                     tv[3 * c] = -(D6[0] * g3[0] + D6[1] * g3[1] + D6[2] * g3[2]);
                     tv[3 * c + 1] = -(D6[1] * g3[0] + D6[3] * g3[1] + D6[4] * g3[2]);
@@ -572,30 +589,28 @@ __global__ void __launch_bounds__(kThreads) srbd_mpc_solve_kernel(const DevParam
             for (int c = tid; c < NCN; c += kThreads) {
                 if (!(hi[c] > lo[c])) { du[3 * c] = du[3 * c + 1] = du[3 * c + 2] = 0.0; continue; }
                 const int k = c / NC;
-                const double *Bc = Bw + 9 * c, *yk = vv + 6 * k, *D6 = Dbi + 6 * c;
-                double z[3];
-#pragma unroll
-                for (int p = 0; p < 3; p++) z[p] = Bc[p] * yk[0] + Bc[3 + p] * yk[1] + Bc[6 + p] * yk[2] + bv * yk[3 + p];
-                const double d0 = tv[3 * c] - (D6[0] * z[0] + D6[1] * z[1] + D6[2] * z[2]);
-                const double d1 = tv[3 * c + 1] - (D6[1] * z[0] + D6[3] * z[1] + D6[4] * z[2]);
-                const double d2 = tv[3 * c + 2] - (D6[2] * z[0] + D6[4] * z[1] + D6[5] * z[2]);
-                du[3 * c] = d0; du[3 * c + 1] = d1; du[3 * c + 2] = d2;
-                double dsl[6] = {-(d0 - mu * d2), -(-d0 - mu * d2), -(d1 - mu * d2), -(-d1 - mu * d2), -d2, d2};
+                const double *Bc = Bw + 9 * c, *yk = vv + 6 * k, *D6 = Dbi + 6 * c, *X = Xc + 18 * c;
                 double *s6 = sl + 6 * c, *l6 = lam + 6 * c, *ds6 = ds + 6 * c, *dl6 = dl + 6 * c;
+                double q6[6];
+#pragma unroll
+                for (int i = 0; i < 6; i++) q6[i] = pass == 0 ? 0.0 : (ds6[i] * dl6[i] - sigma_gap) / s6[i];
+                // rt = rhs - W'y  with rhs = -grad f + C' q
+                double rt[3];
+                rt[0] = -gf[3 * c] + (q6[0] - q6[1]);
+                rt[1] = -gf[3 * c + 1] + (q6[2] - q6[3]);
+                rt[2] = -gf[3 * c + 2] + (-mu * (q6[0] + q6[1] + q6[2] + q6[3]) + q6[4] - q6[5]);
+#pragma unroll
+                for (int p = 0; p < 3; p++) rt[p] -= Bc[p] * yk[0] + Bc[3 + p] * yk[1] + Bc[6 + p] * yk[2] + bv * yk[3 + p];
+                du[3 * c] = D6[0] * rt[0] + D6[1] * rt[1] + D6[2] * rt[2];
+                du[3 * c + 1] = D6[1] * rt[0] + D6[3] * rt[1] + D6[4] * rt[2];
+                du[3 * c + 2] = D6[2] * rt[0] + D6[4] * rt[1] + D6[5] * rt[2];
 #pragma unroll
                 for (int i = 0; i < 6; i++) {
-                    const double Di = l6[i] / s6[i];
-                    double dli;
-                    if (pass == 0) dli = -l6[i] - Di * dsl[i];
-                    else {
-                        const double qi = (ds6[i] * dl6[i] - sigma_gap) / s6[i]; // predictor ds,dl still in smem
-                        dli = -l6[i] - qi - Di * dsl[i];
-                    }
-                    if (dsl[i] < 0.0) p_min = fmin(p_min, -s6[i] / dsl[i]);
+                    const double dsi = -(X[3 * i] * rt[0] + X[3 * i + 1] * rt[1] + X[3 * i + 2] * rt[2]);
+                    const double dli = -l6[i] - q6[i] - (l6[i] / s6[i]) * dsi;
+                    if (dsi < 0.0) p_min = fmin(p_min, -s6[i] / dsi);
                     if (dli < 0.0) p_min = fmin(p_min, -l6[i] / dli);
-                    // stash in registers via local arrays, written below (after q has been read)
-                    dsl[i] = dsl[i];
-                    ds6[i] = dsl[i]; dl6[i] = dli;
+                    ds6[i] = dsi; dl6[i] = dli;
                 }
             }
             block_reduce3(p_sum, p_dummy, p_min, red);
