@@ -1,25 +1,16 @@
 // g1mpc_kernels.cu -- B200 (sm_100a) batched SRBD-MPC: linearise -> condensed build -> constraints ->
-// QP solve -> rollout, one CTA per problem, everything resident in shared memory, FP64.
+// QP solve -> rollout, one WARP per problem, everything resident in shared memory, FP64.
 //
 // Reference path replaced: g1_mpc::MPC::updateMPC (g1_mpc/src/mpc.cpp:448-473) and every step it calls
 // (mpc.cpp:153-446); Python twin g1_mpc/scripts/mpc.py:109-391.  This is not a translation:
 //
-//  * The condensed Hessian is never formed on the solve path.  With W = blockdiag_k [B_k(6:9,:); B_k(9:12,:)]
-//    (6N x 3ncN, the per-step force->wrench map of mpc.cpp:213-254) the reference Hessian (mpc.cpp:361) is
-//        H = s r I + W' M W,     g = W' h,
-//    where M (6N x 6N) = s (S2 (x) dt^2 diag-ish(Q_theta,Q_p) + S0 (x) diag(Q_omega,Q_v)) depends only on
-//    the mean reference yaw, and S0[a,b] = N - max(a,b), S2[a,b] = sum_{i>=max(a,b)} (i-a)(i-b) come from
-//    A^k = I + k dt Ac + C(k,2) dt^2 Ac^2 (Ac of mpc.cpp:196-206 is nilpotent).  Identity checked against
-//    the reference matrices to 1e-15 in tests/test_parity_gpu.py (emit kernel below builds the dense
-//    Aqp/Bqp/H/g/Ac/l/u of mpc.cpp:256-376 for exactly that purpose and for callers that want them).
-//  * QP (mpc.cpp:378-425, OSQP in the reference): Mehrotra predictor-corrector interior point on the
-//    identical QP.  The friction-pyramid/contact-schedule rows (mpc.cpp:293-357) are 6 one-sided rows per
-//    stance contact; swing contacts (flag 0 => fz = 0 => f = 0) drop out.  Newton systems
-//    (H + C'DC) du = rhs are solved by Woodbury on the structure above:
-//        K = Dblk + W' M W,  Dblk = s r I + C'DC (3x3 blocks),   Y = M^-1 + W Dblk^-1 W'  (6N x 6N SPD)
-//    so each iteration factorises a 6N x 6N matrix (60 x 60 at N=10) independent of the contact count.
-//    M^-1 comes from a host-side generalised eigen-decomposition of (S2,S0) plus N 3x3 inverses per problem.
-//  * Rollout (mpc.cpp:427-446) in closed form from the per-step wrenches.
+//  * solve kernel (srbd_solve_warp.cuh): the condensed Hessian is never formed.  The reference Hessian
+//    (mpc.cpp:361) factors as H = s r I + W' M W, g = W' h with W the per-step force->wrench map of
+//    mpc.cpp:213-254 and M the tracking cost seen through the (nilpotent-Ac, mpc.cpp:196-211) dynamics; the
+//    interior-point Newton systems are solved stage by stage (Riccati), O(N) work and memory.
+//  * emit kernel (below): materialises the reference's dense Aqp/Bqp/H/g/Ac/l/u (mpc.cpp:256-376) in closed
+//    form for parity tests and for callers that read those attributes; HBM-write bound.
+//  * host side: C-ABI of include/g1mpc_b200.h.
 #include "../../include/g1mpc_b200.h"
 
 #include <cuda_runtime.h>
@@ -34,8 +25,7 @@
 namespace {
 
 constexpr int NS = G1MPC_NUM_STATES;
-constexpr int kThreads = 128;
-constexpr unsigned kFull = 0xffffffffu;
+constexpr int kWarpThreads = 32;   // one warp per problem
 
 thread_local std::string g_last_error;
 
@@ -44,8 +34,6 @@ struct DevParams {
     double Ib[9];
     double q[13];
     int max_iter;
-    const double *U;    // [N*N] generalised eigenvectors of (S2,S0): U' S0 U = I, U' S2 U = diag(lamE)
-    const double *lamE; // [N]
 };
 
 struct BatchPtrs {
@@ -56,43 +44,8 @@ struct BatchPtrs {
 };
 
 // ------------------------------------------------------------------------------------------------
-// small device helpers
+// linearisation shared by the solve and emit kernels
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ double warp_sum(double v)
-{
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
-    return v;
-}
-__device__ __forceinline__ double warp_max(double v)
-{
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(kFull, v, o));
-    return v;
-}
-__device__ __forceinline__ double warp_min(double v)
-{
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(kFull, v, o));
-    return v;
-}
-
-// Block reduction of (sum, max, min) triple in one pass; result broadcast to all threads.
-// red must hold 3*(kThreads/32) doubles.  Contains two __syncthreads.
-__device__ __forceinline__ void block_reduce3(double &s, double &mx, double &mn, double *red)
-{
-    constexpr int NW = kThreads / 32;
-    s = warp_sum(s); mx = warp_max(mx); mn = warp_min(mn);
-    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-    if (l == 0) { red[w] = s; red[NW + w] = mx; red[2 * NW + w] = mn; }
-    __syncthreads();
-    double a = red[0], b = red[NW], c = red[2 * NW];
-#pragma unroll
-    for (int i = 1; i < NW; i++) { a += red[i]; b = fmax(b, red[NW + i]); c = fmin(c, red[2 * NW + i]); }
-    s = a; mx = b; mn = c;
-    __syncthreads();
-}
-
 struct Lin {            // per-problem linearisation constants (registers, computed redundantly per thread)
     double c, s;        // cos/sin of the mean reference yaw (mpc.cpp:153-178)
     double Iwi[9];      // inverse world inertia (mpc.cpp:220-221)
@@ -151,599 +104,7 @@ __device__ __forceinline__ double S2_entry(int a, int b, int N)
     return acc;
 }
 
-// ------------------------------------------------------------------------------------------------
-// shared-memory layout of the solve kernel (offsets in doubles)
-// ------------------------------------------------------------------------------------------------
-template <int N, int NC>
-struct Lay {
-    static constexpr int NU = 3 * NC, NV = NU * N, NCN = NC * N, N6 = 6 * N, LD = N6 + 1, MC = 6 * NCN;
-    static constexpr int oY = 0;                       // [N6*LD]  Woodbury matrix / its LDL' factor
-    static constexpr int oMinv = oY + N6 * LD;         // [N*N*12] M^-1 blocks: 3x3 (omega) + 3 (v diag)
-    static constexpr int oU = oMinv + N * N * 12;      // [N*N]
-    static constexpr int oS2 = oU + N * N;             // [N*N]
-    static constexpr int oBw = oS2 + N * N;            // [NCN*9]
-    static constexpr int oH = oBw + NCN * 9;           // [N6]   h (gradient in wrench space)
-    static constexpr int oW = oH + N6;                 // [N6]   W u  / W t
-    static constexpr int oX2 = oW + N6;                // [N6]
-    static constexpr int oX0 = oX2 + N6;               // [N6]
-    static constexpr int oV = oX0 + N6;                // [N6]   M w + h   /  solve result y
-    static constexpr int oDinv = oV + N6;              // [N6]   1/d of the LDL'
-    static constexpr int oSk = oDinv + N6;             // [N*36] per-step W Dblk^-1 W'
-    static constexpr int oUv = oSk + N * 36;           // [NV]   u
-    static constexpr int oT = oUv + NV;                // [NV]   Dblk^-1 rhs
-    static constexpr int oGf = oT + NV;                // [NV]   grad f(u)
-    static constexpr int oDu = oGf + NV;               // [NV]
-    static constexpr int oDbi = oDu + NV;              // [NCN*6] Dblk^-1 (symmetric 3x3: 00,01,02,11,12,22)
-    static constexpr int oX = oDbi + NCN * 6;          // [NCN*18] x_i = Dblk^-1 c_i (6 rows per contact)
-    static constexpr int oLam = oX + NCN * 18;         // [MC]
-    static constexpr int oS = oLam + MC;               // [MC]
-    static constexpr int oDl = oS + MC;                // [MC]
-    static constexpr int oDs = oDl + MC;               // [MC]
-    static constexpr int oLo = oDs + MC;               // [NCN]
-    static constexpr int oHi = oLo + NCN;              // [NCN]
-    static constexpr int oCinv = oHi + NCN;            // [N*12]
-    static constexpr int oTh = oCinv + N * 12;         // [16]   Theta' (9) + Omega(3) + c2(3)... see kernel
-    static constexpr int oRed = oTh + 24;              // [3*NW]
-    static constexpr int oEnd = oRed + 3 * (kThreads / 32) + 4;
-    // input staging aliases the Y region during setup
-    static constexpr int iX0 = 0, iXref = 16, iContact = iXref + N * NS, iChor = iContact + NCN,
-                         iPcom = iChor + NCN * 3, iE = iPcom + N * 3, iEnd = iE + N * 12;
-    static_assert(iEnd <= N6 * LD, "input staging must fit in the Y region");
-    static constexpr size_t bytes = sizeof(double) * (size_t)oEnd;
-};
-
-// y = (L D L')^-1 vec, executed by warp 0 only; Y holds unit-lower L below the diagonal, dinv = 1/D.
-template <int N6, int LD>
-__device__ __forceinline__ void ldl_solve_warp(const double *__restrict__ Y, const double *__restrict__ dinv, double *vec)
-{
-    constexpr int R = (N6 + 31) / 32;
-    const int lane = threadIdx.x & 31;
-    double y[R];
-#pragma unroll
-    for (int r = 0; r < R; r++) { const int i = lane + 32 * r; y[r] = i < N6 ? vec[i] : 0.0; }
-#pragma unroll
-    for (int jb = 0; jb < R; jb++) {
-        const int jmax = (N6 - 32 * jb) < 32 ? (N6 - 32 * jb) : 32;
-#pragma unroll 4
-        for (int jj = 0; jj < jmax; jj++) {
-            const double yj = __shfl_sync(kFull, y[jb], jj);
-            const int j = 32 * jb + jj;
-#pragma unroll
-            for (int r = jb; r < R; r++) {
-                const int i = lane + 32 * r;
-                if (i > j && i < N6) y[r] -= Y[i * LD + j] * yj;
-            }
-        }
-    }
-#pragma unroll
-    for (int r = 0; r < R; r++) { const int i = lane + 32 * r; if (i < N6) y[r] *= dinv[i]; }
-#pragma unroll
-    for (int jb = R - 1; jb >= 0; jb--) {
-        const int jmax = (N6 - 32 * jb) < 32 ? (N6 - 32 * jb) : 32;
-#pragma unroll 4
-        for (int jj = jmax - 1; jj >= 0; jj--) {
-            const double yj = __shfl_sync(kFull, y[jb], jj);
-            const int j = 32 * jb + jj;
-#pragma unroll
-            for (int r = 0; r <= jb; r++) {
-                const int i = lane + 32 * r;
-                if (i < j) y[r] -= Y[j * LD + i] * yj;
-            }
-        }
-    }
-#pragma unroll
-    for (int r = 0; r < R; r++) { const int i = lane + 32 * r; if (i < N6) vec[i] = y[r]; }
-}
-
-// ------------------------------------------------------------------------------------------------
-// fused solve kernel
-// ------------------------------------------------------------------------------------------------
-template <int N, int NC>
-__global__ void __launch_bounds__(kThreads) srbd_mpc_solve_kernel(const DevParams P, const BatchPtrs io, long long B)
-{
-    using L_ = Lay<N, NC>;
-    constexpr int NU = L_::NU, NV = L_::NV, NCN = L_::NCN, N6 = L_::N6, LD = L_::LD;
-    extern __shared__ double sm[];
-    double *Y = sm + L_::oY, *Minv = sm + L_::oMinv, *Us = sm + L_::oU, *S2 = sm + L_::oS2, *Bw = sm + L_::oBw;
-    double *hv = sm + L_::oH, *wv = sm + L_::oW, *X2 = sm + L_::oX2, *X0 = sm + L_::oX0, *vv = sm + L_::oV;
-    double *dinv = sm + L_::oDinv, *Sk = sm + L_::oSk, *u = sm + L_::oUv, *tv = sm + L_::oT, *gf = sm + L_::oGf;
-    double *du = sm + L_::oDu, *Dbi = sm + L_::oDbi, *Xc = sm + L_::oX, *lam = sm + L_::oLam, *sl = sm + L_::oS, *dl = sm + L_::oDl;
-    double *ds = sm + L_::oDs, *lo = sm + L_::oLo, *hi = sm + L_::oHi, *Cinv = sm + L_::oCinv, *Th = sm + L_::oTh;
-    double *red = sm + L_::oRed;
-    const int tid = threadIdx.x;
-    const long long b = blockIdx.x;
-    if (b >= B) return;
-
-    // ---- stage inputs (aliasing the Y region) ----------------------------------------------------
-    {
-        const double *gx0 = io.x0 + b * NS, *gxr = io.x_ref + b * (N * NS), *gct = io.contact + b * NCN;
-        const double *gch = io.c_hor + b * (NCN * 3), *gpc = io.p_com + b * (N * 3);
-        for (int i = tid; i < NS; i += kThreads) sm[L_::iX0 + i] = gx0[i];
-        for (int i = tid; i < N * NS; i += kThreads) sm[L_::iXref + i] = gxr[i];
-        for (int i = tid; i < NCN; i += kThreads) sm[L_::iContact + i] = gct[i];
-        for (int i = tid; i < NCN * 3; i += kThreads) sm[L_::iChor + i] = gch[i];
-        for (int i = tid; i < N * 3; i += kThreads) sm[L_::iPcom + i] = gpc[i];
-        for (int i = tid; i < N * N; i += kThreads) Us[i] = P.U[i];
-    }
-    __syncthreads();
-    const double *x0 = sm + L_::iX0, *xref = sm + L_::iXref;
-    Lin lin;
-    linearise(P, xref, N, lin);
-    const double cz = lin.c, sz = lin.s; // Rz = [[cz,-sz,0],[sz,cz,0],[0,0,1]] = rotation_z_T_' (mpc.cpp:199)
-    int bad_bounds = 0;
-    // per contact: lever-arm block, bounds
-    for (int c = tid; c < NCN; c += kThreads) {
-        const int k = c / NC;
-        contact_Bw(P, lin, sm + L_::iChor + 3 * c, sm + L_::iPcom + 3 * k, Bw + 9 * c);
-        const double cf = sm[L_::iContact + c];
-        const double l = P.fz_min * cf, h = P.fz_max * cf;   // mpc.cpp:344,350
-        if (h < l) bad_bounds = 1;
-        lo[c] = l; hi[c] = (h > l) ? h : l;                  // hi==lo  <=>  swing / eliminated
-    }
-    // free-response error e_i = A^(i+1) x0 - x_ref_i  (12 weighted states)  (mpc.cpp:256-270,369-375)
-    for (int i = tid; i < N; i += kThreads) {
-        const double kk = (double)(i + 1), dt = P.dt, g0 = x0[12];
-        double *E = sm + L_::iE + 12 * i;
-        const double *xr = xref + i * NS;
-        const double wx = x0[6], wy = x0[7], wz = x0[8];
-        E[0] = x0[0] + kk * dt * (cz * wx - sz * wy) - xr[0];
-        E[1] = x0[1] + kk * dt * (sz * wx + cz * wy) - xr[1];
-        E[2] = x0[2] + kk * dt * wz - xr[2];
-        E[3] = x0[3] + kk * dt * x0[9] - xr[3];
-        E[4] = x0[4] + kk * dt * x0[10] - xr[4];
-        E[5] = x0[5] + kk * dt * x0[11] + (0.5 * kk * (kk - 1.0)) * dt * dt * g0 - xr[5];
-        E[6] = wx - xr[6]; E[7] = wy - xr[7]; E[8] = wz - xr[8];
-        E[9] = x0[9] - xr[9]; E[10] = x0[10] - xr[10]; E[11] = x0[11] + kk * dt * g0 - xr[11];
-    }
-    for (int e = tid; e < N * N; e += kThreads) S2[e] = S2_entry(e / N, e % N, N);
-    if (tid < 24) {
-        // Th[0..8] = Theta' = s dt^2 Rz' diag(q_theta) Rz ; Th[9..11] = s q_omega ; Th[12..14] = s dt^2 q_p ; Th[15..17] = s q_v
-        const double sc = P.scale, d2 = P.dt * P.dt;
-        const double q0 = P.q[0], q1 = P.q[1], q2 = P.q[2];
-        double v = 0.0;
-        switch (tid) {
-            case 0: v = sc * d2 * (cz * cz * q0 + sz * sz * q1); break;
-            case 1: case 3: v = sc * d2 * (cz * sz * (q1 - q0)); break;
-            case 4: v = sc * d2 * (sz * sz * q0 + cz * cz * q1); break;
-            case 8: v = sc * d2 * q2; break;
-            case 9: case 10: case 11: v = sc * P.q[6 + tid - 9]; break;
-            case 12: case 13: case 14: v = sc * d2 * P.q[3 + tid - 12]; break;
-            case 15: case 16: case 17: v = sc * P.q[9 + tid - 15]; break;
-            default: v = 0.0;
-        }
-        Th[tid] = v;
-    }
-    __syncthreads();
-    // h_k (wrench-space gradient):  g = W' h   (mpc.cpp:366-376)
-    for (int e = tid; e < N6; e += kThreads) {
-        const int k = e / 6, al = e % 6;
-        double acc = 0.0;
-        for (int i = k; i < N; i++) {
-            const double *E = sm + L_::iE + 12 * i;
-            const double lev = (double)(i - k) * P.dt;
-            double a;
-            if (al == 0) a = lev * (cz * P.q[0] * E[0] + sz * P.q[1] * E[1]) + P.q[6] * E[6];
-            else if (al == 1) a = lev * (-sz * P.q[0] * E[0] + cz * P.q[1] * E[1]) + P.q[7] * E[7];
-            else if (al == 2) a = lev * P.q[2] * E[2] + P.q[8] * E[8];
-            else a = lev * P.q[al] * E[al] + P.q[6 + al] * E[6 + al];
-            acc += a;
-        }
-        hv[e] = P.scale * acc;
-    }
-    // (lamE_i Theta' + Omega)^-1 per generalised eigenvalue: 2x2 (xy) + scalar (z) ; v axes scalars
-    for (int i = tid; i < N; i += kThreads) {
-        const double le = P.lamE[i];
-        const double a = le * Th[0] + Th[9], bb = le * Th[1], d = le * Th[4] + Th[10];
-        const double idet = 1.0 / (a * d - bb * bb);
-        double *C = Cinv + 12 * i;
-        C[0] = d * idet; C[1] = -bb * idet; C[2] = 0.0;
-        C[3] = -bb * idet; C[4] = a * idet; C[5] = 0.0;
-        C[6] = 0.0; C[7] = 0.0; C[8] = 1.0 / (le * Th[8] + Th[11]);
-        C[9] = 1.0 / (le * Th[12] + Th[15]); C[10] = 1.0 / (le * Th[13] + Th[16]); C[11] = 1.0 / (le * Th[14] + Th[17]);
-    }
-    __syncthreads();
-    // M^-1 blocks
-    for (int e = tid; e < N * N * 12; e += kThreads) {
-        const int ab = e / 12, el = e % 12, a = ab / N, bq = ab % N;
-        double acc = 0.0;
-        for (int i = 0; i < N; i++) acc += Us[a * N + i] * Us[bq * N + i] * Cinv[12 * i + el];
-        Minv[e] = acc;
-    }
-    // start point: weight shared by the stance contacts of each step, clamped into the interior
-    for (int c = tid; c < NCN; c += kThreads) {
-        const int k = c / NC;
-        int ns = 0;
-        for (int j = 0; j < NC; j++) ns += (hi[k * NC + j] > lo[k * NC + j]) ? 1 : 0;
-        const bool st = hi[c] > lo[c];
-        double fz = 0.0;
-        if (st) {
-            const double span = hi[c] - lo[c];
-            fz = P.weight / (double)ns;
-            fz = fmin(fmax(fz, lo[c] + 0.1 * span), hi[c] - 0.1 * span);
-        }
-        u[3 * c] = 0.0; u[3 * c + 1] = 0.0; u[3 * c + 2] = fz;
-        double *s6 = sl + 6 * c, *l6 = lam + 6 * c;
-        if (st) {
-            s6[0] = P.mu * fz; s6[1] = P.mu * fz; s6[2] = P.mu * fz; s6[3] = P.mu * fz; s6[4] = hi[c] - fz; s6[5] = fz - lo[c];
-        } else {
-#pragma unroll
-            for (int i = 0; i < 6; i++) s6[i] = 1.0;
-        }
-#pragma unroll
-        for (int i = 0; i < 6; i++) l6[i] = 0.0;
-    }
-    __syncthreads();
-
-    const double sr = P.sr, mu = P.mu, bv = P.bv;
-    int n_stance = 0;
-    for (int c = 0; c < NCN; c++) n_stance += (hi[c] > lo[c]) ? 1 : 0;
-    const double m_ineq = 6.0 * (double)(n_stance > 0 ? n_stance : 1);
-    int status = G1MPC_MAX_ITER, it = 0;
-    double gap = 0.0, rdmax = 0.0;
-    bool lam_init = false;
-
-    for (it = 0;; it++) {
-        // (1) w = W u
-        for (int e = tid; e < N6; e += kThreads) {
-            const int k = e / 6, al = e % 6;
-            double acc = 0.0;
-            if (al < 3) {
-                for (int j = 0; j < NC; j++) {
-                    const double *Bc = Bw + 9 * (k * NC + j) + 3 * al, *uc = u + 3 * (k * NC + j);
-                    acc += Bc[0] * uc[0] + Bc[1] * uc[1] + Bc[2] * uc[2];
-                }
-            } else {
-                for (int j = 0; j < NC; j++) acc += u[3 * (k * NC + j) + al - 3];
-                acc *= bv;
-            }
-            wv[e] = acc;
-        }
-        __syncthreads();
-        // (2) per-step 6-vectors X2 = blockdiag(Theta', c2) w_k, X0 = blockdiag(Omega, c0) w_k
-        for (int e = tid; e < N6; e += kThreads) {
-            const int k = e / 6, al = e % 6;
-            const double *wk = wv + 6 * k;
-            if (al < 3) {
-                X2[e] = Th[3 * al] * wk[0] + Th[3 * al + 1] * wk[1] + Th[3 * al + 2] * wk[2];
-                X0[e] = Th[9 + al] * wk[al];
-            } else {
-                X2[e] = Th[12 + al - 3] * wk[al];
-                X0[e] = Th[15 + al - 3] * wk[al];
-            }
-        }
-        __syncthreads();
-        // (3) v = M w + h
-        for (int e = tid; e < N6; e += kThreads) {
-            const int a = e / 6, al = e % 6;
-            double acc = hv[e];
-            for (int bq = 0; bq < N; bq++) {
-                const int mx = a > bq ? a : bq;
-                acc += S2[a * N + bq] * X2[6 * bq + al] + (double)(N - mx) * X0[6 * bq + al];
-            }
-            vv[e] = acc;
-        }
-        __syncthreads();
-        // (4) per contact: grad f, dual residual, scaling matrices, predictor right-hand side
-        double p_gap = 0.0, p_rd = 0.0, p_gf = 0.0;
-        for (int c = tid; c < NCN; c += kThreads) {
-            const int k = c / NC;
-            const double *Bc = Bw + 9 * c, *vk = vv + 6 * k, *uc = u + 3 * c;
-            double g3[3];
-#pragma unroll
-            for (int p = 0; p < 3; p++)
-                g3[p] = sr * uc[p] + Bc[p] * vk[0] + Bc[3 + p] * vk[1] + Bc[6 + p] * vk[2] + bv * vk[3 + p];
-            gf[3 * c] = g3[0]; gf[3 * c + 1] = g3[1]; gf[3 * c + 2] = g3[2];
-            double *D6 = Dbi + 6 * c;
-            if (hi[c] > lo[c]) {
-                double *s6 = sl + 6 * c, *l6 = lam + 6 * c;
-                p_gf = fmax(p_gf, fmax(fabs(g3[0]), fmax(fabs(g3[1]), fabs(g3[2]))));
-                if (lam_init) {
-                    const double r0 = g3[0] + l6[0] - l6[1], r1 = g3[1] + l6[2] - l6[3];
-                    const double r2 = g3[2] - mu * (l6[0] + l6[1] + l6[2] + l6[3]) + l6[4] - l6[5];
-                    p_rd = fmax(p_rd, fmax(fabs(r0), fmax(fabs(r1), fabs(r2))));
-                    double D[6];
-#pragma unroll
-                    for (int i = 0; i < 6; i++) { p_gap += s6[i] * l6[i]; D[i] = l6[i] / s6[i]; }
-                    // Dblk = sr I + Cb' D Cb = [[a,0,e],[0,b,f],[e,f,cc]] ; LDL' with cancellation-free Schur term
-                    const double a = sr + D[0] + D[1], bq = sr + D[2] + D[3];
-                    const double e = -mu * (D[0] - D[1]), f = -mu * (D[2] - D[3]);
-                    const double d2 = sr + D[4] + D[5] + mu * mu * ((sr * (D[0] + D[1]) + 4.0 * D[0] * D[1]) / a +
-                                                                    (sr * (D[2] + D[3]) + 4.0 * D[2] * D[3]) / bq);
-                    const double l20 = e / a, l21 = f / bq, id2 = 1.0 / d2;
-                    D6[0] = 1.0 / a + l20 * l20 * id2; D6[1] = l20 * l21 * id2; D6[2] = -l20 * id2;
-                    D6[3] = 1.0 / bq + l21 * l21 * id2; D6[4] = -l21 * id2; D6[5] = id2;
-                    // x_i = Dblk^-1 c_i in cancellation-free closed form: c_i' du must be accurate to << s_i near
-                    // the solution, which a 3x3 mat-vec in (fx,fy,fz) coordinates cannot deliver
-                    {
-                        double *X = Xc + 18 * c;
-                        const double ia = 1.0 / a, ib = 1.0 / bq, iad = ia * id2, ibd = ib * id2;
-                        double x2 = -mu * (sr + 2.0 * D[1]) * iad;
-                        X[0] = (1.0 - e * x2) * ia; X[1] = -f * x2 * ib; X[2] = x2;
-                        x2 = -mu * (sr + 2.0 * D[0]) * iad;
-                        X[3] = (-1.0 - e * x2) * ia; X[4] = -f * x2 * ib; X[5] = x2;
-                        x2 = -mu * (sr + 2.0 * D[3]) * ibd;
-                        X[6] = -e * x2 * ia; X[7] = (1.0 - f * x2) * ib; X[8] = x2;
-                        x2 = -mu * (sr + 2.0 * D[2]) * ibd;
-                        X[9] = -e * x2 * ia; X[10] = (-1.0 - f * x2) * ib; X[11] = x2;
-                        X[12] = -e * id2 * ia; X[13] = -f * id2 * ib; X[14] = id2;
-                        X[15] = -X[12]; X[16] = -X[13]; X[17] = -id2;
-                    }
-                    // predictor rhs = -grad f ; t = Dblk^-1 rhs
-                    tv[3 * c] = -(D6[0] * g3[0] + D6[1] * g3[1] + D6[2] * g3[2]);
-                    tv[3 * c + 1] = -(D6[1] * g3[0] + D6[3] * g3[1] + D6[4] * g3[2]);
-                    tv[3 * c + 2] = -(D6[2] * g3[0] + D6[4] * g3[1] + D6[5] * g3[2]);
-                }
-            } else {
-#pragma unroll
-                for (int i = 0; i < 6; i++) D6[i] = 0.0;
-                tv[3 * c] = 0.0; tv[3 * c + 1] = 0.0; tv[3 * c + 2] = 0.0;
-            }
-        }
-        {
-            double dummy = 0.0;
-            block_reduce3(p_gap, p_rd, dummy, red);
-        }
-        if (!lam_init) {
-            // lambda_0 = mu0 / s with mu0 tied to the gradient scale at the start point; redo step (4)
-            double gmax = p_gf, d1 = 0.0, d2 = 0.0;
-            block_reduce3(d1, gmax, d2, red);
-            const double mu0 = fmax(1e-2, 0.1 * gmax);
-            for (int c = tid; c < NCN; c += kThreads)
-                if (hi[c] > lo[c]) {
-#pragma unroll
-                    for (int i = 0; i < 6; i++) lam[6 * c + i] = mu0 / sl[6 * c + i];
-                }
-            lam_init = true;
-            __syncthreads();
-            it = -1;
-            continue;
-        }
-        gap = p_gap / m_ineq; rdmax = p_rd;
-        if (!(gap == gap) || !(rdmax == rdmax) || isinf(gap) || isinf(rdmax)) { status = G1MPC_NUMERICAL; break; }
-        if (gap <= P.gap_tol || n_stance == 0) { status = G1MPC_SOLVED; break; }
-        if (it >= P.max_iter) { status = G1MPC_MAX_ITER; break; }
-
-        // (5) S_k = sum_j W_kj Dblk_kj^-1 W_kj'  (6x6 per step), then Y = M^-1 + blockdiag(S_k) (lower triangle)
-        for (int e = tid; e < N * 21; e += kThreads) {
-            const int k = e / 21;
-            int pr = e % 21, al = 0;
-            while (pr > al) { pr -= al + 1; al++; }   // (al, be = pr) with be <= al
-            const int be = pr;
-            double acc = 0.0;
-            for (int j = 0; j < NC; j++) {
-                const int c = k * NC + j;
-                const double *D6 = Dbi + 6 * c, *Bc = Bw + 9 * c;
-                double ra[3], rb[3];
-                if (al < 3) { ra[0] = Bc[3 * al]; ra[1] = Bc[3 * al + 1]; ra[2] = Bc[3 * al + 2]; }
-                else { ra[0] = al == 3 ? bv : 0.0; ra[1] = al == 4 ? bv : 0.0; ra[2] = al == 5 ? bv : 0.0; }
-                if (be < 3) { rb[0] = Bc[3 * be]; rb[1] = Bc[3 * be + 1]; rb[2] = Bc[3 * be + 2]; }
-                else { rb[0] = be == 3 ? bv : 0.0; rb[1] = be == 4 ? bv : 0.0; rb[2] = be == 5 ? bv : 0.0; }
-                const double x0_ = D6[0] * rb[0] + D6[1] * rb[1] + D6[2] * rb[2];
-                const double x1_ = D6[1] * rb[0] + D6[3] * rb[1] + D6[4] * rb[2];
-                const double x2_ = D6[2] * rb[0] + D6[4] * rb[1] + D6[5] * rb[2];
-                acc += ra[0] * x0_ + ra[1] * x1_ + ra[2] * x2_;
-            }
-            Sk[36 * k + 6 * al + be] = acc;
-            Sk[36 * k + 6 * be + al] = acc;
-        }
-        __syncthreads();
-        for (int e = tid; e < N6 * N6; e += kThreads) {
-            const int I = e / N6, J = e % N6;
-            if (J > I) continue;
-            const int a = I / 6, al = I % 6, bq = J / 6, be = J % 6;
-            double v = 0.0;
-            if (al < 3 && be < 3) v = Minv[(a * N + bq) * 12 + 3 * al + be];
-            else if (al == be) v = Minv[(a * N + bq) * 12 + 9 + al - 3];
-            if (a == bq) v += Sk[36 * a + 6 * al + be];
-            Y[I * LD + J] = v;
-        }
-        __syncthreads();
-        // (6) LDL' (right-looking, unscaled columns; one barrier per column)
-        bool breakdown = false;
-        for (int j = 0; j < N6; j++) {
-            const double piv = Y[j * LD + j];
-            if (!(piv > 0.0)) { breakdown = true; break; }
-            const double ip = 1.0 / piv;
-            const int rem = N6 - 1 - j;
-            // 2-D thread tiling of the trailing lower triangle
-            const int tr = tid >> 4, tc = tid & 15;
-            for (int i = j + 1 + tr; i < N6; i += kThreads / 16) {
-                const double lij = Y[i * LD + j] * ip;
-                for (int c = j + 1 + tc; c <= i; c += 16) Y[i * LD + c] -= lij * Y[c * LD + j];
-            }
-            (void)rem;
-            __syncthreads();
-        }
-        if (breakdown) { status = G1MPC_NUMERICAL; break; }
-        for (int j = tid; j < N6; j += kThreads) dinv[j] = 1.0 / Y[j * LD + j];
-        __syncthreads();
-        for (int e = tid; e < N6 * N6; e += kThreads) {
-            const int I = e / N6, J = e % N6;
-            if (J < I) Y[I * LD + J] *= dinv[J];
-        }
-        // (7)/(9) two Newton solves sharing the factor: predictor then corrector
-        double sigma_gap = 0.0;
-        double alpha = 1.0;
-        for (int pass = 0; pass < 2; pass++) {
-            __syncthreads();
-            // wv = W t
-            for (int e = tid; e < N6; e += kThreads) {
-                const int k = e / 6, al = e % 6;
-                double acc = 0.0;
-                if (al < 3) {
-                    for (int j = 0; j < NC; j++) {
-                        const double *Bc = Bw + 9 * (k * NC + j) + 3 * al, *tc_ = tv + 3 * (k * NC + j);
-                        acc += Bc[0] * tc_[0] + Bc[1] * tc_[1] + Bc[2] * tc_[2];
-                    }
-                } else {
-                    for (int j = 0; j < NC; j++) acc += tv[3 * (k * NC + j) + al - 3];
-                    acc *= bv;
-                }
-                vv[e] = acc;
-            }
-            __syncthreads();
-            if (tid < 32) ldl_solve_warp<N6, LD>(Y, dinv, vv);
-            __syncthreads();
-            // du = t - Dblk^-1 W' y ; ds = -C du ; dlam ; step lengths
-            double p_min = 1e300, p_sum = 0.0, p_dummy = 0.0;
-            for (int c = tid; c < NCN; c += kThreads) {
-                if (!(hi[c] > lo[c])) { du[3 * c] = du[3 * c + 1] = du[3 * c + 2] = 0.0; continue; }
-                const int k = c / NC;
-                const double *Bc = Bw + 9 * c, *yk = vv + 6 * k, *D6 = Dbi + 6 * c, *X = Xc + 18 * c;
-                double *s6 = sl + 6 * c, *l6 = lam + 6 * c, *ds6 = ds + 6 * c, *dl6 = dl + 6 * c;
-                double q6[6];
-#pragma unroll
-                for (int i = 0; i < 6; i++) q6[i] = pass == 0 ? 0.0 : (ds6[i] * dl6[i] - sigma_gap) / s6[i];
-                // rt = rhs - W'y  with rhs = -grad f + C' q
-                double rt[3];
-                rt[0] = -gf[3 * c] + (q6[0] - q6[1]);
-                rt[1] = -gf[3 * c + 1] + (q6[2] - q6[3]);
-                rt[2] = -gf[3 * c + 2] + (-mu * (q6[0] + q6[1] + q6[2] + q6[3]) + q6[4] - q6[5]);
-#pragma unroll
-                for (int p = 0; p < 3; p++) rt[p] -= Bc[p] * yk[0] + Bc[3 + p] * yk[1] + Bc[6 + p] * yk[2] + bv * yk[3 + p];
-                du[3 * c] = D6[0] * rt[0] + D6[1] * rt[1] + D6[2] * rt[2];
-                du[3 * c + 1] = D6[1] * rt[0] + D6[3] * rt[1] + D6[4] * rt[2];
-                du[3 * c + 2] = D6[2] * rt[0] + D6[4] * rt[1] + D6[5] * rt[2];
-#pragma unroll
-                for (int i = 0; i < 6; i++) {
-                    const double dsi = -(X[3 * i] * rt[0] + X[3 * i + 1] * rt[1] + X[3 * i + 2] * rt[2]);
-                    const double dli = -l6[i] - q6[i] - (l6[i] / s6[i]) * dsi;
-                    if (dsi < 0.0) p_min = fmin(p_min, -s6[i] / dsi);
-                    if (dli < 0.0) p_min = fmin(p_min, -l6[i] / dli);
-                    ds6[i] = dsi; dl6[i] = dli;
-                }
-            }
-            block_reduce3(p_sum, p_dummy, p_min, red);
-            if (pass == 0) {
-                const double a_aff = fmin(1.0, p_min);
-                double g_aff = 0.0, dmx = 0.0, dmn = 0.0;
-                for (int c = tid; c < NCN; c += kThreads)
-                    if (hi[c] > lo[c]) {
-#pragma unroll
-                        for (int i = 0; i < 6; i++)
-                            g_aff += (sl[6 * c + i] + a_aff * ds[6 * c + i]) * (lam[6 * c + i] + a_aff * dl[6 * c + i]);
-                    }
-                block_reduce3(g_aff, dmx, dmn, red);
-                g_aff /= m_ineq;
-                double sig = g_aff / gap;
-                sig = sig * sig * sig;
-                sigma_gap = sig * gap;
-                // corrector rhs = -grad f + C'((ds_a dl_a - sigma mu)/s) ; t = Dblk^-1 rhs
-                for (int c = tid; c < NCN; c += kThreads) {
-                    if (!(hi[c] > lo[c])) continue;
-                    const double *s6 = sl + 6 * c, *ds6 = ds + 6 * c, *dl6 = dl + 6 * c, *D6 = Dbi + 6 * c;
-                    double q6[6];
-#pragma unroll
-                    for (int i = 0; i < 6; i++) q6[i] = (ds6[i] * dl6[i] - sigma_gap) / s6[i];
-                    const double r0 = -gf[3 * c] + (q6[0] - q6[1]);
-                    const double r1 = -gf[3 * c + 1] + (q6[2] - q6[3]);
-                    const double r2 = -gf[3 * c + 2] + (-mu * (q6[0] + q6[1] + q6[2] + q6[3]) + q6[4] - q6[5]);
-                    tv[3 * c] = D6[0] * r0 + D6[1] * r1 + D6[2] * r2;
-                    tv[3 * c + 1] = D6[1] * r0 + D6[3] * r1 + D6[4] * r2;
-                    tv[3 * c + 2] = D6[2] * r0 + D6[4] * r1 + D6[5] * r2;
-                }
-            } else {
-                alpha = fmin(1.0, 0.995 * p_min);
-            }
-        }
-        // (10) step
-        for (int c = tid; c < NCN; c += kThreads) {
-            if (!(hi[c] > lo[c])) continue;
-#pragma unroll
-            for (int p = 0; p < 3; p++) u[3 * c + p] += alpha * du[3 * c + p];
-#pragma unroll
-            for (int i = 0; i < 6; i++) {
-                lam[6 * c + i] += alpha * dl[6 * c + i];
-                sl[6 * c + i] += alpha * ds[6 * c + i];
-            }
-        }
-        __syncthreads();
-    }
-
-    // ---- outputs ------------------------------------------------------------------------------------
-    // here wv = W u, vv = M w + h, gf = grad f(u) are consistent with the returned u (breaks happen after step 4)
-    if (status == G1MPC_SOLVED && bad_bounds) status = G1MPC_BAD_BOUNDS;
-    {
-        int any_bad = __syncthreads_or(bad_bounds);
-        if (any_bad && status == G1MPC_SOLVED) status = G1MPC_BAD_BOUNDS;
-    }
-    double *gu = io.u_opt + b * NV;
-    for (int i = tid; i < NV; i += kThreads) gu[i] = u[i];
-    if (io.status && tid == 0) io.status[b] = status;
-    if (io.iters && tid == 0) io.iters[b] = it;
-    if (io.resid) {
-        double obj = 0.0, pv = 0.0, dmn = 0.0;
-        for (int i = tid; i < NV; i += kThreads) obj += 0.5 * sr * u[i] * u[i];
-        for (int e = tid; e < N6; e += kThreads) obj += 0.5 * wv[e] * (vv[e] + hv[e]);
-        for (int c = tid; c < NCN; c += kThreads) {
-            const double fx = u[3 * c], fy = u[3 * c + 1], fz = u[3 * c + 2];
-            pv = fmax(pv, fmax(fabs(fx) - mu * fz, fabs(fy) - mu * fz));
-            pv = fmax(pv, fmax(fz - hi[c], lo[c] - fz));
-        }
-        block_reduce3(obj, pv, dmn, red);
-        if (tid == 0) {
-            double *r = io.resid + b * 4;
-            r[0] = gap; r[1] = rdmax; r[2] = fmax(pv, 0.0); r[3] = obj;
-        }
-    }
-    if (io.y_opt) {
-        // multipliers of the reference's 5 rows per contact (OSQP sign: y<0 at a lower bound)
-        double *gy = io.y_opt + b * (5 * NCN);
-        for (int c = tid; c < NCN; c += kThreads) {
-            double y5[5];
-            if (hi[c] > lo[c]) {
-                const double *l6 = lam + 6 * c;
-                y5[0] = -l6[1]; y5[1] = l6[0]; y5[2] = -l6[3]; y5[3] = l6[2]; y5[4] = l6[4] - l6[5];
-            } else {
-                // swing contact: any sign-feasible multiplier set that balances the gradient
-                const double g0 = gf[3 * c], g1 = gf[3 * c + 1], g2 = gf[3 * c + 2];
-                y5[0] = y5[1] = y5[2] = y5[3] = 0.0;
-                if (-g0 <= 0.0) y5[0] = -g0; else y5[1] = -g0;
-                if (-g1 <= 0.0) y5[2] = -g1; else y5[3] = -g1;
-                y5[4] = -g2 - mu * (y5[0] - y5[1] + y5[2] - y5[3]);
-            }
-#pragma unroll
-            for (int i = 0; i < 5; i++) gy[5 * c + i] = y5[i];
-        }
-    }
-    // rollout (mpc.cpp:427-446) in closed form; x_opt is in/out
-    {
-        double *gx = io.x_opt + b * (N * NS);
-        const double *xc = io.x_current ? io.x_current + b * NS : gx;
-        const int last = io.one_rollout ? 1 : N - 1;
-        for (int e = tid; e < (last + 1) * NS; e += kThreads) {
-            const int i = e / NS, r = e % NS;
-            if (i == 0) { if (io.x_current) gx[r] = xc[r]; continue; }
-            const double dt = P.dt, di = (double)i;
-            double val;
-            if (r < 3) {        // theta_i = theta_c + dt Rz (i w_c + sum_{j<i-1} (i-1-j) ww_j)
-                double a0 = di * xc[6], a1 = di * xc[7], a2 = di * xc[8];
-                for (int j = 0; j + 1 < i; j++) {
-                    const double f = (double)(i - 1 - j);
-                    a0 += f * wv[6 * j]; a1 += f * wv[6 * j + 1]; a2 += f * wv[6 * j + 2];
-                }
-                const double rot = r == 0 ? (cz * a0 - sz * a1) : (r == 1 ? (sz * a0 + cz * a1) : a2);
-                val = xc[r] + dt * rot;
-            } else if (r < 6) { // p_i = p_c + dt (i v_c + C(i,2) dt g e_z + sum (i-1-j) wv_j)
-                const int ax = r - 3;
-                double a = di * xc[9 + ax];
-                if (ax == 2) a += 0.5 * di * (di - 1.0) * dt * xc[12];
-                for (int j = 0; j + 1 < i; j++) a += (double)(i - 1 - j) * wv[6 * j + 3 + ax];
-                val = xc[r] + dt * a;
-            } else if (r < 9) {
-                double a = xc[r];
-                for (int j = 0; j < i; j++) a += wv[6 * j + r - 6];
-                val = a;
-            } else if (r < 12) {
-                double a = xc[r];
-                if (r == 11) a += di * dt * xc[12];
-                for (int j = 0; j < i; j++) a += wv[6 * j + 3 + r - 9];
-                val = a;
-            } else val = xc[12];
-            gx[i * NS + r] = val;
-        }
-    }
-}
+#include "srbd_solve_warp.cuh"
 
 // ------------------------------------------------------------------------------------------------
 // emit kernel: materialise the reference's dense intermediates (mpc.cpp:196-376) -- HBM-write bound
@@ -931,93 +292,12 @@ __global__ void fp64_peak_kernel(double *out, int iters)
     } while (0)
 
 typedef void (*solve_fn)(const DevParams, const BatchPtrs, long long);
-struct KernelEntry { int N, NC; solve_fn fn; size_t smem; };
+struct KernelEntry { int N, NC; solve_fn fn; size_t smem; };   // smem = bytes per warp (= per problem)
 
-#define G1MPC_SHAPES(X) X(10, 4) X(15, 4) X(20, 4) X(10, 8) X(12, 8) X(20, 8) X(5, 4) X(8, 4)
-#define X_ENTRY(n, c) {n, c, srbd_mpc_solve_kernel<n, c>, Lay<n, c>::bytes},
+#define G1MPC_SHAPES(X) X(10, 4) X(15, 4) X(20, 4) X(40, 4) X(10, 8) X(12, 8) X(20, 8) X(40, 8) X(5, 4) X(8, 4)
+#define X_ENTRY(n, c) {n, c, v2::srbd_mpc_solve_warp_kernel<n, c>, v2::WLay<n, c>::bytes},
 const KernelEntry kKernels[] = {G1MPC_SHAPES(X_ENTRY)};
 #undef X_ENTRY
-
-// symmetric Jacobi eigen-solver (n <= 64), A overwritten, V columns = eigenvectors
-void jacobi_eig(std::vector<double> &A, std::vector<double> &V, int n)
-{
-    V.assign((size_t)n * n, 0.0);
-    for (int i = 0; i < n; i++) V[(size_t)i * n + i] = 1.0;
-    for (int sweep = 0; sweep < 100; sweep++) {
-        double off = 0.0;
-        for (int i = 0; i < n; i++) for (int j = i + 1; j < n; j++) off += A[(size_t)i * n + j] * A[(size_t)i * n + j];
-        if (off < 1e-300) break;
-        for (int p = 0; p < n; p++)
-            for (int q = p + 1; q < n; q++) {
-                const double apq = A[(size_t)p * n + q];
-                if (fabs(apq) < 1e-300) continue;
-                const double theta = (A[(size_t)q * n + q] - A[(size_t)p * n + p]) / (2.0 * apq);
-                const double t = (theta >= 0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
-                const double c = 1.0 / sqrt(t * t + 1.0), s = t * c;
-                for (int k = 0; k < n; k++) {
-                    const double akp = A[(size_t)k * n + p], akq = A[(size_t)k * n + q];
-                    A[(size_t)k * n + p] = c * akp - s * akq; A[(size_t)k * n + q] = s * akp + c * akq;
-                }
-                for (int k = 0; k < n; k++) {
-                    const double apk = A[(size_t)p * n + k], aqk = A[(size_t)q * n + k];
-                    A[(size_t)p * n + k] = c * apk - s * aqk; A[(size_t)q * n + k] = s * apk + c * aqk;
-                }
-                for (int k = 0; k < n; k++) {
-                    const double vkp = V[(size_t)k * n + p], vkq = V[(size_t)k * n + q];
-                    V[(size_t)k * n + p] = c * vkp - s * vkq; V[(size_t)k * n + q] = s * vkp + c * vkq;
-                }
-            }
-    }
-}
-
-// generalised symmetric eigenproblem S2 u = lam S0 u with U' S0 U = I
-void gen_eig_S2_S0(int N, std::vector<double> &U, std::vector<double> &lam)
-{
-    std::vector<double> S0((size_t)N * N), S2((size_t)N * N), L((size_t)N * N, 0.0);
-    for (int a = 0; a < N; a++)
-        for (int b = 0; b < N; b++) {
-            const int m = a > b ? a : b;
-            S0[(size_t)a * N + b] = N - m;
-            double acc = 0; for (int i = m; i < N; i++) acc += (double)((i - a) * (i - b));
-            S2[(size_t)a * N + b] = acc;
-        }
-    for (int j = 0; j < N; j++) {   // Cholesky S0 = L L'
-        double d = S0[(size_t)j * N + j];
-        for (int k = 0; k < j; k++) d -= L[(size_t)j * N + k] * L[(size_t)j * N + k];
-        d = sqrt(d); L[(size_t)j * N + j] = d;
-        for (int i = j + 1; i < N; i++) {
-            double s = S0[(size_t)i * N + j];
-            for (int k = 0; k < j; k++) s -= L[(size_t)i * N + k] * L[(size_t)j * N + k];
-            L[(size_t)i * N + j] = s / d;
-        }
-    }
-    // C = L^-1 S2 L^-T
-    std::vector<double> T((size_t)N * N), C((size_t)N * N);
-    for (int c = 0; c < N; c++)      // T = L^-1 S2 (column by column)
-        for (int i = 0; i < N; i++) {
-            double s = S2[(size_t)i * N + c];
-            for (int k = 0; k < i; k++) s -= L[(size_t)i * N + k] * T[(size_t)k * N + c];
-            T[(size_t)i * N + c] = s / L[(size_t)i * N + i];
-        }
-    for (int r = 0; r < N; r++)      // C = T L^-T  <=> C' = L^-1 T'
-        for (int i = 0; i < N; i++) {
-            double s = T[(size_t)r * N + i];
-            for (int k = 0; k < i; k++) s -= L[(size_t)i * N + k] * C[(size_t)r * N + k];
-            C[(size_t)r * N + i] = s / L[(size_t)i * N + i];
-        }
-    for (int i = 0; i < N; i++) for (int j = i + 1; j < N; j++) { const double m = 0.5 * (C[(size_t)i * N + j] + C[(size_t)j * N + i]); C[(size_t)i * N + j] = C[(size_t)j * N + i] = m; }
-    std::vector<double> Wv;
-    jacobi_eig(C, Wv, N);
-    lam.resize(N);
-    for (int i = 0; i < N; i++) lam[i] = C[(size_t)i * N + i];
-    U.assign((size_t)N * N, 0.0);   // U = L^-T W
-    for (int c = 0; c < N; c++)
-        for (int i = N - 1; i >= 0; i--) {
-            double s = Wv[(size_t)i * N + c];
-            for (int k = i + 1; k < N; k++) s -= L[(size_t)k * N + i] * U[(size_t)k * N + c];
-            U[(size_t)i * N + c] = s / L[(size_t)i * N + i];
-        }
-}
 
 } // namespace
 
@@ -1026,7 +306,7 @@ struct g1mpc_handle {
     DevParams dev;
     int device;
     const KernelEntry *kernel;
-    double *d_U = nullptr, *d_lam = nullptr;
+    int warps_per_block = 1;
     int ctas_per_sm = 0;
     // host-API staging
     cudaStream_t stream = nullptr;
@@ -1077,19 +357,10 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
     d.gap_tol = h->params.gap_tol; d.max_iter = h->params.max_iter;
     memcpy(d.Ib, p->inertia_body, sizeof d.Ib);
     memcpy(d.q, p->q_weights, sizeof d.q);
-    std::vector<double> U, lam;
-    gen_eig_S2_S0(p->horizon, U, lam);
-    const int N = p->horizon;
-    if (cudaMalloc(&h->d_U, sizeof(double) * N * N) != cudaSuccess || cudaMalloc(&h->d_lam, sizeof(double) * N) != cudaSuccess) {
-        g_last_error = "cudaMalloc failed"; delete h; return G1MPC_ERR_CUDA;
-    }
-    cudaMemcpy(h->d_U, U.data(), sizeof(double) * N * N, cudaMemcpyHostToDevice);
-    cudaMemcpy(h->d_lam, lam.data(), sizeof(double) * N, cudaMemcpyHostToDevice);
-    d.U = h->d_U; d.lamE = h->d_lam;
-    cudaError_t e = cudaFuncSetAttribute((const void *)ke->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ke->smem);
+    cudaError_t e = cudaFuncSetAttribute((const void *)ke->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ke->smem * h->warps_per_block));
     if (e != cudaSuccess) { g_last_error = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
     cudaFuncSetAttribute((const void *)srbd_mpc_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->ctas_per_sm, (const void *)ke->fn, kThreads, ke->smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->ctas_per_sm, (const void *)ke->fn, kWarpThreads * h->warps_per_block, ke->smem * h->warps_per_block);
     e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) { g_last_error = "cudaStreamCreate failed"; g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
     *out = h;
@@ -1100,8 +371,6 @@ void g1mpc_destroy(g1mpc_handle *h)
 {
     if (!h) return;
     cudaSetDevice(h->device);
-    if (h->d_U) cudaFree(h->d_U);
-    if (h->d_lam) cudaFree(h->d_lam);
     if (h->h_stage) cudaFreeHost(h->h_stage);
     if (h->d_stage) cudaFree(h->d_stage);
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -1111,8 +380,8 @@ void g1mpc_destroy(g1mpc_handle *h)
 int g1mpc_kernel_info(const g1mpc_handle *h, int32_t *smem_bytes, int32_t *threads, int32_t *ctas_per_sm)
 {
     if (!h) return G1MPC_ERR_INVALID_ARGUMENT;
-    if (smem_bytes) *smem_bytes = (int32_t)h->kernel->smem;
-    if (threads) *threads = kThreads;
+    if (smem_bytes) *smem_bytes = (int32_t)(h->kernel->smem * h->warps_per_block);
+    if (threads) *threads = kWarpThreads * h->warps_per_block;
     if (ctas_per_sm) *ctas_per_sm = h->ctas_per_sm;
     return G1MPC_OK;
 }
@@ -1129,7 +398,8 @@ int g1mpc_solve_batch(g1mpc_handle *h, int64_t B, const double *x0, const double
     if (B > 0x7fffffffLL) { g_last_error = "batch too large for one launch"; return G1MPC_ERR_INVALID_ARGUMENT; }
     CUDA_TRY(cudaSetDevice(h->device));
     BatchPtrs io{x0, x_ref, contact, c_horizon, p_com, x_current, u_opt, x_opt, resid, y_opt, status, iters, one_rollout};
-    h->kernel->fn<<<(unsigned)B, kThreads, h->kernel->smem, (cudaStream_t)stream>>>(h->dev, io, (long long)B);
+    const int wpb = h->warps_per_block;
+    h->kernel->fn<<<(unsigned)((B + wpb - 1) / wpb), kWarpThreads * wpb, h->kernel->smem * wpb, (cudaStream_t)stream>>>(h->dev, io, (long long)B);
     CUDA_TRY(cudaGetLastError());
     return G1MPC_OK;
 }

@@ -1,0 +1,948 @@
+// srbd_solve_warp.cuh -- v2 solve kernel: ONE WARP PER PROBLEM, stage-wise (Riccati) interior point, FP64.
+// Included by g1mpc_kernels.cu inside its anonymous namespace (uses DevParams, BatchPtrs, Lin, linearise, NS).
+//
+// Reference path replaced: g1_mpc::MPC::updateMPC (g1_mpc/src/mpc.cpp:448-473) = linearise/discretise
+// (mpc.cpp:153-254), condensed build (mpc.cpp:256-291,359-376), constraints (mpc.cpp:293-357), QP solve
+// (mpc.cpp:378-425, OSQP in the reference) and rollout (mpc.cpp:427-446).
+//
+// Mathematics (checked on the CPU against the oracle by tests/ipm_model.py + tests/test_ipm_model_cpu.py):
+//   * states y = (theta, p | omega, v) (12 weighted states; gravity is constant), per-step wrench increment
+//     w_k = Bm (sum_c r_c x f_c, sum_c f_c),  Bm = blockdiag(dt Iw^-1, dt/m I)         (mpc.cpp:213-254)
+//     y_{k+1} = [I Phi; 0 I] y_k + [0; I] w_k,  Phi = dt blockdiag(Rz(psi), I)           (mpc.cpp:196-211)
+//     so the reference Hessian/gradient (mpc.cpp:361,375) are H = s r I + W'MW, g = W'h with M = G' sQ G.
+//   * QP: Mehrotra predictor-corrector on the 6 one-sided rows per stance contact (mpc.cpp:293-357); swing
+//     contacts (flag 0 => f = 0) drop out.  Newton systems (Dblk + W'MW) du = rhs with Dblk block-diagonal 3x3
+//     reduce to (M^-1 + S) y = t in wrench space, S_k = W_k Dblk_k^-1 W_k' (6x6 per stage), solved by a
+//     backward Riccati sweep over the horizon: per stage two 6x6 LDL' factorisations, explicit closed-loop
+//     blocks Gamma' and Psi, then one small mat-vec per stage in each of the backward/forward vector sweeps.
+//     Cost O(N) per iteration, shared memory O(N): the condensed 3ncN x 3ncN Hessian is never formed.
+//   * one warp owns one problem: no block-level barrier anywhere, only __syncwarp(); the sequential 6x6
+//     factorisations run redundantly in every lane's registers (no shuffles on the critical path), the wide
+//     phases (per contact, per stage, per matrix column) are spread over the lanes.
+#pragma once
+
+namespace v2 {
+
+constexpr unsigned kFullMask = 0xffffffffu;
+
+__device__ __forceinline__ double wsum(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFullMask, v, o);
+    return v;
+}
+__device__ __forceinline__ double wmax(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(kFullMask, v, o));
+    return v;
+}
+__device__ __forceinline__ double wmin(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(kFullMask, v, o));
+    return v;
+}
+
+// packed lower-triangular index of a symmetric 6x6, i >= j
+__host__ __device__ constexpr int tri(int i, int j) { return i * (i + 1) / 2 + j; }
+__device__ __forceinline__ int trs(int i, int j) { return i >= j ? i * (i + 1) / 2 + j : j * (j + 1) / 2 + i; }
+
+// Shared-memory layout of one problem (offsets in doubles).  Regions that are never live at the same time
+// share storage; the comments say who owns what when.
+template <int N, int NC>
+struct WLay {
+    static constexpr int NCN = NC * N;
+    // ---- per contact, persistent over the solve ----
+    static constexpr int oR = 0;                    // [NCN*3] lever arm r = c - p_com            (mpc.cpp:229-233)
+    static constexpr int oCf = oR + NCN * 3;        // [NCN]   contact flag (multiplies fz bounds, mpc.cpp:344,350)
+    static constexpr int oU = oCf + NCN;            // [NCN*3] forces
+    static constexpr int oSl = oU + NCN * 3;        // [NCN*6] slacks
+    static constexpr int oLam = oSl + NCN * 6;      // [NCN*6] multipliers
+    static constexpr int oGf = oLam + NCN * 6;      // [NCN*3] grad f(u)
+    static constexpr int oDst = oGf + NCN * 3;      // [NCN*9] D0..D5 = lam/s, 1/a, 1/b, 1/d2 of the 3x3 block
+    static constexpr int oProd = oDst + NCN * 9;    // [NCN*6] predictor ds*dl (Mehrotra second-order term)
+    static constexpr int oTv = oProd + NCN * 6;     // [NCN*3] Dblk^-1 rhs, then du
+    // ---- per stage ----
+    static constexpr int oE = oTv + NCN * 3;        // [N*12]  free-response error A^(k+1) x0 - xref_k (mpc.cpp:369-375)
+    static constexpr int oS = oE + N * 12;          // [N*21]  S_k packed
+    static constexpr int STG = 36 + 36 + 36 + 21;   // per stage: Gamma' | Psi | P12 | P22(packed) of P_{k+1}
+    static constexpr int oRic = oS + N * 21;        // [N*STG] ; after the corrector solve: ds | dl  (needs 12 NCN <= STG N)
+    static constexpr int oP = oRic + N * STG;       // [36+36+21] running P11 | P12 | P22(packed)
+    // ---- scratch, three users: gradient sweeps | factor exchange | solve vectors ----
+    static constexpr int oX = oP + 93;              // gradient: w[N*6] X[N*12] L1[N*6] V[N*6]
+    static constexpr int oW = oX;                   //   w  [N*6]
+    static constexpr int oXs = oW + N * 6;          //   X  [N*12]
+    static constexpr int oL1 = oXs + N * 12;        //   L1 [N*6]
+    static constexpr int oV = oL1 + N * 6;          //   V  [N*6]  (then Bm' V in place)
+    static constexpr int oVa = oX;                  // solve: vA [N*6]  t -> Gamma't -> b -> y2 -> zeta~
+    static constexpr int oVb = oVa + N * 6;         //        vB [N*6]  c1 -> y1
+    static constexpr int oVc = oVb + N * 6;         //        vC [N*6]  c2' -> p2 (saved)
+    static constexpr int oEx = oVc + N * 6;         // factor exchange: A11 | A21 | A22 [108]
+    static constexpr int scratch = (N * 30 > N * 18 + 108) ? N * 30 : N * 18 + 108;
+    static constexpr int oEnd = oX + scratch;
+    static_assert(12 * NCN <= STG * N, "ds|dl alias the stage storage: needs num_contacts <= 10");
+    static constexpr size_t bytes = sizeof(double) * (size_t)oEnd;
+};
+
+// LDL' of a symmetric positive definite 6x6 held packed (21) in registers; afterwards a[tri(i,j)], i>j, holds
+// the unit-lower factor and dinv[j] = 1/d_j.  Returns false on a non-positive pivot.
+__device__ __forceinline__ bool ldl6(double (&a)[21], double (&dinv)[6])
+{
+    bool ok = true;
+#pragma unroll
+    for (int j = 0; j < 6; j++) {
+        const double dj = a[tri(j, j)];
+        ok = ok && (dj > 0.0);
+        const double r = 1.0 / dj;
+        dinv[j] = r;
+        double col[6];
+#pragma unroll
+        for (int i = j + 1; i < 6; i++) col[i] = a[tri(i, j)];
+#pragma unroll
+        for (int i = j + 1; i < 6; i++) {
+            const double lij = col[i] * r;
+#pragma unroll
+            for (int c = j + 1; c <= i; c++) a[tri(i, c)] = fma(-lij, col[c], a[tri(i, c)]);
+            a[tri(i, j)] = lij;
+        }
+    }
+    return ok;
+}
+
+// x <- L^-1 x  (unit lower, packed)
+__device__ __forceinline__ void fsub6(const double (&l)[21], double (&x)[6])
+{
+#pragma unroll
+    for (int i = 1; i < 6; i++)
+#pragma unroll
+        for (int j = 0; j < i; j++) x[i] = fma(-l[tri(i, j)], x[j], x[i]);
+}
+// x <- L^-T x
+__device__ __forceinline__ void bsub6(const double (&l)[21], double (&x)[6])
+{
+#pragma unroll
+    for (int j = 5; j >= 1; j--)
+#pragma unroll
+        for (int i = 0; i < j; i++) x[i] = fma(-l[tri(j, i)], x[j], x[i]);
+}
+// x <- L x
+__device__ __forceinline__ void lmul6(const double (&l)[21], double (&x)[6])
+{
+#pragma unroll
+    for (int i = 5; i >= 1; i--)
+#pragma unroll
+        for (int j = 0; j < i; j++) x[i] = fma(l[tri(i, j)], x[j], x[i]);
+}
+
+// (Phi x)[c] and (Phi' x)[c] for a 6-vector in registers, Phi = dt blockdiag(Rz, I)   (mpc.cpp:199,210)
+struct PhiC { double dc, dsn, dt; };   // dt cos(psi), dt sin(psi), dt
+__device__ __forceinline__ void phiT6(const PhiC &F, const double (&x)[6], double (&y)[6])
+{
+    y[0] = F.dc * x[0] + F.dsn * x[1];
+    y[1] = -F.dsn * x[0] + F.dc * x[1];
+    y[2] = F.dt * x[2]; y[3] = F.dt * x[3]; y[4] = F.dt * x[4]; y[5] = F.dt * x[5];
+}
+
+
+// 3x3 block of one stance contact from the stored D-state: Dinv (symmetric, 6: 00,01,02,11,12,22)
+__device__ __forceinline__ void contact_dinv(const double *Ds, double sr, double mu, double (&Di)[6])
+{
+    const double ia = Ds[6], ib = Ds[7], id2 = Ds[8];
+    const double e = -mu * (Ds[0] - Ds[1]), f = -mu * (Ds[2] - Ds[3]);
+    const double l20 = e * ia, l21 = f * ib;
+    Di[0] = ia + l20 * l20 * id2; Di[1] = l20 * l21 * id2; Di[2] = -l20 * id2;
+    Di[3] = ib + l21 * l21 * id2; Di[4] = -l21 * id2; Di[5] = id2;
+}
+// X = Dblk^-1 Cb' (6 rows x 3) in the cancellation-free closed form: c_i' du must stay accurate to << s_i
+// near the solution, which a 3x3 mat-vec in (fx,fy,fz) coordinates cannot deliver.
+__device__ __forceinline__ void contact_X(const double *Ds, double sr, double mu, double (&X)[18])
+{
+    const double ia = Ds[6], ib = Ds[7], id2 = Ds[8];
+    const double e = -mu * (Ds[0] - Ds[1]), f = -mu * (Ds[2] - Ds[3]);
+    const double iad = ia * id2, ibd = ib * id2;
+    double x2 = -mu * (sr + 2.0 * Ds[1]) * iad;
+    X[0] = (1.0 - e * x2) * ia; X[1] = -f * x2 * ib; X[2] = x2;
+    x2 = -mu * (sr + 2.0 * Ds[0]) * iad;
+    X[3] = (-1.0 - e * x2) * ia; X[4] = -f * x2 * ib; X[5] = x2;
+    x2 = -mu * (sr + 2.0 * Ds[3]) * ibd;
+    X[6] = -e * x2 * ia; X[7] = (1.0 - f * x2) * ib; X[8] = x2;
+    x2 = -mu * (sr + 2.0 * Ds[2]) * ibd;
+    X[9] = -e * x2 * ia; X[10] = (-1.0 - f * x2) * ib; X[11] = x2;
+    X[12] = -e * id2 * ia; X[13] = -f * id2 * ib; X[14] = id2;
+    X[15] = -X[12]; X[16] = -X[13]; X[17] = -id2;
+}
+
+// Per-stage constants every lane keeps in registers.
+struct StageC {
+    double J[9];      // dt Iw^-1                       (mpc.cpp:220-221,237,251)
+    double bv;        // dt / m                         (mpc.cpp:238,251)
+    PhiC F;
+};
+
+// t_k = Bm sum_c [r x tv_c ; tv_c]  (lane k), optionally also S_k = Bm (sum_c W~ Dinv W~') Bm'
+template <int N, int NC, bool WITH_S>
+__device__ __forceinline__ void assemble_stage(double *sm, const DevParams &P, const StageC &C, int lane)
+{
+    using L_ = WLay<N, NC>;
+    for (int k = lane; k < N; k += 32) {
+        double tt[3] = {0, 0, 0}, tf[3] = {0, 0, 0};
+        double Stt[6] = {0, 0, 0, 0, 0, 0}, Sff[6] = {0, 0, 0, 0, 0, 0}, Stf[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};   // tau-tau, F-F (sym), tau-F (full)
+        for (int j = 0; j < NC; j++) {
+            const int c = k * NC + j;
+            const double cf = sm[L_::oCf + c];
+            if (!(P.fz_max * cf > P.fz_min * cf)) continue;          // swing / eliminated
+            const double *r = sm + L_::oR + 3 * c, *tv = sm + L_::oTv + 3 * c;
+            const double r0 = r[0], r1 = r[1], r2 = r[2];
+            tt[0] += r1 * tv[2] - r2 * tv[1]; tt[1] += r2 * tv[0] - r0 * tv[2]; tt[2] += r0 * tv[1] - r1 * tv[0];
+            tf[0] += tv[0]; tf[1] += tv[1]; tf[2] += tv[2];
+            if (WITH_S) {
+                double Di[6];
+                contact_dinv(sm + L_::oDst + 9 * c, P.sr, P.mu, Di);
+                const double D00 = Di[0], D01 = Di[1], D02 = Di[2], D11 = Di[3], D12 = Di[4], D22 = Di[5];
+                // RD = skew(r) Dinv
+                const double a00 = -r2 * D01 + r1 * D02, a01 = -r2 * D11 + r1 * D12, a02 = -r2 * D12 + r1 * D22;
+                const double a10 = r2 * D00 - r0 * D02, a11 = r2 * D01 - r0 * D12, a12 = r2 * D02 - r0 * D22;
+                const double a20 = -r1 * D00 + r0 * D01, a21 = -r1 * D01 + r0 * D11, a22 = -r1 * D02 + r0 * D12;
+                // tau-tau += RD skew(r)'   ( (RD R')[i][j] = sum_m RD[i][m] R[j][m] )
+                Stt[0] += -r2 * a01 + r1 * a02;                       // (0,0)
+                Stt[1] += -r2 * a11 + r1 * a12;                       // (1,0)
+                Stt[2] += r2 * a10 - r0 * a12;                        // (1,1)
+                Stt[3] += -r2 * a21 + r1 * a22;                       // (2,0)
+                Stt[4] += r2 * a20 - r0 * a22;                        // (2,1)
+                Stt[5] += -r1 * a20 + r0 * a21;                       // (2,2)
+                Stf[0] += a00; Stf[1] += a01; Stf[2] += a02; Stf[3] += a10; Stf[4] += a11; Stf[5] += a12;
+                Stf[6] += a20; Stf[7] += a21; Stf[8] += a22;
+                Sff[0] += D00; Sff[1] += D01; Sff[2] += D11; Sff[3] += D02; Sff[4] += D12; Sff[5] += D22;   // packed (0,0)(1,0)(1,1)(2,0)(2,1)(2,2)
+            }
+        }
+        const double *J = C.J;
+        double *t = sm + L_::oVa + 6 * k;
+        t[0] = J[0] * tt[0] + J[1] * tt[1] + J[2] * tt[2];
+        t[1] = J[3] * tt[0] + J[4] * tt[1] + J[5] * tt[2];
+        t[2] = J[6] * tt[0] + J[7] * tt[1] + J[8] * tt[2];
+        t[3] = C.bv * tf[0]; t[4] = C.bv * tf[1]; t[5] = C.bv * tf[2];
+        if (WITH_S) {
+            double *S = sm + L_::oS + 21 * k;
+            // omega-omega = J Stt J'
+            double JS[9];
+#pragma unroll
+            for (int i = 0; i < 3; i++)
+#pragma unroll
+                for (int m = 0; m < 3; m++) {
+                    double acc = 0.0;
+#pragma unroll
+                    for (int q = 0; q < 3; q++) acc += J[3 * i + q] * Stt[q >= m ? tri(q, m) : tri(m, q)];
+                    JS[3 * i + m] = acc;
+                }
+#pragma unroll
+            for (int i = 0; i < 3; i++)
+#pragma unroll
+                for (int m = 0; m <= i; m++) S[tri(i, m)] = JS[3 * i] * J[3 * m] + JS[3 * i + 1] * J[3 * m + 1] + JS[3 * i + 2] * J[3 * m + 2];
+            // v-omega = bv (Stf)' J'  :  S[3+i][m] = bv sum_q Stf[q][i] J[m][q]
+#pragma unroll
+            for (int i = 0; i < 3; i++)
+#pragma unroll
+                for (int m = 0; m < 3; m++)
+                    S[tri(3 + i, m)] = C.bv * (Stf[i] * J[3 * m] + Stf[3 + i] * J[3 * m + 1] + Stf[6 + i] * J[3 * m + 2]);
+#pragma unroll
+            for (int i = 0; i < 3; i++)
+#pragma unroll
+                for (int m = 0; m <= i; m++) S[tri(3 + i, 3 + m)] = C.bv * C.bv * Sff[tri(i, m)];
+        }
+    }
+}
+
+
+// Backward Riccati sweep: for k = N-1..0 factor stage k against P_{k+1} and store Gamma' | Psi | P12 | P22.
+// Returns false if a pivot was not positive.
+template <int N, int NC>
+__device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, const StageC &C, int lane)
+{
+    using L_ = WLay<N, NC>;
+    double *Pc = sm + L_::oP, *Ex = sm + L_::oEx;
+    const int grp = lane / 6, cb = lane - 6 * grp;
+    // Phi column cb:  (M Phi)[:,cb] = ga M[:,ja] + gb M[:,jb]   and   (Phi' x)[cb] likewise
+    const double ga = cb == 0 ? C.F.dc : (cb == 1 ? -C.F.dsn : C.F.dt), gb = cb == 0 ? C.F.dsn : (cb == 1 ? C.F.dc : 0.0);
+    const int ja = cb < 2 ? 0 : cb, jb = cb < 2 ? 1 : cb;
+    const double sq1 = P.scale * P.q[cb], sq2 = P.scale * P.q[6 + cb];
+    // P_N = s Q
+    for (int e = lane; e < 93; e += 32) {
+        double v = 0.0;
+        if (e < 36) { if (e / 6 == e % 6) v = P.scale * P.q[e / 6]; }
+        else if (e >= 72) {
+            const int t = e - 72;
+            if (t == 0 || t == 2 || t == 5 || t == 9 || t == 14 || t == 20) {
+                const int d = t == 0 ? 0 : t == 2 ? 1 : t == 5 ? 2 : t == 9 ? 3 : t == 14 ? 4 : 5;
+                v = P.scale * P.q[6 + d];
+            }
+        }
+        Pc[e] = v;
+    }
+    __syncwarp();
+    bool ok = true;
+#pragma unroll 1
+    for (int k = N - 1; k >= 0; k--) {
+        double *St = sm + L_::oRic + k * L_::STG;
+        for (int e = lane; e < 57; e += 32) St[72 + e] = Pc[36 + e];       // keep P12 | P22 of P_{k+1} for the solves
+        double L1[21], d1[6], Sr[21];
+#pragma unroll
+        for (int e = 0; e < 21; e++) { L1[e] = Pc[72 + e]; Sr[e] = sm[L_::oS + 21 * k + e]; }
+        ok = ldl6(L1, d1) && ok;
+        // K = D^-1 + L' S L
+        double Kr[21];
+        {
+            double SL[36];
+#pragma unroll
+            for (int i = 0; i < 6; i++)
+#pragma unroll
+                for (int b = 0; b < 6; b++) {
+                    double acc = Sr[i >= b ? tri(i, b) : tri(b, i)];
+#pragma unroll
+                    for (int j = b + 1; j < 6; j++) acc = fma(Sr[i >= j ? tri(i, j) : tri(j, i)], L1[tri(j, b)], acc);
+                    SL[6 * i + b] = acc;
+                }
+#pragma unroll
+            for (int a = 0; a < 6; a++)
+#pragma unroll
+                for (int b = 0; b <= a; b++) {
+                    double acc = SL[6 * a + b];
+#pragma unroll
+                    for (int i = a + 1; i < 6; i++) acc = fma(L1[tri(i, a)], SL[6 * i + b], acc);
+                    Kr[tri(a, b)] = acc;
+                }
+#pragma unroll
+            for (int a = 0; a < 6; a++) Kr[tri(a, a)] += d1[a];
+        }
+        double d2[6];
+        ok = ldl6(Kr, d2) && ok;
+        // column pipeline: Gamma [ I | P21 | P22 ]  ->  Gamma | A21 | A22     (lane = column, 18 lanes)
+        double col[6];
+        if (lane < 18) {
+#pragma unroll
+            for (int i = 0; i < 6; i++)
+                col[i] = grp == 0 ? (i == cb ? 1.0 : 0.0) : (grp == 1 ? Pc[36 + 6 * cb + i] : Pc[72 + trs(i, cb)]);
+            fsub6(L1, col);
+#pragma unroll
+            for (int i = 0; i < 6; i++) col[i] *= d1[i];
+            fsub6(Kr, col);
+#pragma unroll
+            for (int i = 0; i < 6; i++) col[i] *= d2[i];
+            bsub6(Kr, col);
+            lmul6(L1, col);
+        }
+        double a11[6];
+        if (lane < 12) {
+            double v[6], wv[6];
+#pragma unroll
+            for (int i = 0; i < 6; i++) {
+                double acc = 0.0;
+#pragma unroll
+                for (int j = 0; j < 6; j++) acc = fma(Sr[i >= j ? tri(i, j) : tri(j, i)], col[j], acc);
+                v[i] = acc;
+            }
+#pragma unroll
+            for (int i = 0; i < 6; i++) {
+                double acc = 0.0;
+#pragma unroll
+                for (int j = 0; j < 6; j++) acc = fma(Pc[36 + 6 * i + j], v[j], acc);
+                wv[i] = acc;
+            }
+            if (grp == 0) {
+                double pw[6];
+                phiT6(C.F, wv, pw);
+#pragma unroll
+                for (int i = 0; i < 6; i++) { St[36 + 6 * i + cb] = wv[i]; St[6 * i + cb] = col[i] - pw[i]; }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 6; i++) { a11[i] = Pc[6 * i + cb] - wv[i]; Ex[6 * i + cb] = a11[i]; Ex[36 + 6 * i + cb] = col[i]; }
+            }
+        } else if (lane < 18) {
+#pragma unroll
+            for (int i = 0; i < 6; i++) Ex[72 + 6 * i + cb] = col[i];
+        }
+        __syncwarp();
+        if (k > 0) {
+            // P_k = s Q + Abar' Ptilde Abar
+            if (lane < 18) {
+                double m12[6];
+#pragma unroll
+                for (int i = 0; i < 6; i++) m12[i] = Ex[36 + 6 * cb + i] + ga * Ex[6 * i + ja] + gb * Ex[6 * i + jb];
+                if (grp == 0) {
+#pragma unroll
+                    for (int i = 0; i < 6; i++) Pc[36 + 6 * i + cb] = m12[i];
+                } else if (grp == 1) {
+#pragma unroll
+                    for (int i = 0; i < 6; i++) Pc[6 * i + cb] = a11[i] + (i == cb ? sq1 : 0.0);
+                } else {
+                    double pm[6];
+                    phiT6(C.F, m12, pm);
+#pragma unroll
+                    for (int i = 0; i < 6; i++) {
+                        const double val = col[i] + pm[i] + ga * Ex[36 + 6 * i + ja] + gb * Ex[36 + 6 * i + jb] + (i == cb ? sq2 : 0.0);
+                        if (i >= cb) Pc[72 + tri(i, 0) + cb] = val;
+                    }
+                }
+            }
+            __syncwarp();
+        }
+    }
+    return ok;
+}
+
+
+// Solve (M^-1 + S) y = t with the stored stage factors.  In: t in vA.  Out: zeta~ = Bm^T y in vA (what the
+// per-contact step needs: W_c^T y = zeta~_tau x r + zeta~_F).  G2 below denotes the stored Gamma - Phi^T Psi.
+template <int N, int NC>
+__device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int lane)
+{
+    using L_ = WLay<N, NC>;
+    double *vA = sm + L_::oVa, *vB = sm + L_::oVb, *vC = sm + L_::oVc;
+    const PhiC F = C.F;
+    // ---- pre (lane = stage): gt = Gamma^T t = G2^T t + Psi^T Phi t, c1 = P12 gt, c2 = Phi^T c1 + P22 gt
+    for (int k = lane; k < N; k += 32) {
+        const double *St = sm + L_::oRic + k * L_::STG;
+        double t[6], pt[6], gt[6], c1[6], c2[6], pc1[6];
+#pragma unroll
+        for (int i = 0; i < 6; i++) t[i] = vA[6 * k + i];
+        pt[0] = F.dc * t[0] - F.dsn * t[1]; pt[1] = F.dsn * t[0] + F.dc * t[1];            // Phi t
+        pt[2] = F.dt * t[2]; pt[3] = F.dt * t[3]; pt[4] = F.dt * t[4]; pt[5] = F.dt * t[5];
+#pragma unroll
+        for (int j = 0; j < 6; j++) {
+            double acc = 0.0;
+#pragma unroll
+            for (int i = 0; i < 6; i++) acc = fma(St[6 * i + j], t[i], fma(St[36 + 6 * i + j], pt[i], acc));
+            gt[j] = acc;
+        }
+#pragma unroll
+        for (int i = 0; i < 6; i++) {
+            double a1 = 0.0, a2 = 0.0;
+#pragma unroll
+            for (int j = 0; j < 6; j++) {
+                a1 = fma(St[72 + 6 * i + j], gt[j], a1);
+                a2 = fma(St[108 + (i >= j ? tri(i, j) : tri(j, i))], gt[j], a2);
+            }
+            c1[i] = a1; c2[i] = a2;
+        }
+        phiT6(F, c1, pc1);
+#pragma unroll
+        for (int i = 0; i < 6; i++) { vA[6 * k + i] = gt[i]; vB[6 * k + i] = c1[i]; vC[6 * k + i] = c2[i] + pc1[i]; }
+    }
+    __syncwarp();
+    // ---- backward sweep (lane r < 12 holds p_r):  p1 <- p1 - Psi p2 + c1 ;  p2 <- Phi^T p1 + G2 p2 + c2
+    const int r6 = lane < 6 ? lane : (lane < 12 ? lane - 6 : 0);
+    // Phi column r6 (for Phi^T x) and Phi row r6 (for Phi x)
+    const double ga = r6 == 0 ? F.dc : (r6 == 1 ? -F.dsn : F.dt), gb = r6 == 0 ? F.dsn : (r6 == 1 ? F.dc : 0.0);
+    const double fa = r6 == 0 ? F.dc : (r6 == 1 ? F.dsn : F.dt), fb = r6 == 0 ? -F.dsn : (r6 == 1 ? F.dc : 0.0);
+    const int ja = r6 < 2 ? 0 : r6, jb = r6 < 2 ? 1 : r6;
+    {
+        double p = 0.0;
+#pragma unroll 2
+        for (int k = N - 1; k >= 0; k--) {
+            const double *St = sm + L_::oRic + k * L_::STG;
+            const double *row = St + (lane < 6 ? 36 : 0) + 6 * r6;        // Psi row (lanes 0-5) / G2 row (6-11)
+            const double cadd = lane < 6 ? vB[6 * k + r6] : vC[6 * k + r6];
+            double acc0 = 0.0, acc1 = 0.0;
+#pragma unroll
+            for (int j = 0; j < 6; j += 2) {
+                acc0 = fma(row[j], __shfl_sync(kFullMask, p, 6 + j), acc0);
+                acc1 = fma(row[j + 1], __shfl_sync(kFullMask, p, 7 + j), acc1);
+            }
+            const double pa = __shfl_sync(kFullMask, p, ja), pb = __shfl_sync(kFullMask, p, jb);
+            if (lane >= 6 && lane < 12) vC[6 * k + r6] = p;               // p2 of P_{k+1}, for b_k and the output
+            const double acc = acc0 + acc1;
+            p = lane < 6 ? (p - acc + cadd) : (ga * pa + gb * pb + acc + cadd);
+        }
+    }
+    __syncwarp();
+    // ---- b_k = gt_k - S_k Gamma p2,  Gamma p2 = G2 p2 + Phi^T Psi p2   (lane = stage)
+    for (int k = lane; k < N; k += 32) {
+        const double *St = sm + L_::oRic + k * L_::STG, *S = sm + L_::oS + 21 * k;
+        double p2[6], ps[6], pp[6], g[6];
+#pragma unroll
+        for (int i = 0; i < 6; i++) p2[i] = vC[6 * k + i];
+#pragma unroll
+        for (int i = 0; i < 6; i++) {
+            double acc = 0.0;
+#pragma unroll
+            for (int j = 0; j < 6; j++) acc = fma(St[36 + 6 * i + j], p2[j], acc);
+            ps[i] = acc;
+        }
+        phiT6(F, ps, pp);
+#pragma unroll
+        for (int i = 0; i < 6; i++) {
+            double acc = pp[i];
+#pragma unroll
+            for (int j = 0; j < 6; j++) acc = fma(St[6 * i + j], p2[j], acc);
+            g[i] = acc;
+        }
+#pragma unroll
+        for (int i = 0; i < 6; i++) {
+            double acc = vA[6 * k + i];
+#pragma unroll
+            for (int j = 0; j < 6; j++) acc = fma(-S[i >= j ? tri(i, j) : tri(j, i)], g[j], acc);
+            vA[6 * k + i] = acc;
+        }
+    }
+    __syncwarp();
+    // ---- forward sweep (lane r < 12 holds y_r):  y1 <- y1 + Phi y2 ;  y2 <- b + G2^T y2 - Psi^T y1
+    {
+        double y = 0.0;
+#pragma unroll 2
+        for (int k = 0; k < N; k++) {
+            const double *St = sm + L_::oRic + k * L_::STG;
+            const double bk = vA[6 * k + r6];
+            double acc0 = 0.0, acc1 = 0.0;
+#pragma unroll
+            for (int i = 0; i < 6; i++) {
+                acc0 = fma(St[6 * i + r6], __shfl_sync(kFullMask, y, 6 + i), acc0);
+                acc1 = fma(-St[36 + 6 * i + r6], __shfl_sync(kFullMask, y, i), acc1);
+            }
+            const double ya = __shfl_sync(kFullMask, y, 6 + ja), yb = __shfl_sync(kFullMask, y, 6 + jb);
+            y = lane < 6 ? (y + fa * ya + fb * yb) : (bk + acc0 + acc1);
+            if (lane < 6) vB[6 * k + r6] = y;
+            else if (lane < 12) vA[6 * k + r6] = y;
+        }
+    }
+    __syncwarp();
+    // ---- output (lane = stage): y_k = P12^T y1 + P22 y2 + p2 ; zeta~ = Bm^T y_k
+    for (int k = lane; k < N; k += 32) {
+        const double *St = sm + L_::oRic + k * L_::STG;
+        double y1[6], y2[6], z[6];
+#pragma unroll
+        for (int i = 0; i < 6; i++) { y1[i] = vB[6 * k + i]; y2[i] = vA[6 * k + i]; }
+#pragma unroll
+        for (int i = 0; i < 6; i++) {
+            double acc = vC[6 * k + i];
+#pragma unroll
+            for (int j = 0; j < 6; j++) acc = fma(St[72 + 6 * j + i], y1[j], fma(St[108 + (i >= j ? tri(i, j) : tri(j, i))], y2[j], acc));
+            z[i] = acc;
+        }
+        const double *J = C.J;
+        vA[6 * k + 0] = J[0] * z[0] + J[3] * z[1] + J[6] * z[2];
+        vA[6 * k + 1] = J[1] * z[0] + J[4] * z[1] + J[7] * z[2];
+        vA[6 * k + 2] = J[2] * z[0] + J[5] * z[1] + J[8] * z[2];
+        vA[6 * k + 3] = C.bv * z[3]; vA[6 * k + 4] = C.bv * z[4]; vA[6 * k + 5] = C.bv * z[5];
+    }
+    __syncwarp();
+}
+
+
+// grad f(u) = s r u + W^T (M W u + h): per-stage wrench, state rollout, adjoint sweep (all O(N)), then the
+// per-stage co-state wrench in physical units (Bm^T v) is left in V for the per-contact pass.
+template <int N, int NC>
+__device__ __forceinline__ void gradient_sweeps(double *sm, const DevParams &P, const StageC &C, int lane)
+{
+    using L_ = WLay<N, NC>;
+    double *w = sm + L_::oW, *X = sm + L_::oXs, *L1 = sm + L_::oL1, *V = sm + L_::oV;
+    const double *E = sm + L_::oE;
+    const PhiC F = C.F;
+    // w_k = Bm sum_c [r x f ; f]    (lane = stage)                                   (mpc.cpp:213-254)
+    for (int k = lane; k < N; k += 32) {
+        double tt[3] = {0, 0, 0}, tf[3] = {0, 0, 0};
+        for (int j = 0; j < NC; j++) {
+            const int c = k * NC + j;
+            const double *r = sm + L_::oR + 3 * c, *f = sm + L_::oU + 3 * c;
+            tt[0] += r[1] * f[2] - r[2] * f[1]; tt[1] += r[2] * f[0] - r[0] * f[2]; tt[2] += r[0] * f[1] - r[1] * f[0];
+            tf[0] += f[0]; tf[1] += f[1]; tf[2] += f[2];
+        }
+        const double *J = C.J;
+        w[6 * k + 0] = J[0] * tt[0] + J[1] * tt[1] + J[2] * tt[2];
+        w[6 * k + 1] = J[3] * tt[0] + J[4] * tt[1] + J[5] * tt[2];
+        w[6 * k + 2] = J[6] * tt[0] + J[7] * tt[1] + J[8] * tt[2];
+        w[6 * k + 3] = C.bv * tf[0]; w[6 * k + 4] = C.bv * tf[1]; w[6 * k + 5] = C.bv * tf[2];
+    }
+    __syncwarp();
+    const int r6 = lane < 6 ? lane : (lane < 12 ? lane - 6 : 0);
+    const double ga = r6 == 0 ? F.dc : (r6 == 1 ? -F.dsn : F.dt), gb = r6 == 0 ? F.dsn : (r6 == 1 ? F.dc : 0.0);   // Phi column
+    const double fa = r6 == 0 ? F.dc : (r6 == 1 ? F.dsn : F.dt), fb = r6 == 0 ? -F.dsn : (r6 == 1 ? F.dc : 0.0);   // Phi row
+    const int ja = r6 < 2 ? 0 : r6, jb = r6 < 2 ? 1 : r6;
+    const double sq = lane < 12 ? P.scale * P.q[lane] : 0.0;
+    // X[k] = response of state k+1 to the wrenches (zero initial state): (omega, v) part, then (theta, p) part
+    if (lane >= 6 && lane < 12) {
+        double acc = 0.0;
+#pragma unroll
+        for (int k = 0; k < N; k++) { acc += w[6 * k + r6]; X[12 * k + lane] = acc; }
+    }
+    __syncwarp();
+    if (lane < 6) {
+        double acc = 0.0;
+        X[lane] = 0.0;
+#pragma unroll
+        for (int k = 1; k < N; k++) { acc += fa * X[12 * (k - 1) + 6 + ja] + fb * X[12 * (k - 1) + 6 + jb]; X[12 * k + lane] = acc; }
+    }
+    __syncwarp();
+    // adjoint: lam1 (theta, p) suffix sums, then lam2 (omega, v);  V[k] = lam2 at state k+1
+    if (lane < 6) {
+        double acc = 0.0;
+#pragma unroll
+        for (int k = N - 1; k >= 0; k--) { acc += sq * (E[12 * k + lane] + X[12 * k + lane]); L1[6 * k + lane] = acc; }
+    }
+    __syncwarp();
+    if (lane >= 6 && lane < 12) {
+        double acc = 0.0;
+#pragma unroll
+        for (int k = N - 1; k >= 0; k--) {
+            acc += sq * (E[12 * k + lane] + X[12 * k + lane]);
+            if (k < N - 1) acc += ga * L1[6 * (k + 1) + ja] + gb * L1[6 * (k + 1) + jb];
+            V[6 * k + r6] = acc;
+        }
+    }
+    __syncwarp();
+    for (int k = lane; k < N; k += 32) {                          // V <- Bm^T V
+        double *v = V + 6 * k;
+        const double *J = C.J;
+        const double v0 = v[0], v1 = v[1], v2 = v[2];
+        v[0] = J[0] * v0 + J[3] * v1 + J[6] * v2;
+        v[1] = J[1] * v0 + J[4] * v1 + J[7] * v2;
+        v[2] = J[2] * v0 + J[5] * v1 + J[8] * v2;
+        v[3] *= C.bv; v[4] *= C.bv; v[5] *= C.bv;
+    }
+    __syncwarp();
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// fused solve kernel: blockDim.x = 32 * warps_per_block, warp -> problem
+// ------------------------------------------------------------------------------------------------
+template <int N, int NC>
+__global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParams P, const BatchPtrs io, long long B)
+{
+    using L_ = WLay<N, NC>;
+    constexpr int NU = 3 * NC, NV = NU * N, NCN = NC * N;
+    extern __shared__ double sm_all[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double *sm = sm_all + (size_t)warp * L_::oEnd;
+    const long long b = (long long)blockIdx.x * (blockDim.x >> 5) + warp;
+    if (b >= B) return;
+    double *rr = sm + L_::oR, *cfl = sm + L_::oCf, *u = sm + L_::oU, *sl = sm + L_::oSl, *lam = sm + L_::oLam;
+    double *gf = sm + L_::oGf, *Dst = sm + L_::oDst, *prod = sm + L_::oProd, *tv = sm + L_::oTv, *E = sm + L_::oE;
+    double *dsv = sm + L_::oRic, *dlv = sm + L_::oRic + 6 * NCN;     // alias: valid only after the corrector solve
+    const double *gx0 = io.x0 + b * NS, *gxr = io.x_ref + b * (N * NS), *gct = io.contact + b * NCN;
+    const double *gch = io.c_hor + b * (NCN * 3), *gpc = io.p_com + b * (N * 3);
+    const double sr = P.sr, mu = P.mu;
+
+    // ---- linearise (mpc.cpp:153-221) and stage the inputs ----------------------------------------
+    Lin lin;
+    linearise(P, gxr, N, lin);
+    StageC C;
+#pragma unroll
+    for (int i = 0; i < 9; i++) C.J[i] = lin.Iwi[i] * P.dt;
+    C.bv = P.bv;
+    C.F.dc = P.dt * lin.c; C.F.dsn = P.dt * lin.s; C.F.dt = P.dt;
+    const double cz = lin.c, sz = lin.s;
+    int bad_bounds = 0, n_st_lane = 0;
+    for (int c = lane; c < NCN; c += 32) {
+        const int k = c / NC;
+        rr[3 * c] = gch[3 * c] - gpc[3 * k]; rr[3 * c + 1] = gch[3 * c + 1] - gpc[3 * k + 1]; rr[3 * c + 2] = gch[3 * c + 2] - gpc[3 * k + 2];
+        const double cf = gct[c];
+        const double lo = P.fz_min * cf, hi = P.fz_max * cf;         // mpc.cpp:344,350
+        if (hi < lo) bad_bounds = 1;
+        cfl[c] = cf;
+        n_st_lane += hi > lo ? 1 : 0;
+    }
+    // free-response error e_k = A^(k+1) x0 - xref_k on the 12 weighted states (mpc.cpp:256-270,369-375)
+    {
+        double x0r[13];
+#pragma unroll
+        for (int i = 0; i < 13; i++) x0r[i] = gx0[i];
+        const double g0 = x0r[12], dt = P.dt;
+        for (int k = lane; k < N; k += 32) {
+            const double kk = (double)(k + 1);
+            const double *xr = gxr + k * NS;
+            double *Ek = E + 12 * k;
+            Ek[0] = x0r[0] + kk * dt * (cz * x0r[6] - sz * x0r[7]) - xr[0];
+            Ek[1] = x0r[1] + kk * dt * (sz * x0r[6] + cz * x0r[7]) - xr[1];
+            Ek[2] = x0r[2] + kk * dt * x0r[8] - xr[2];
+            Ek[3] = x0r[3] + kk * dt * x0r[9] - xr[3];
+            Ek[4] = x0r[4] + kk * dt * x0r[10] - xr[4];
+            Ek[5] = x0r[5] + kk * dt * x0r[11] + (0.5 * kk * (kk - 1.0)) * dt * dt * g0 - xr[5];
+            Ek[6] = x0r[6] - xr[6]; Ek[7] = x0r[7] - xr[7]; Ek[8] = x0r[8] - xr[8];
+            Ek[9] = x0r[9] - xr[9]; Ek[10] = x0r[10] - xr[10]; Ek[11] = x0r[11] + kk * dt * g0 - xr[11];
+        }
+    }
+    __syncwarp();
+    // start point: weight shared by the stance contacts of each step, clamped into the interior
+    for (int c = lane; c < NCN; c += 32) {
+        const int k = c / NC;
+        int ns = 0;
+        for (int j = 0; j < NC; j++) { const double cj = cfl[k * NC + j]; ns += (P.fz_max * cj > P.fz_min * cj) ? 1 : 0; }
+        const double cf = cfl[c], lo = P.fz_min * cf, hi = P.fz_max * cf;
+        const bool st = hi > lo;
+        double fz = 0.0;
+        double *s6 = sl + 6 * c, *l6 = lam + 6 * c;
+        if (st) {
+            const double span = hi - lo;
+            fz = P.weight / (double)ns;
+            fz = fmin(fmax(fz, lo + 0.1 * span), hi - 0.1 * span);
+            s6[0] = mu * fz; s6[1] = mu * fz; s6[2] = mu * fz; s6[3] = mu * fz; s6[4] = hi - fz; s6[5] = fz - lo;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 6; i++) s6[i] = 1.0;
+        }
+        u[3 * c] = 0.0; u[3 * c + 1] = 0.0; u[3 * c + 2] = fz;
+#pragma unroll
+        for (int i = 0; i < 6; i++) l6[i] = 0.0;
+    }
+    int n_stance = n_st_lane;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) n_stance += __shfl_xor_sync(kFullMask, n_stance, o);
+    const double m_ineq = 6.0 * (double)(n_stance > 0 ? n_stance : 1);
+    __syncwarp();
+
+    int status = G1MPC_MAX_ITER, it = 0;
+    double gap = 0.0, rdmax = 0.0;
+    bool lam_init = false;
+
+#pragma unroll 1
+    for (it = 0;; it++) {
+        // (1) gradient: V <- Bm^T (M W u + h)
+        gradient_sweeps<N, NC>(sm, P, C, lane);
+        const double *Vt = sm + L_::oV;
+        // (2) per contact: grad f, dual residual, gap, D-state of the 3x3 block, predictor t = -Dblk^-1 grad f
+        double p_gap = 0.0, p_rd = 0.0, p_gf = 0.0;
+        for (int c = lane; c < NCN; c += 32) {
+            const int k = c / NC;
+            const double *vk = Vt + 6 * k, *r = rr + 3 * c, *uc = u + 3 * c;
+            const double g0 = sr * uc[0] + (vk[1] * r[2] - vk[2] * r[1]) + vk[3];
+            const double g1 = sr * uc[1] + (vk[2] * r[0] - vk[0] * r[2]) + vk[4];
+            const double g2 = sr * uc[2] + (vk[0] * r[1] - vk[1] * r[0]) + vk[5];
+            gf[3 * c] = g0; gf[3 * c + 1] = g1; gf[3 * c + 2] = g2;
+            const double cf = cfl[c];
+            if (P.fz_max * cf > P.fz_min * cf) p_gf = fmax(p_gf, fmax(fabs(g0), fmax(fabs(g1), fabs(g2))));
+        }
+        if (!lam_init) {
+            // lambda_0 = mu0 / s with mu0 tied to the gradient scale at the start point
+            const double mu0 = fmax(1e-2, 0.1 * wmax(p_gf));
+            for (int c = lane; c < NCN; c += 32) {
+                const double cf = cfl[c];
+                if (P.fz_max * cf > P.fz_min * cf) {
+#pragma unroll
+                    for (int i = 0; i < 6; i++) lam[6 * c + i] = mu0 / sl[6 * c + i];
+                }
+            }
+            lam_init = true;
+        }
+        for (int c = lane; c < NCN; c += 32) {
+            const double cf = cfl[c];
+            double t0 = 0.0, t1 = 0.0, t2 = 0.0;
+            if (P.fz_max * cf > P.fz_min * cf) {
+                const double *s6 = sl + 6 * c, *l6 = lam + 6 * c;
+                const double g0 = gf[3 * c], g1 = gf[3 * c + 1], g2 = gf[3 * c + 2];
+                const double r0 = g0 + l6[0] - l6[1], r1 = g1 + l6[2] - l6[3];
+                const double r2 = g2 - mu * (l6[0] + l6[1] + l6[2] + l6[3]) + l6[4] - l6[5];
+                p_rd = fmax(p_rd, fmax(fabs(r0), fmax(fabs(r1), fabs(r2))));
+                double D[6];
+#pragma unroll
+                for (int i = 0; i < 6; i++) { p_gap += s6[i] * l6[i]; D[i] = l6[i] / s6[i]; }
+                // Dblk = sr I + Cb' D Cb = [[a,0,e],[0,b,f],[e,f,cc]] ; LDL' with a cancellation-free Schur term
+                const double a = sr + D[0] + D[1], bq = sr + D[2] + D[3];
+                const double d2 = sr + D[4] + D[5] + mu * mu * ((sr * (D[0] + D[1]) + 4.0 * D[0] * D[1]) / a +
+                                                                (sr * (D[2] + D[3]) + 4.0 * D[2] * D[3]) / bq);
+                double *Ds = Dst + 9 * c;
+#pragma unroll
+                for (int i = 0; i < 6; i++) Ds[i] = D[i];
+                Ds[6] = 1.0 / a; Ds[7] = 1.0 / bq; Ds[8] = 1.0 / d2;
+                double Di[6];
+                contact_dinv(Ds, sr, mu, Di);
+                t0 = -(Di[0] * g0 + Di[1] * g1 + Di[2] * g2);
+                t1 = -(Di[1] * g0 + Di[3] * g1 + Di[4] * g2);
+                t2 = -(Di[2] * g0 + Di[4] * g1 + Di[5] * g2);
+            }
+            tv[3 * c] = t0; tv[3 * c + 1] = t1; tv[3 * c + 2] = t2;
+        }
+        gap = wsum(p_gap) / m_ineq; rdmax = wmax(p_rd);
+        if (!(gap == gap) || !(rdmax == rdmax) || isinf(gap) || isinf(rdmax)) { status = G1MPC_NUMERICAL; break; }
+        if (gap <= P.gap_tol || n_stance == 0) { status = G1MPC_SOLVED; break; }
+        if (it >= P.max_iter) { status = G1MPC_MAX_ITER; break; }
+        __syncwarp();
+
+        // (3) S_k, t_k, then the backward Riccati sweep (shared by predictor and corrector)
+        assemble_stage<N, NC, true>(sm, P, C, lane);
+        __syncwarp();
+        if (!factor_stages<N, NC>(sm, P, C, lane)) { status = G1MPC_NUMERICAL; break; }
+        // (4) predictor
+        solve_stages<N, NC>(sm, C, lane);
+        const double *zt = sm + L_::oVa;
+        double p_min = 1e300, p_sum = 0.0;
+        for (int c = lane; c < NCN; c += 32) {
+            const double cf = cfl[c];
+            if (!(P.fz_max * cf > P.fz_min * cf)) continue;
+            const int k = c / NC;
+            const double *z = zt + 6 * k, *r = rr + 3 * c, *Ds = Dst + 9 * c, *s6 = sl + 6 * c, *l6 = lam + 6 * c;
+            double rt[3], X[18];
+            rt[0] = -gf[3 * c] - ((z[1] * r[2] - z[2] * r[1]) + z[3]);
+            rt[1] = -gf[3 * c + 1] - ((z[2] * r[0] - z[0] * r[2]) + z[4]);
+            rt[2] = -gf[3 * c + 2] - ((z[0] * r[1] - z[1] * r[0]) + z[5]);
+            contact_X(Ds, sr, mu, X);
+#pragma unroll
+            for (int i = 0; i < 6; i++) {
+                const double dsi = -(X[3 * i] * rt[0] + X[3 * i + 1] * rt[1] + X[3 * i + 2] * rt[2]);
+                const double dli = -l6[i] - Ds[i] * dsi;
+                if (dsi < 0.0) p_min = fmin(p_min, -s6[i] / dsi);
+                if (dli < 0.0) p_min = fmin(p_min, -l6[i] / dli);
+                prod[6 * c + i] = dsi * dli;
+                p_sum += dsi * dli;
+            }
+        }
+        const double a_aff = fmin(1.0, wmin(p_min));
+        // sum (s + a ds)(lam + a dl) = (1 - a) s'lam + a^2 ds'dl for the affine direction
+        const double g_aff = ((1.0 - a_aff) * gap * m_ineq + a_aff * a_aff * wsum(p_sum)) / m_ineq;
+        double sig = g_aff / gap;
+        sig = sig * sig * sig;
+        const double sigma_gap = sig * gap;
+        // (5) corrector right-hand side: t = Dblk^-1 (-grad f + Cb'((ds dl - sigma mu)/s))
+        for (int c = lane; c < NCN; c += 32) {
+            const double cf = cfl[c];
+            if (!(P.fz_max * cf > P.fz_min * cf)) continue;
+            const double *s6 = sl + 6 * c;
+            double q6[6], Di[6];
+#pragma unroll
+            for (int i = 0; i < 6; i++) q6[i] = (prod[6 * c + i] - sigma_gap) / s6[i];
+            const double r0 = -gf[3 * c] + (q6[0] - q6[1]);
+            const double r1 = -gf[3 * c + 1] + (q6[2] - q6[3]);
+            const double r2 = -gf[3 * c + 2] + (-mu * (q6[0] + q6[1] + q6[2] + q6[3]) + q6[4] - q6[5]);
+            contact_dinv(Dst + 9 * c, sr, mu, Di);
+            tv[3 * c] = Di[0] * r0 + Di[1] * r1 + Di[2] * r2;
+            tv[3 * c + 1] = Di[1] * r0 + Di[3] * r1 + Di[4] * r2;
+            tv[3 * c + 2] = Di[2] * r0 + Di[4] * r1 + Di[5] * r2;
+#pragma unroll
+            for (int i = 0; i < 6; i++) prod[6 * c + i] = q6[i];
+        }
+        __syncwarp();
+        assemble_stage<N, NC, false>(sm, P, C, lane);
+        __syncwarp();
+        solve_stages<N, NC>(sm, C, lane);
+        // (6) combined direction, step length (the stage storage is dead now: ds | dl live there)
+        p_min = 1e300;
+        for (int c = lane; c < NCN; c += 32) {
+            const double cf = cfl[c];
+            if (!(P.fz_max * cf > P.fz_min * cf)) continue;
+            const int k = c / NC;
+            const double *z = zt + 6 * k, *r = rr + 3 * c, *Ds = Dst + 9 * c, *s6 = sl + 6 * c, *l6 = lam + 6 * c, *q6 = prod + 6 * c;
+            double rt[3], X[18], Di[6];
+            rt[0] = -gf[3 * c] + (q6[0] - q6[1]) - ((z[1] * r[2] - z[2] * r[1]) + z[3]);
+            rt[1] = -gf[3 * c + 1] + (q6[2] - q6[3]) - ((z[2] * r[0] - z[0] * r[2]) + z[4]);
+            rt[2] = -gf[3 * c + 2] + (-mu * (q6[0] + q6[1] + q6[2] + q6[3]) + q6[4] - q6[5]) - ((z[0] * r[1] - z[1] * r[0]) + z[5]);
+            contact_dinv(Ds, sr, mu, Di);
+            contact_X(Ds, sr, mu, X);
+            tv[3 * c] = Di[0] * rt[0] + Di[1] * rt[1] + Di[2] * rt[2];
+            tv[3 * c + 1] = Di[1] * rt[0] + Di[3] * rt[1] + Di[4] * rt[2];
+            tv[3 * c + 2] = Di[2] * rt[0] + Di[4] * rt[1] + Di[5] * rt[2];
+#pragma unroll
+            for (int i = 0; i < 6; i++) {
+                const double dsi = -(X[3 * i] * rt[0] + X[3 * i + 1] * rt[1] + X[3 * i + 2] * rt[2]);
+                const double dli = -l6[i] - q6[i] - Ds[i] * dsi;
+                if (dsi < 0.0) p_min = fmin(p_min, -s6[i] / dsi);
+                if (dli < 0.0) p_min = fmin(p_min, -l6[i] / dli);
+                dsv[6 * c + i] = dsi; dlv[6 * c + i] = dli;
+            }
+        }
+        const double alpha = fmin(1.0, 0.995 * wmin(p_min));
+        // (7) step (same lane -> same contacts as in (6): no barrier needed)
+        for (int c = lane; c < NCN; c += 32) {
+            const double cf = cfl[c];
+            if (!(P.fz_max * cf > P.fz_min * cf)) continue;
+#pragma unroll
+            for (int p = 0; p < 3; p++) u[3 * c + p] += alpha * tv[3 * c + p];
+#pragma unroll
+            for (int i = 0; i < 6; i++) {
+                lam[6 * c + i] += alpha * dlv[6 * c + i];
+                sl[6 * c + i] += alpha * dsv[6 * c + i];
+            }
+        }
+        __syncwarp();
+    }
+
+    // ---- outputs ------------------------------------------------------------------------------------
+    if (status == G1MPC_NUMERICAL) {            // a failed factorisation leaves the scratch in solve-phase state
+        __syncwarp();
+        gradient_sweeps<N, NC>(sm, P, C, lane);
+    }
+    __syncwarp();
+    // here w = W u, X = state response, gf = grad f(u) are consistent with the returned u
+    bad_bounds = __any_sync(kFullMask, bad_bounds);
+    if (bad_bounds && status == G1MPC_SOLVED) status = G1MPC_BAD_BOUNDS;
+    double *gu = io.u_opt + b * NV;
+    for (int i = lane; i < NV; i += 32) gu[i] = u[i];
+    if (io.status && lane == 0) io.status[b] = status;
+    if (io.iters && lane == 0) io.iters[b] = it;
+    const double *wv = sm + L_::oW, *Xs = sm + L_::oXs;
+    if (io.resid) {
+        double obj = 0.0, pv = 0.0;
+        for (int i = lane; i < NV; i += 32) obj += 0.5 * sr * u[i] * u[i];
+        // 1/2 u'Hu + g'u = 1/2 sr |u|^2 + 1/2 sum sQ (e^2 - E^2),  e = E + X
+        for (int e = lane; e < 12 * N; e += 32) obj += 0.5 * P.scale * P.q[e % 12] * Xs[e] * (2.0 * E[e] + Xs[e]);
+        for (int c = lane; c < NCN; c += 32) {
+            const double fx = u[3 * c], fy = u[3 * c + 1], fz = u[3 * c + 2];
+            const double cf = cfl[c], lo = P.fz_min * cf, hi = fmax(P.fz_max * cf, lo);
+            pv = fmax(pv, fmax(fabs(fx) - mu * fz, fabs(fy) - mu * fz));
+            pv = fmax(pv, fmax(fz - hi, lo - fz));
+        }
+        obj = wsum(obj); pv = wmax(pv);
+        if (lane == 0) {
+            double *r = io.resid + b * 4;
+            r[0] = gap; r[1] = rdmax; r[2] = fmax(pv, 0.0); r[3] = obj;
+        }
+    }
+    if (io.y_opt) {
+        // multipliers of the reference's 5 rows per contact (OSQP sign: y<0 at a lower bound)
+        double *gy = io.y_opt + b * (5 * NCN);
+        for (int c = lane; c < NCN; c += 32) {
+            double y5[5];
+            const double cf = cfl[c];
+            if (P.fz_max * cf > P.fz_min * cf) {
+                const double *l6 = lam + 6 * c;
+                y5[0] = -l6[1]; y5[1] = l6[0]; y5[2] = -l6[3]; y5[3] = l6[2]; y5[4] = l6[4] - l6[5];
+            } else {
+                // swing contact: any sign-feasible multiplier set that balances the gradient
+                const double g0 = gf[3 * c], g1 = gf[3 * c + 1], g2 = gf[3 * c + 2];
+                y5[0] = y5[1] = y5[2] = y5[3] = 0.0;
+                if (-g0 <= 0.0) y5[0] = -g0; else y5[1] = -g0;
+                if (-g1 <= 0.0) y5[2] = -g1; else y5[3] = -g1;
+                y5[4] = -g2 - mu * (y5[0] - y5[1] + y5[2] - y5[3]);
+            }
+#pragma unroll
+            for (int i = 0; i < 5; i++) gy[5 * c + i] = y5[i];
+        }
+    }
+    // rollout (mpc.cpp:427-446) in closed form; x_opt is in/out
+    {
+        double *gx = io.x_opt + b * (N * NS);
+        const double *xc = io.x_current ? io.x_current + b * NS : gx;
+        const int last = io.one_rollout ? 1 : N - 1;
+        for (int e = lane; e < (last + 1) * NS; e += 32) {
+            const int i = e / NS, r = e % NS;
+            if (i == 0) { if (io.x_current) gx[r] = xc[r]; continue; }
+            const double dt = P.dt, di = (double)i;
+            double val;
+            if (r < 3) {        // theta_i = theta_c + dt Rz (i w_c + sum_{j<i-1} (i-1-j) ww_j)
+                double a0 = di * xc[6], a1 = di * xc[7], a2 = di * xc[8];
+                for (int j = 0; j + 1 < i; j++) {
+                    const double f = (double)(i - 1 - j);
+                    a0 += f * wv[6 * j]; a1 += f * wv[6 * j + 1]; a2 += f * wv[6 * j + 2];
+                }
+                const double rot = r == 0 ? (cz * a0 - sz * a1) : (r == 1 ? (sz * a0 + cz * a1) : a2);
+                val = xc[r] + dt * rot;
+            } else if (r < 6) { // p_i = p_c + dt (i v_c + C(i,2) dt g e_z + sum (i-1-j) wv_j)
+                const int ax = r - 3;
+                double a = di * xc[9 + ax];
+                if (ax == 2) a += 0.5 * di * (di - 1.0) * dt * xc[12];
+                for (int j = 0; j + 1 < i; j++) a += (double)(i - 1 - j) * wv[6 * j + 3 + ax];
+                val = xc[r] + dt * a;
+            } else if (r < 9) {
+                double a = xc[r];
+                for (int j = 0; j < i; j++) a += wv[6 * j + r - 6];
+                val = a;
+            } else if (r < 12) {
+                double a = xc[r];
+                if (r == 11) a += di * dt * xc[12];
+                for (int j = 0; j < i; j++) a += wv[6 * j + 3 + r - 9];
+                val = a;
+            } else val = xc[12];
+            gx[i * NS + r] = val;
+        }
+    }
+}
+
+} // namespace v2
