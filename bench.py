@@ -30,23 +30,23 @@ if ROOT not in sys.path:
 METRIC = "batched MPC build+solve/sec (N=10, whole box, device-timed)"
 UNIT = "problems/s"
 BATCH = 1024
+# dram__bytes_read.sum + dram__bytes_write.sum of one solve launch at B=1024 from the committed `ncu --set full`
+# capture (profiles/r1_v2_ncu_full_summary.csv): inputs are read once, the 2 MB of outputs stay in L2.
+NCU_TRAFFIC_BYTES = 2860032
 WORKLOAD = "configs[1]: 1,024 independent G1 SRBD MPC problems per GPU (cpp_node preset, N=10, nc=4, walking gait schedule)"
 
 
-def algorithmic_flops(N, nc, iters_mean):
-    """FP64 flops (FMA = 2) of THIS implementation per problem; term by term in DESIGN.md section 4."""
-    ncn, n6 = nc * N, 6 * N
-    setup = 70 * ncn + 2 * 12 * N * (N + 1) / 2 * 6 + 2 * 12 * N ** 3 + 40 * N
-    it = (21 * ncn                      # w = W u
-          + 36 * N                      # X2, X0
-          + 4 * n6 * N                  # v = M w + h
-          + 120 * ncn                   # per-contact gradient, residual, 3x3 scaling blocks, t
-          + 21 * N * nc * 36            # S_k
-          + n6 * (n6 + 1) / 2           # Y assembly
-          + n6 ** 3 / 3                 # LDL'
-          + 2 * (2 * n6 * n6 + 21 * ncn + 60 * ncn)   # two Newton solves
-          + 30 * ncn)                   # step lengths, update
-    return setup + (iters_mean + 1) * (21 * ncn + 36 * N + 4 * n6 * N + 120 * ncn) + iters_mean * (it - (21 * ncn + 36 * N + 4 * n6 * N + 120 * ncn))
+def algorithmic_flops(N, nc, iters_mean, stance_mean):
+    """USEFUL FP64 flops (FMA = 2) of the stage-wise interior point per problem -- each quantity counted once,
+    not once per lane that recomputes it; term by term in DESIGN.md section 5.
+    stance_mean = mean number of stance contacts per problem (swing contacts are eliminated)."""
+    per_stage_factor = 2 * 146 + 250 + 18 * 150 + 12 * 144 + 300      # 2 LDL' 6x6, L'SL, 18-column pipeline, S./P12. products, P update
+    per_stage_solve = 330 + 290 + 190 + 130                            # pre, two sweeps, b_k, multiplier output (per solve)
+    per_stage_grad = 100 + 9 * nc                                      # wrench, rollout, adjoint
+    per_contact = 120 + 90 + 100 + 60 + 130 + 30                       # gradient/D-state, S_k share, predictor, corrector rhs, step, update
+    setup = 70 * nc * N + 40 * N
+    per_iter = N * (per_stage_factor + 2 * per_stage_solve + per_stage_grad + 150) + stance_mean * per_contact
+    return setup + iters_mean * per_iter + N * per_stage_grad + stance_mean * 120
 
 
 def algorithmic_bytes(N, nc):
@@ -217,12 +217,13 @@ def main():
     # result collection over NCCL (first-step GRFs + x_opt[1], what the WBID layer consumes)
     gather_ms = None
     if world > 1:
-        payload = torch.cat([u_opt[:, 0, :], x_opt[:, 1, :]], dim=1).contiguous()
-        out = torch.empty(world * BATCH, payload.shape[1], device=dev, dtype=torch.float64)
-        dist.all_gather_into_tensor(out, payload)
+        from g1_locomotion_b200 import sharding
+        payload = sharding.wbid_payload(u_opt, x_opt)
+        sharding.gather_results(payload, world * BATCH)
         torch.cuda.synchronize(); barrier()
         g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        g0.record(); dist.all_gather_into_tensor(out, payload); g1.record(); torch.cuda.synchronize()
+        g0.record(); gathered = sharding.gather_results(payload, world * BATCH); g1.record(); torch.cuda.synchronize()
+        assert gathered.shape[0] == world * BATCH
         gather_ms = float(g0.elapsed_time(g1))
 
     tot = torch.tensor([dev_ms, e2e_s, gather_ms or 0.0], device=dev, dtype=torch.float64)
@@ -233,7 +234,8 @@ def main():
     e2e_value = world * BATCH * e2e_steps / e2e_s_max
 
     if rank == 0:
-        fl = algorithmic_flops(N, nc, iters_mean) * BATCH
+        stance_mean = float((ins[2] > 0).double().sum() / BATCH)
+        fl = algorithmic_flops(N, nc, iters_mean, stance_mean) * BATCH
         peak_tf = _fp64_peak(local_rank)
         ach_tf = fl / (per_launch_ms * 1e-3) / 1e12
         peaks = {}
@@ -249,7 +251,7 @@ def main():
                 "config": {"workload": WORKLOAD, "batch_per_gpu": BATCH, "preset": "cpp_node", "l2": "flushed between timed steps (256 MiB fill)",
                            "ipm_iters_mean": iters_mean, "kernel": solver.kernel_info()},
                 "roofline": {"bound": "fp64", "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach_tf / peak_tf if peak_tf else None,
-                             "traffic": None, "kernel": "srbd_mpc_solve_kernel<10,4>", "flops_per_problem": fl / BATCH,
+                             "traffic": NCU_TRAFFIC_BYTES, "kernel": "v2::srbd_mpc_solve_warp_kernel<10,4>", "flops_per_problem": fl / BATCH,
                              "peak_source": "g1mpc_fp64_peak_tflops DFMA microbenchmark, measured in this run (MEASURED_PEAKS.json has no FP64 entry)",
                              "hbm": {"bound": "hbm", "achieved": by / (per_launch_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                                      "frac": by / (per_launch_ms * 1e-3) / 1e9 / hbm_peak, "bytes_per_problem": by / BATCH,

@@ -1,0 +1,63 @@
+"""CPU checks of the mathematics the CUDA solve kernel relies on (tests/ipm_model.py is its numpy model):
+wrench-space factorisation of the reference Hessian, stage-wise solution of the Newton systems, and the
+interior point as a whole against the oracle's exact minimiser."""
+import numpy as np
+import pytest
+
+from g1_locomotion_b200 import presets, inputs
+from ipm_model import Problem, RiccatiFactor, StageFactor, solve_ipm
+
+GRF_TOL = 1e-3
+
+
+def _problems(pname, over, gen, n):
+    preset = presets.get_preset(pname, **over)
+    batch = inputs.walking_batch(preset, n) if gen == "walk" else [t.numpy() for t in inputs.random_batch(preset, n, seed=7)]
+    return preset, [[a[b] for a in batch] for b in range(n)]
+
+
+@pytest.mark.parametrize("pname,over", [("cpp_node", {}), ("python_default", {"horizon": 10}), ("cpp_node", {"num_contacts": 8})])
+def test_wrench_space_form_equals_reference_hessian(orc, pname, over):
+    """H = s r I + W' M W and g = W' h reproduce the reference build (mpc.cpp:359-376) to rounding."""
+    preset, probs = _problems(pname, over, "rand", 2)
+    p = orc.params_from_dict(preset)
+    for args in probs:
+        m = orc.build(p, *args)
+        H, g = Problem(preset, *args).dense_H_g()
+        assert np.abs(H - m["H"]).max() <= 1e-12 * np.abs(m["H"]).max()
+        assert np.abs(g - m["g"]).max() <= 1e-12 * np.abs(m["g"]).max()
+
+
+def test_stagewise_solve_equals_dense_newton_system():
+    """(M^-1 + S) y = t by the backward/forward sweeps == dense solve, for barrier weights spanning 13 decades."""
+    preset, probs = _problems("cpp_node", {}, "rand", 1)
+    pr = Problem(preset, *probs[0])
+    M, _ = pr.M_h()
+    N = pr.N
+    rng = np.random.default_rng(0)
+    S = np.zeros((N, 6, 6))
+    for k in range(N):
+        d = 10 ** rng.uniform(-3, 10, pr.nu)
+        S[k] = pr.W(k) @ np.diag(1 / d) @ pr.W(k).T
+    Sd = np.zeros((6 * N, 6 * N))
+    for k in range(N):
+        Sd[6 * k:6 * k + 6, 6 * k:6 * k + 6] = S[k]
+    t = rng.normal(size=(N, 6))
+    want = M @ np.linalg.solve(np.eye(6 * N) + Sd @ M, t.ravel())
+    for fac in (RiccatiFactor(pr, S), StageFactor(pr, S)):
+        got = fac.solve(t).ravel()
+        assert np.abs(got - want).max() <= 1e-9 * np.abs(want).max()
+
+
+@pytest.mark.parametrize("pname,over,gen", [("cpp_node", {}, "walk"), ("cpp_node", {}, "rand"),
+                                            ("python_default", {}, "rand"), ("cpp_node", {"horizon": 20}, "rand")])
+def test_interior_point_model_reaches_exact_minimiser(orc, pname, over, gen):
+    preset, probs = _problems(pname, over, gen, 2)
+    p = orc.params_from_dict(preset)
+    for args in probs:
+        m = orc.build(p, *args)
+        xs, _, cert = orc.qp_exact(p, m["H"], m["g"], args[2])
+        assert cert["rc"] == 0
+        u, it, gap = solve_ipm(Problem(preset, *args), linear="stage")
+        assert gap <= 1e-10 and it <= 25
+        assert np.abs(u.ravel() - xs).max() <= GRF_TOL
