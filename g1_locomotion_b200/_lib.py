@@ -7,7 +7,7 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libg1mpc_b200.so")
+LIB_PATH = os.environ.get("G1MPC_B200_LIB") or os.path.join(_HERE, "libg1mpc_b200.so")   # override: A/B runs of two builds
 _lib = None
 
 EXPORTS = ["g1mpc_create", "g1mpc_destroy", "g1mpc_solve_batch", "g1mpc_emit_qp_batch", "g1mpc_update_host",

@@ -60,13 +60,15 @@ struct WLay {
     static constexpr int oSl = oU + NCN * 3;        // [NCN*6] slacks
     static constexpr int oLam = oSl + NCN * 6;      // [NCN*6] multipliers
     static constexpr int oGf = oLam + NCN * 6;      // [NCN*3] grad f(u)
-    static constexpr int oDst = oGf + NCN * 3;      // [NCN*9] D0..D5 = lam/s, 1/a, 1/b, 1/d2 of the 3x3 block
-    static constexpr int oProd = oDst + NCN * 9;    // [NCN*6] predictor ds*dl (Mehrotra second-order term)
+    static constexpr int oDst = oGf + NCN * 3;      // [NCN*9] 1/s (6), 1/a, 1/b, 1/d2 of the 3x3 block
+    static constexpr int oProd = oDst + NCN * 9;    // [NCN*6] predictor ds*dl (Mehrotra second-order term), then q
     static constexpr int oTv = oProd + NCN * 6;     // [NCN*3] Dblk^-1 rhs, then du
     // ---- per stage ----
-    static constexpr int oE = oTv + NCN * 3;        // [N*12]  free-response error A^(k+1) x0 - xref_k (mpc.cpp:369-375)
+    static constexpr int oSt = oTv + NCN * 3;       // [(NCN+1)/2] int32 list of stance contacts (compacted)
+    static constexpr int oE = oSt + (NCN + 1) / 2;  // [N*12]  free-response error A^(k+1) x0 - xref_k (mpc.cpp:369-375)
     static constexpr int oS = oE + N * 12;          // [N*21]  S_k packed
-    static constexpr int STG = 36 + 36 + 36 + 21;   // per stage: Gamma' | Psi | P12 | P22(packed) of P_{k+1}
+    static constexpr int STG = 36 + 36 + 36 + 21 + 36;   // per stage: G2 = Gamma - Phi^T Psi | Psi | P12 | P22(packed) of P_{k+1} | Gamma
+    // (Gamma is kept beside G2: rebuilding it as G2 + Phi^T Psi cancels badly on long horizons -- measured at N = 40)
     static constexpr int oRic = oS + N * 21;        // [N*STG] ; after the corrector solve: ds | dl  (needs 12 NCN <= STG N)
     static constexpr int oP = oRic + N * STG;       // [36+36+21] running P11 | P12 | P22(packed)
     // ---- scratch, three users: gradient sweeps | factor exchange | solve vectors ----
@@ -145,29 +147,31 @@ __device__ __forceinline__ void phiT6(const PhiC &F, const double (&x)[6], doubl
 }
 
 
-// 3x3 block of one stance contact from the stored D-state: Dinv (symmetric, 6: 00,01,02,11,12,22)
-__device__ __forceinline__ void contact_dinv(const double *Ds, double sr, double mu, double (&Di)[6])
+// 3x3 block of one stance contact, Dblk = sr I + Cb' D Cb = [[a,0,e],[0,b,f],[e,f,c]], from D0..D3 = lam/s of the
+// four friction rows and the stored reciprocals ia = 1/a, ib = 1/b, id2 = 1/(Schur complement):
+// Dinv (symmetric, 6: 00,01,02,11,12,22)
+__device__ __forceinline__ void contact_dinv(double D0, double D1, double D2, double D3, double ia, double ib, double id2,
+                                             double mu, double (&Di)[6])
 {
-    const double ia = Ds[6], ib = Ds[7], id2 = Ds[8];
-    const double e = -mu * (Ds[0] - Ds[1]), f = -mu * (Ds[2] - Ds[3]);
+    const double e = -mu * (D0 - D1), f = -mu * (D2 - D3);
     const double l20 = e * ia, l21 = f * ib;
     Di[0] = ia + l20 * l20 * id2; Di[1] = l20 * l21 * id2; Di[2] = -l20 * id2;
     Di[3] = ib + l21 * l21 * id2; Di[4] = -l21 * id2; Di[5] = id2;
 }
 // X = Dblk^-1 Cb' (6 rows x 3) in the cancellation-free closed form: c_i' du must stay accurate to << s_i
 // near the solution, which a 3x3 mat-vec in (fx,fy,fz) coordinates cannot deliver.
-__device__ __forceinline__ void contact_X(const double *Ds, double sr, double mu, double (&X)[18])
+__device__ __forceinline__ void contact_X(double D0, double D1, double D2, double D3, double ia, double ib, double id2,
+                                          double sr, double mu, double (&X)[18])
 {
-    const double ia = Ds[6], ib = Ds[7], id2 = Ds[8];
-    const double e = -mu * (Ds[0] - Ds[1]), f = -mu * (Ds[2] - Ds[3]);
+    const double e = -mu * (D0 - D1), f = -mu * (D2 - D3);
     const double iad = ia * id2, ibd = ib * id2;
-    double x2 = -mu * (sr + 2.0 * Ds[1]) * iad;
+    double x2 = -mu * (sr + 2.0 * D1) * iad;
     X[0] = (1.0 - e * x2) * ia; X[1] = -f * x2 * ib; X[2] = x2;
-    x2 = -mu * (sr + 2.0 * Ds[0]) * iad;
+    x2 = -mu * (sr + 2.0 * D0) * iad;
     X[3] = (-1.0 - e * x2) * ia; X[4] = -f * x2 * ib; X[5] = x2;
-    x2 = -mu * (sr + 2.0 * Ds[3]) * ibd;
+    x2 = -mu * (sr + 2.0 * D3) * ibd;
     X[6] = -e * x2 * ia; X[7] = (1.0 - f * x2) * ib; X[8] = x2;
-    x2 = -mu * (sr + 2.0 * Ds[2]) * ibd;
+    x2 = -mu * (sr + 2.0 * D2) * ibd;
     X[9] = -e * x2 * ia; X[10] = (-1.0 - f * x2) * ib; X[11] = x2;
     X[12] = -e * id2 * ia; X[13] = -f * id2 * ib; X[14] = id2;
     X[15] = -X[12]; X[16] = -X[13]; X[17] = -id2;
@@ -198,7 +202,8 @@ __device__ __forceinline__ void assemble_stage(double *sm, const DevParams &P, c
             tf[0] += tv[0]; tf[1] += tv[1]; tf[2] += tv[2];
             if (WITH_S) {
                 double Di[6];
-                contact_dinv(sm + L_::oDst + 9 * c, P.sr, P.mu, Di);
+                const double *Ds = sm + L_::oDst + 9 * c, *l6 = sm + L_::oLam + 6 * c;
+                contact_dinv(l6[0] * Ds[0], l6[1] * Ds[1], l6[2] * Ds[2], l6[3] * Ds[3], Ds[6], Ds[7], Ds[8], P.mu, Di);
                 const double D00 = Di[0], D01 = Di[1], D02 = Di[2], D11 = Di[3], D12 = Di[4], D22 = Di[5];
                 // RD = skew(r) Dinv
                 const double a00 = -r2 * D01 + r1 * D02, a01 = -r2 * D11 + r1 * D12, a02 = -r2 * D12 + r1 * D22;
@@ -352,7 +357,7 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
                 double pw[6];
                 phiT6(C.F, wv, pw);
 #pragma unroll
-                for (int i = 0; i < 6; i++) { St[36 + 6 * i + cb] = wv[i]; St[6 * i + cb] = col[i] - pw[i]; }
+                for (int i = 0; i < 6; i++) { St[36 + 6 * i + cb] = wv[i]; St[6 * i + cb] = col[i] - pw[i]; St[129 + 6 * i + cb] = col[i]; }
             } else {
 #pragma unroll
                 for (int i = 0; i < 6; i++) { a11[i] = Pc[6 * i + cb] - wv[i]; Ex[6 * i + cb] = a11[i]; Ex[36 + 6 * i + cb] = col[i]; }
@@ -399,19 +404,17 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
     using L_ = WLay<N, NC>;
     double *vA = sm + L_::oVa, *vB = sm + L_::oVb, *vC = sm + L_::oVc;
     const PhiC F = C.F;
-    // ---- pre (lane = stage): gt = Gamma^T t = G2^T t + Psi^T Phi t, c1 = P12 gt, c2 = Phi^T c1 + P22 gt
+    // ---- pre (lane = stage): gt = Gamma^T t, c1 = P12 gt, c2 = Phi^T c1 + P22 gt
     for (int k = lane; k < N; k += 32) {
         const double *St = sm + L_::oRic + k * L_::STG;
-        double t[6], pt[6], gt[6], c1[6], c2[6], pc1[6];
+        double t[6], gt[6], c1[6], c2[6], pc1[6];
 #pragma unroll
         for (int i = 0; i < 6; i++) t[i] = vA[6 * k + i];
-        pt[0] = F.dc * t[0] - F.dsn * t[1]; pt[1] = F.dsn * t[0] + F.dc * t[1];            // Phi t
-        pt[2] = F.dt * t[2]; pt[3] = F.dt * t[3]; pt[4] = F.dt * t[4]; pt[5] = F.dt * t[5];
 #pragma unroll
         for (int j = 0; j < 6; j++) {
             double acc = 0.0;
 #pragma unroll
-            for (int i = 0; i < 6; i++) acc = fma(St[6 * i + j], t[i], fma(St[36 + 6 * i + j], pt[i], acc));
+            for (int i = 0; i < 6; i++) acc = fma(St[129 + 6 * i + j], t[i], acc);
             gt[j] = acc;
         }
 #pragma unroll
@@ -455,25 +458,17 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
         }
     }
     __syncwarp();
-    // ---- b_k = gt_k - S_k Gamma p2,  Gamma p2 = G2 p2 + Phi^T Psi p2   (lane = stage)
+    // ---- b_k = gt_k - S_k Gamma p2   (lane = stage)
     for (int k = lane; k < N; k += 32) {
         const double *St = sm + L_::oRic + k * L_::STG, *S = sm + L_::oS + 21 * k;
-        double p2[6], ps[6], pp[6], g[6];
+        double p2[6], g[6];
 #pragma unroll
         for (int i = 0; i < 6; i++) p2[i] = vC[6 * k + i];
 #pragma unroll
         for (int i = 0; i < 6; i++) {
             double acc = 0.0;
 #pragma unroll
-            for (int j = 0; j < 6; j++) acc = fma(St[36 + 6 * i + j], p2[j], acc);
-            ps[i] = acc;
-        }
-        phiT6(F, ps, pp);
-#pragma unroll
-        for (int i = 0; i < 6; i++) {
-            double acc = pp[i];
-#pragma unroll
-            for (int j = 0; j < 6; j++) acc = fma(St[6 * i + j], p2[j], acc);
+            for (int j = 0; j < 6; j++) acc = fma(St[129 + 6 * i + j], p2[j], acc);
             g[i] = acc;
         }
 #pragma unroll
@@ -618,6 +613,7 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
     double *rr = sm + L_::oR, *cfl = sm + L_::oCf, *u = sm + L_::oU, *sl = sm + L_::oSl, *lam = sm + L_::oLam;
     double *gf = sm + L_::oGf, *Dst = sm + L_::oDst, *prod = sm + L_::oProd, *tv = sm + L_::oTv, *E = sm + L_::oE;
     double *dsv = sm + L_::oRic, *dlv = sm + L_::oRic + 6 * NCN;     // alias: valid only after the corrector solve
+    int *stIdx = reinterpret_cast<int *>(sm + L_::oSt);
     const double *gx0 = io.x0 + b * NS, *gxr = io.x_ref + b * (N * NS), *gct = io.contact + b * NCN;
     const double *gch = io.c_hor + b * (NCN * 3), *gpc = io.p_com + b * (N * 3);
     const double sr = P.sr, mu = P.mu;
@@ -631,15 +627,23 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
     C.bv = P.bv;
     C.F.dc = P.dt * lin.c; C.F.dsn = P.dt * lin.s; C.F.dt = P.dt;
     const double cz = lin.c, sz = lin.s;
-    int bad_bounds = 0, n_st_lane = 0;
-    for (int c = lane; c < NCN; c += 32) {
+    int bad_bounds = 0, n_stance = 0;
+    for (int c0 = 0; c0 < NCN; c0 += 32) {
+        const int c = c0 + lane;
+        bool st = false;
+        if (c < NCN) {
         const int k = c / NC;
         rr[3 * c] = gch[3 * c] - gpc[3 * k]; rr[3 * c + 1] = gch[3 * c + 1] - gpc[3 * k + 1]; rr[3 * c + 2] = gch[3 * c + 2] - gpc[3 * k + 2];
         const double cf = gct[c];
         const double lo = P.fz_min * cf, hi = P.fz_max * cf;         // mpc.cpp:344,350
         if (hi < lo) bad_bounds = 1;
         cfl[c] = cf;
-        n_st_lane += hi > lo ? 1 : 0;
+        st = hi > lo;
+        }
+        // compacted list of stance contacts (order preserved)
+        const unsigned m = __ballot_sync(kFullMask, st);
+        if (st) stIdx[n_stance + __popc(m & ((1u << lane) - 1u))] = c;
+        n_stance += __popc(m);
     }
     // free-response error e_k = A^(k+1) x0 - xref_k on the 12 weighted states (mpc.cpp:256-270,369-375)
     {
@@ -684,9 +688,6 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
 #pragma unroll
         for (int i = 0; i < 6; i++) l6[i] = 0.0;
     }
-    int n_stance = n_st_lane;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) n_stance += __shfl_xor_sync(kFullMask, n_stance, o);
     const double m_ineq = 6.0 * (double)(n_stance > 0 ? n_stance : 1);
     __syncwarp();
 
@@ -699,57 +700,56 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         // (1) gradient: V <- Bm^T (M W u + h)
         gradient_sweeps<N, NC>(sm, P, C, lane);
         const double *Vt = sm + L_::oV;
-        // (2) per contact: grad f, dual residual, gap, D-state of the 3x3 block, predictor t = -Dblk^-1 grad f
-        double p_gap = 0.0, p_rd = 0.0, p_gf = 0.0;
-        for (int c = lane; c < NCN; c += 32) {
-            const int k = c / NC;
+        // (2) per stance contact: grad f, dual residual, gap, reciprocals and D-state of the 3x3 block,
+        //     predictor t = -Dblk^-1 grad f
+        double p_gf = 0.0;
+        for (int i = lane; i < n_stance; i += 32) {
+            const int c = stIdx[i], k = c / NC;
             const double *vk = Vt + 6 * k, *r = rr + 3 * c, *uc = u + 3 * c;
             const double g0 = sr * uc[0] + (vk[1] * r[2] - vk[2] * r[1]) + vk[3];
             const double g1 = sr * uc[1] + (vk[2] * r[0] - vk[0] * r[2]) + vk[4];
             const double g2 = sr * uc[2] + (vk[0] * r[1] - vk[1] * r[0]) + vk[5];
             gf[3 * c] = g0; gf[3 * c + 1] = g1; gf[3 * c + 2] = g2;
-            const double cf = cfl[c];
-            if (P.fz_max * cf > P.fz_min * cf) p_gf = fmax(p_gf, fmax(fabs(g0), fmax(fabs(g1), fabs(g2))));
+            p_gf = fmax(p_gf, fmax(fabs(g0), fmax(fabs(g1), fabs(g2))));
         }
         if (!lam_init) {
             // lambda_0 = mu0 / s with mu0 tied to the gradient scale at the start point
             const double mu0 = fmax(1e-2, 0.1 * wmax(p_gf));
-            for (int c = lane; c < NCN; c += 32) {
-                const double cf = cfl[c];
-                if (P.fz_max * cf > P.fz_min * cf) {
+            for (int i = lane; i < n_stance; i += 32) {
+                const int c = stIdx[i];
 #pragma unroll
-                    for (int i = 0; i < 6; i++) lam[6 * c + i] = mu0 / sl[6 * c + i];
-                }
+                for (int j = 0; j < 6; j++) lam[6 * c + j] = mu0 / sl[6 * c + j];
             }
             lam_init = true;
         }
-        for (int c = lane; c < NCN; c += 32) {
-            const double cf = cfl[c];
-            double t0 = 0.0, t1 = 0.0, t2 = 0.0;
-            if (P.fz_max * cf > P.fz_min * cf) {
-                const double *s6 = sl + 6 * c, *l6 = lam + 6 * c;
-                const double g0 = gf[3 * c], g1 = gf[3 * c + 1], g2 = gf[3 * c + 2];
-                const double r0 = g0 + l6[0] - l6[1], r1 = g1 + l6[2] - l6[3];
-                const double r2 = g2 - mu * (l6[0] + l6[1] + l6[2] + l6[3]) + l6[4] - l6[5];
-                p_rd = fmax(p_rd, fmax(fabs(r0), fmax(fabs(r1), fabs(r2))));
-                double D[6];
+        double p_gap = 0.0, p_rd = 0.0;
+        for (int i = lane; i < n_stance; i += 32) {
+            const int c = stIdx[i];
+            const double *s6 = sl + 6 * c, *l6 = lam + 6 * c;
+            const double g0 = gf[3 * c], g1 = gf[3 * c + 1], g2 = gf[3 * c + 2];
+            const double r0 = g0 + l6[0] - l6[1], r1 = g1 + l6[2] - l6[3];
+            const double r2 = g2 - mu * (l6[0] + l6[1] + l6[2] + l6[3]) + l6[4] - l6[5];
+            p_rd = fmax(p_rd, fmax(fabs(r0), fmax(fabs(r1), fabs(r2))));
+            double D[6];
+            double *Ds = Dst + 9 * c;
 #pragma unroll
-                for (int i = 0; i < 6; i++) { p_gap += s6[i] * l6[i]; D[i] = l6[i] / s6[i]; }
-                // Dblk = sr I + Cb' D Cb = [[a,0,e],[0,b,f],[e,f,cc]] ; LDL' with a cancellation-free Schur term
-                const double a = sr + D[0] + D[1], bq = sr + D[2] + D[3];
-                const double d2 = sr + D[4] + D[5] + mu * mu * ((sr * (D[0] + D[1]) + 4.0 * D[0] * D[1]) / a +
-                                                                (sr * (D[2] + D[3]) + 4.0 * D[2] * D[3]) / bq);
-                double *Ds = Dst + 9 * c;
-#pragma unroll
-                for (int i = 0; i < 6; i++) Ds[i] = D[i];
-                Ds[6] = 1.0 / a; Ds[7] = 1.0 / bq; Ds[8] = 1.0 / d2;
-                double Di[6];
-                contact_dinv(Ds, sr, mu, Di);
-                t0 = -(Di[0] * g0 + Di[1] * g1 + Di[2] * g2);
-                t1 = -(Di[1] * g0 + Di[3] * g1 + Di[4] * g2);
-                t2 = -(Di[2] * g0 + Di[4] * g1 + Di[5] * g2);
+            for (int j = 0; j < 6; j++) {
+                const double si = 1.0 / s6[j];
+                p_gap += s6[j] * l6[j];
+                D[j] = l6[j] * si;
+                Ds[j] = si;
             }
-            tv[3 * c] = t0; tv[3 * c + 1] = t1; tv[3 * c + 2] = t2;
+            // Dblk = sr I + Cb' D Cb = [[a,0,e],[0,b,f],[e,f,cc]] ; LDL' with a cancellation-free Schur term
+            const double ia = 1.0 / (sr + D[0] + D[1]), ib = 1.0 / (sr + D[2] + D[3]);
+            const double d2 = sr + D[4] + D[5] + mu * mu * ((sr * (D[0] + D[1]) + 4.0 * D[0] * D[1]) * ia +
+                                                            (sr * (D[2] + D[3]) + 4.0 * D[2] * D[3]) * ib);
+            const double id2 = 1.0 / d2;
+            Ds[6] = ia; Ds[7] = ib; Ds[8] = id2;
+            double Di[6];
+            contact_dinv(D[0], D[1], D[2], D[3], ia, ib, id2, mu, Di);
+            tv[3 * c] = -(Di[0] * g0 + Di[1] * g1 + Di[2] * g2);
+            tv[3 * c + 1] = -(Di[1] * g0 + Di[3] * g1 + Di[4] * g2);
+            tv[3 * c + 2] = -(Di[2] * g0 + Di[4] * g1 + Di[5] * g2);
         }
         gap = wsum(p_gap) / m_ineq; rdmax = wmax(p_rd);
         if (!(gap == gap) || !(rdmax == rdmax) || isinf(gap) || isinf(rdmax)) { status = G1MPC_NUMERICAL; break; }
@@ -761,94 +761,91 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         assemble_stage<N, NC, true>(sm, P, C, lane);
         __syncwarp();
         if (!factor_stages<N, NC>(sm, P, C, lane)) { status = G1MPC_NUMERICAL; break; }
-        // (4) predictor
+        // (4) predictor.  With x = ds/s:  dl = -lam (1 + x), and the largest feasible step is
+        //     1 / max_i max(-x_i, 1 + x_i)  -- no division per constraint.
         solve_stages<N, NC>(sm, C, lane);
         const double *zt = sm + L_::oVa;
-        double p_min = 1e300, p_sum = 0.0;
-        for (int c = lane; c < NCN; c += 32) {
-            const double cf = cfl[c];
-            if (!(P.fz_max * cf > P.fz_min * cf)) continue;
-            const int k = c / NC;
-            const double *z = zt + 6 * k, *r = rr + 3 * c, *Ds = Dst + 9 * c, *s6 = sl + 6 * c, *l6 = lam + 6 * c;
+        double p_rmax = 0.0, p_sum = 0.0;
+        for (int i = lane; i < n_stance; i += 32) {
+            const int c = stIdx[i], k = c / NC;
+            const double *z = zt + 6 * k, *r = rr + 3 * c, *Ds = Dst + 9 * c, *l6 = lam + 6 * c;
             double rt[3], X[18];
             rt[0] = -gf[3 * c] - ((z[1] * r[2] - z[2] * r[1]) + z[3]);
             rt[1] = -gf[3 * c + 1] - ((z[2] * r[0] - z[0] * r[2]) + z[4]);
             rt[2] = -gf[3 * c + 2] - ((z[0] * r[1] - z[1] * r[0]) + z[5]);
-            contact_X(Ds, sr, mu, X);
+            contact_X(l6[0] * Ds[0], l6[1] * Ds[1], l6[2] * Ds[2], l6[3] * Ds[3], Ds[6], Ds[7], Ds[8], sr, mu, X);
 #pragma unroll
-            for (int i = 0; i < 6; i++) {
-                const double dsi = -(X[3 * i] * rt[0] + X[3 * i + 1] * rt[1] + X[3 * i + 2] * rt[2]);
-                const double dli = -l6[i] - Ds[i] * dsi;
-                if (dsi < 0.0) p_min = fmin(p_min, -s6[i] / dsi);
-                if (dli < 0.0) p_min = fmin(p_min, -l6[i] / dli);
-                prod[6 * c + i] = dsi * dli;
+            for (int j = 0; j < 6; j++) {
+                const double dsi = -(X[3 * j] * rt[0] + X[3 * j + 1] * rt[1] + X[3 * j + 2] * rt[2]);
+                const double x = dsi * Ds[j];
+                const double dli = -l6[j] * (1.0 + x);
+                p_rmax = fmax(p_rmax, fmax(-x, 1.0 + x));
+                prod[6 * c + j] = dsi * dli;
                 p_sum += dsi * dli;
             }
         }
-        const double a_aff = fmin(1.0, wmin(p_min));
+        const double a_aff = fmin(1.0, 1.0 / wmax(p_rmax));
         // sum (s + a ds)(lam + a dl) = (1 - a) s'lam + a^2 ds'dl for the affine direction
         const double g_aff = ((1.0 - a_aff) * gap * m_ineq + a_aff * a_aff * wsum(p_sum)) / m_ineq;
         double sig = g_aff / gap;
         sig = sig * sig * sig;
         const double sigma_gap = sig * gap;
-        // (5) corrector right-hand side: t = Dblk^-1 (-grad f + Cb'((ds dl - sigma mu)/s))
-        for (int c = lane; c < NCN; c += 32) {
-            const double cf = cfl[c];
-            if (!(P.fz_max * cf > P.fz_min * cf)) continue;
-            const double *s6 = sl + 6 * c;
+        // (5) corrector right-hand side: t = Dblk^-1 (-grad f + Cb'q),  q = (ds dl - sigma mu)/s
+        for (int i = lane; i < n_stance; i += 32) {
+            const int c = stIdx[i];
+            const double *Ds = Dst + 9 * c, *l6 = lam + 6 * c;
             double q6[6], Di[6];
 #pragma unroll
-            for (int i = 0; i < 6; i++) q6[i] = (prod[6 * c + i] - sigma_gap) / s6[i];
+            for (int j = 0; j < 6; j++) q6[j] = (prod[6 * c + j] - sigma_gap) * Ds[j];
             const double r0 = -gf[3 * c] + (q6[0] - q6[1]);
             const double r1 = -gf[3 * c + 1] + (q6[2] - q6[3]);
             const double r2 = -gf[3 * c + 2] + (-mu * (q6[0] + q6[1] + q6[2] + q6[3]) + q6[4] - q6[5]);
-            contact_dinv(Dst + 9 * c, sr, mu, Di);
+            contact_dinv(l6[0] * Ds[0], l6[1] * Ds[1], l6[2] * Ds[2], l6[3] * Ds[3], Ds[6], Ds[7], Ds[8], mu, Di);
             tv[3 * c] = Di[0] * r0 + Di[1] * r1 + Di[2] * r2;
             tv[3 * c + 1] = Di[1] * r0 + Di[3] * r1 + Di[4] * r2;
             tv[3 * c + 2] = Di[2] * r0 + Di[4] * r1 + Di[5] * r2;
 #pragma unroll
-            for (int i = 0; i < 6; i++) prod[6 * c + i] = q6[i];
+            for (int j = 0; j < 6; j++) prod[6 * c + j] = q6[j];
         }
         __syncwarp();
         assemble_stage<N, NC, false>(sm, P, C, lane);
         __syncwarp();
         solve_stages<N, NC>(sm, C, lane);
-        // (6) combined direction, step length (the stage storage is dead now: ds | dl live there)
-        p_min = 1e300;
-        for (int c = lane; c < NCN; c += 32) {
-            const double cf = cfl[c];
-            if (!(P.fz_max * cf > P.fz_min * cf)) continue;
-            const int k = c / NC;
-            const double *z = zt + 6 * k, *r = rr + 3 * c, *Ds = Dst + 9 * c, *s6 = sl + 6 * c, *l6 = lam + 6 * c, *q6 = prod + 6 * c;
+        // (6) combined direction, step length (the stage storage is dead now: ds | dl live there).
+        //     dl = -lam (1 + x + q/lam)
+        p_rmax = 0.0;
+        for (int i = lane; i < n_stance; i += 32) {
+            const int c = stIdx[i], k = c / NC;
+            const double *z = zt + 6 * k, *r = rr + 3 * c, *Ds = Dst + 9 * c, *l6 = lam + 6 * c, *q6 = prod + 6 * c;
             double rt[3], X[18], Di[6];
             rt[0] = -gf[3 * c] + (q6[0] - q6[1]) - ((z[1] * r[2] - z[2] * r[1]) + z[3]);
             rt[1] = -gf[3 * c + 1] + (q6[2] - q6[3]) - ((z[2] * r[0] - z[0] * r[2]) + z[4]);
             rt[2] = -gf[3 * c + 2] + (-mu * (q6[0] + q6[1] + q6[2] + q6[3]) + q6[4] - q6[5]) - ((z[0] * r[1] - z[1] * r[0]) + z[5]);
-            contact_dinv(Ds, sr, mu, Di);
-            contact_X(Ds, sr, mu, X);
+            const double D0 = l6[0] * Ds[0], D1 = l6[1] * Ds[1], D2 = l6[2] * Ds[2], D3 = l6[3] * Ds[3];
+            contact_dinv(D0, D1, D2, D3, Ds[6], Ds[7], Ds[8], mu, Di);
+            contact_X(D0, D1, D2, D3, Ds[6], Ds[7], Ds[8], sr, mu, X);
             tv[3 * c] = Di[0] * rt[0] + Di[1] * rt[1] + Di[2] * rt[2];
             tv[3 * c + 1] = Di[1] * rt[0] + Di[3] * rt[1] + Di[4] * rt[2];
             tv[3 * c + 2] = Di[2] * rt[0] + Di[4] * rt[1] + Di[5] * rt[2];
 #pragma unroll
-            for (int i = 0; i < 6; i++) {
-                const double dsi = -(X[3 * i] * rt[0] + X[3 * i + 1] * rt[1] + X[3 * i + 2] * rt[2]);
-                const double dli = -l6[i] - q6[i] - Ds[i] * dsi;
-                if (dsi < 0.0) p_min = fmin(p_min, -s6[i] / dsi);
-                if (dli < 0.0) p_min = fmin(p_min, -l6[i] / dli);
-                dsv[6 * c + i] = dsi; dlv[6 * c + i] = dli;
+            for (int j = 0; j < 6; j++) {
+                const double dsi = -(X[3 * j] * rt[0] + X[3 * j + 1] * rt[1] + X[3 * j + 2] * rt[2]);
+                const double x = dsi * Ds[j];
+                const double rl = 1.0 + x + q6[j] / l6[j];
+                p_rmax = fmax(p_rmax, fmax(-x, rl));
+                dsv[6 * c + j] = dsi; dlv[6 * c + j] = -l6[j] * rl;
             }
         }
-        const double alpha = fmin(1.0, 0.995 * wmin(p_min));
+        const double alpha = fmin(1.0, 0.995 / wmax(p_rmax));
         // (7) step (same lane -> same contacts as in (6): no barrier needed)
-        for (int c = lane; c < NCN; c += 32) {
-            const double cf = cfl[c];
-            if (!(P.fz_max * cf > P.fz_min * cf)) continue;
+        for (int i = lane; i < n_stance; i += 32) {
+            const int c = stIdx[i];
 #pragma unroll
             for (int p = 0; p < 3; p++) u[3 * c + p] += alpha * tv[3 * c + p];
 #pragma unroll
-            for (int i = 0; i < 6; i++) {
-                lam[6 * c + i] += alpha * dlv[6 * c + i];
-                sl[6 * c + i] += alpha * dsv[6 * c + i];
+            for (int j = 0; j < 6; j++) {
+                lam[6 * c + j] += alpha * dlv[6 * c + j];
+                sl[6 * c + j] += alpha * dsv[6 * c + j];
             }
         }
         __syncwarp();
@@ -896,7 +893,9 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
                 y5[0] = -l6[1]; y5[1] = l6[0]; y5[2] = -l6[3]; y5[3] = l6[2]; y5[4] = l6[4] - l6[5];
             } else {
                 // swing contact: any sign-feasible multiplier set that balances the gradient
-                const double g0 = gf[3 * c], g1 = gf[3 * c + 1], g2 = gf[3 * c + 2];
+                const double *vk = sm + L_::oV + 6 * (c / NC), *r = rr + 3 * c;      // u = 0 here: grad f = W_c^T v
+                const double g0 = (vk[1] * r[2] - vk[2] * r[1]) + vk[3], g1 = (vk[2] * r[0] - vk[0] * r[2]) + vk[4];
+                const double g2 = (vk[0] * r[1] - vk[1] * r[0]) + vk[5];
                 y5[0] = y5[1] = y5[2] = y5[3] = 0.0;
                 if (-g0 <= 0.0) y5[0] = -g0; else y5[1] = -g0;
                 if (-g1 <= 0.0) y5[2] = -g1; else y5[3] = -g1;

@@ -112,6 +112,36 @@ def test_solve_random_vs_exact(orc, pname, over, B):
     print(pname, over, "worst |u-x*| = %.2e N, iters mean %.1f max %d" % (worst, iters.mean(), iters.max()))
 
 
+@pytest.mark.parametrize("N,B", [(10, 64), (20, 32), (40, 8)])
+def test_config4_horizon_sweep_nc8_kkt(orc, N, B):
+    """Config 4 (N = 10/20/40, 8 contact points, n up to 960): the exact active-set oracle needs minutes at
+    n = 960, so optimality is certified through the KKT conditions of the reference-built QP instead:
+    primal feasible, multipliers sign-correct, stationarity and complementarity at rounding level."""
+    preset = presets.get_preset("cpp_node", horizon=N, num_contacts=8)
+    batch = [t.numpy() for t in inputs.random_batch(preset, B, seed=11)]
+    s = _solver(preset)
+    ins = _dev(batch)
+    u, x, info = s.update_batch(*ins, x_current=ins[0], want_multipliers=True)
+    torch.cuda.synchronize()
+    st = info["status"].cpu().numpy()
+    assert np.all(st == 0), (np.unique(st, return_counts=True), info["iters"].max())
+    p = orc.params_from_dict(preset)
+    un, yn = u.cpu().numpy(), info["y"].cpu().numpy()
+    for b in range(3):
+        args = [a[b] for a in batch]
+        m = orc.build(p, *args)
+        xg = un[b].ravel()
+        r = orc.kkt_residuals(m["H"], m["g"], m["Acon"], m["l"], m["u"], xg, yn[b])
+        gs = 1 + np.abs(m["g"]).max()
+        assert r["primal"] <= 1e-9, r
+        assert r["stationarity"] <= 1e-7 * gs, (r, gs)
+        # s_i lam_i <= m * gap_tol by construction; the slack seen through the reference rows carries the rounding of
+        # u (|u| ~ 1e3 N) times multipliers of the size of the gradient, hence the relative term
+        assert r["complementarity"] <= 1e-6 + 1e-12 * np.abs(yn[b]).max() * np.abs(xg).max(), r
+        assert np.all(xg[np.repeat(args[2].ravel() == 0, 3)] == 0.0)
+    print("N=%d nc=8: iters mean %.1f max %d" % (N, info["iters"].double().mean(), info["iters"].max()))
+
+
 def test_fractional_and_all_swing_contacts(orc):
     preset = presets.get_preset("cpp_node")
     batch = [t.numpy().copy() for t in inputs.random_batch(preset, 8, seed=5)]
