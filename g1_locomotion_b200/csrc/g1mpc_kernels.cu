@@ -105,6 +105,7 @@ __device__ __forceinline__ double S2_entry(int a, int b, int N)
 }
 
 #include "srbd_solve_warp.cuh"
+#include "node_adaptors.cuh"
 
 // ------------------------------------------------------------------------------------------------
 // emit kernel: materialise the reference's dense intermediates (mpc.cpp:196-376) -- HBM-write bound
@@ -294,7 +295,11 @@ __global__ void fp64_peak_kernel(double *out, int iters)
 typedef void (*solve_fn)(const DevParams, const BatchPtrs, long long);
 struct KernelEntry { int N, NC; solve_fn fn; size_t smem; };   // smem = bytes per warp (= per problem)
 
+#ifdef G1MPC_DEV_SHAPE   /* development builds: only the bench shape */
+#define G1MPC_SHAPES(X) X(10, 4)
+#else
 #define G1MPC_SHAPES(X) X(10, 4) X(15, 4) X(20, 4) X(40, 4) X(10, 8) X(12, 8) X(20, 8) X(40, 8) X(5, 4) X(8, 4)
+#endif
 #define X_ENTRY(n, c) {n, c, v2::srbd_mpc_solve_warp_kernel<n, c>, v2::WLay<n, c>::bytes},
 const KernelEntry kKernels[] = {G1MPC_SHAPES(X_ENTRY)};
 #undef X_ENTRY
@@ -474,6 +479,44 @@ int g1mpc_update_host(g1mpc_handle *h, int64_t B, const double *x0, const double
     if (resid) memcpy(resid, hs + o_res, sizeof(double) * n_res);
     if (status) memcpy(status, hs_i, sizeof(int32_t) * B);
     if (iters) memcpy(iters, hs_i + B, sizeof(int32_t) * B);
+    return G1MPC_OK;
+}
+
+int g1mpc_walk_inputs_batch(g1mpc_handle *h, int64_t B, const double *x0, const double *contacts_now, const double *sim_time,
+                            const double *x_opt_prev, double *x_ref, double *contact, double *c_horizon, double *p_com,
+                            double *landing, void *stream)
+{
+    if (!h || B < 0 || (B > 0 && (!x0 || !contacts_now || !sim_time || !x_opt_prev || !x_ref || !contact || !c_horizon || !p_com))) {
+        g_last_error = "g1mpc_walk_inputs_batch: null argument"; return G1MPC_ERR_INVALID_ARGUMENT;
+    }
+    if (h->params.num_contacts != 4 || h->params.horizon > 10) {
+        g_last_error = "g1mpc_walk_inputs_batch: the node's gait table needs num_contacts == 4 and horizon <= 10";
+        return G1MPC_ERR_UNSUPPORTED_SHAPE;
+    }
+    if (B == 0) return G1MPC_OK;
+    CUDA_TRY(cudaSetDevice(h->device));
+    adaptors::WalkPtrs io{x0, contacts_now, sim_time, x_opt_prev, x_ref, contact, c_horizon, p_com, landing};
+    adaptors::walk_inputs_kernel<<<(unsigned)((B + 3) / 4), 128, 0, (cudaStream_t)stream>>>(io, (long long)B, h->params.horizon,
+                                                                                            h->params.dt, h->params.gravity);
+    CUDA_TRY(cudaGetLastError());
+    return G1MPC_OK;
+}
+
+int g1mpc_wbid_refs_batch(g1mpc_handle *h, int64_t B, const double *u_opt, const double *x_opt, const double *foot_positions,
+                          double wbid_mass, double *refs, void *stream)
+{
+    if (!h || B < 0 || (B > 0 && (!u_opt || !x_opt || !foot_positions || !refs)) || !(wbid_mass > 0)) {
+        g_last_error = "g1mpc_wbid_refs_batch: bad argument"; return G1MPC_ERR_INVALID_ARGUMENT;
+    }
+    if (h->params.num_contacts != 4 || h->params.horizon < 2) {
+        g_last_error = "g1mpc_wbid_refs_batch: the WBID layer has four contact frames (wbid.py:39-44)";
+        return G1MPC_ERR_UNSUPPORTED_SHAPE;
+    }
+    if (B == 0) return G1MPC_OK;
+    CUDA_TRY(cudaSetDevice(h->device));
+    adaptors::wbid_refs_kernel<<<(unsigned)((B + 127) / 128), 128, 0, (cudaStream_t)stream>>>(u_opt, x_opt, foot_positions, refs, (long long)B,
+                                                                                              h->params.horizon, wbid_mass);
+    CUDA_TRY(cudaGetLastError());
     return G1MPC_OK;
 }
 

@@ -50,42 +50,59 @@ __device__ __forceinline__ int trs(int i, int j) { return i >= j ? i * (i + 1) /
 
 // Shared-memory layout of one problem (offsets in doubles).  Regions that are never live at the same time
 // share storage; the comments say who owns what when.
+__host__ __device__ constexpr int ev(int x) { return (x + 1) & ~1; }
+
 template <int N, int NC>
 struct WLay {
     static constexpr int NCN = NC * N;
     // ---- per contact, persistent over the solve ----
     static constexpr int oR = 0;                    // [NCN*3] lever arm r = c - p_com            (mpc.cpp:229-233)
-    static constexpr int oCf = oR + NCN * 3;        // [NCN]   contact flag (multiplies fz bounds, mpc.cpp:344,350)
-    static constexpr int oU = oCf + NCN;            // [NCN*3] forces
-    static constexpr int oSl = oU + NCN * 3;        // [NCN*6] slacks
+    static constexpr int oCf = ev(oR + NCN * 3);        // [NCN]   contact flag (multiplies fz bounds, mpc.cpp:344,350)
+    static constexpr int oU = ev(oCf + NCN);            // [NCN*3] forces
+    static constexpr int oSl = ev(oU + NCN * 3);        // [NCN*6] slacks
     static constexpr int oLam = oSl + NCN * 6;      // [NCN*6] multipliers
     static constexpr int oGf = oLam + NCN * 6;      // [NCN*3] grad f(u)
-    static constexpr int oDst = oGf + NCN * 3;      // [NCN*9] 1/s (6), 1/a, 1/b, 1/d2 of the 3x3 block
-    static constexpr int oProd = oDst + NCN * 9;    // [NCN*6] predictor ds*dl (Mehrotra second-order term), then q
+    static constexpr int oDst = ev(oGf + NCN * 3);      // [NCN*9] 1/s (6), 1/a, 1/b, 1/d2 of the 3x3 block
+    static constexpr int oProd = ev(oDst + NCN * 9);    // [NCN*6] predictor ds*dl (Mehrotra second-order term), then q
     static constexpr int oTv = oProd + NCN * 6;     // [NCN*3] Dblk^-1 rhs, then du
-    // ---- per stage ----
+    // ---- per stage ----  (every region below starts on a 16-byte boundary: rows are read as double2)
     static constexpr int oSt = oTv + NCN * 3;       // [(NCN+1)/2] int32 list of stance contacts (compacted)
-    static constexpr int oE = oSt + (NCN + 1) / 2;  // [N*12]  free-response error A^(k+1) x0 - xref_k (mpc.cpp:369-375)
-    static constexpr int oS = oE + N * 12;          // [N*21]  S_k packed
-    static constexpr int STG = 36 + 36 + 36 + 21 + 36;   // per stage: G2 = Gamma - Phi^T Psi | Psi | P12 | P22(packed) of P_{k+1} | Gamma
+    static constexpr int oE = ev(oSt + (NCN + 1) / 2);   // [N*12]  free-response error A^(k+1) x0 - xref_k (mpc.cpp:369-375)
+    static constexpr int SST = 22;                  // S_k packed (21) + pad
+    static constexpr int oS = oE + N * 12;          // [N*SST]
+    // per stage: G2 = Gamma - Phi^T Psi | Psi | P12 of P_{k+1} | Gamma | P22 of P_{k+1} (packed 21 + pad)
     // (Gamma is kept beside G2: rebuilding it as G2 + Phi^T Psi cancels badly on long horizons -- measured at N = 40)
-    static constexpr int oRic = oS + N * 21;        // [N*STG] ; after the corrector solve: ds | dl  (needs 12 NCN <= STG N)
-    static constexpr int oP = oRic + N * STG;       // [36+36+21] running P11 | P12 | P22(packed)
+    static constexpr int sG2 = 0, sPsi = 36, sP12 = 72, sGam = 108, sP22 = 144, STG = 166;
+    static constexpr int oRic = oS + N * SST;       // [N*STG] ; after the corrector solve: ds | dl  (needs 12 NCN <= STG N)
     // ---- scratch, three users: gradient sweeps | factor exchange | solve vectors ----
-    static constexpr int oX = oP + 93;              // gradient: w[N*6] X[N*12] L1[N*6] V[N*6]
+    static constexpr int oX = oRic + N * STG;       // gradient: w[N*6] X[N*12] L1[N*6] V[N*6]
     static constexpr int oW = oX;                   //   w  [N*6]
     static constexpr int oXs = oW + N * 6;          //   X  [N*12]
     static constexpr int oL1 = oXs + N * 12;        //   L1 [N*6]
     static constexpr int oV = oL1 + N * 6;          //   V  [N*6]  (then Bm' V in place)
-    static constexpr int oVa = oX;                  // solve: vA [N*6]  t -> Gamma't -> b -> y2 -> zeta~
+    static constexpr int oVa = oX;                  // solve: vA [N*6]  t -> Gamma't -> b -> y2
     static constexpr int oVb = oVa + N * 6;         //        vB [N*6]  c1 -> y1
-    static constexpr int oVc = oVb + N * 6;         //        vC [N*6]  c2' -> p2 (saved)
-    static constexpr int oEx = oVc + N * 6;         // factor exchange: A11 | A21 | A22 [108]
-    static constexpr int scratch = (N * 30 > N * 18 + 108) ? N * 30 : N * 18 + 108;
-    static constexpr int oEnd = oX + scratch;
+    static constexpr int oVc = oVb + N * 6;         //        vC [N*6]  c2' -> y (multiplier wrench, output of the solve)
+    static constexpr int oVd = oVc + N * 6;         //        vD [N*6]  p2 of P_{k+1} (incoming co-state of stage k)
+    static constexpr int oPb = oVd + N * 6;         //        p1 exchange, double buffered [12]
+    static constexpr int oEx = oVd;                 // factor exchange: A21 [36] (dead before the solve starts)
+    static constexpr int scratch = (N * 30 > N * 24 + 12) ? ((N * 30 > 18 * N + 36) ? N * 30 : 18 * N + 36) : ((N * 24 + 12 > 18 * N + 36) ? N * 24 + 12 : 18 * N + 36);
+    static constexpr int oEnd = ev(oX + scratch);
     static_assert(12 * NCN <= STG * N, "ds|dl alias the stage storage: needs num_contacts <= 10");
     static constexpr size_t bytes = sizeof(double) * (size_t)oEnd;
 };
+
+// 1/d: MUFU.RCP64H seed (relative error 9.6e-7 measured on B200, profiles/micro/lat.cu) + one cubically convergent
+// step x (1 + e + e^2), e = 1 - d x: 2.2e-16 maximum relative error measured, 39 cycles dependent latency against 74 of
+// `1.0 / d`.  No special cases: every caller passes a finite, normal, non-zero value or the problem is discarded
+// afterwards by the NaN checks.
+__device__ __forceinline__ double frcp(double d)
+{
+    double x;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x) : "d"(d));
+    const double e = fma(-d, x, 1.0);
+    return fma(x, fma(e, e, e), x);
+}
 
 // LDL' of a symmetric positive definite 6x6 held packed (21) in registers; afterwards a[tri(i,j)], i>j, holds
 // the unit-lower factor and dinv[j] = 1/d_j.  Returns false on a non-positive pivot.
@@ -96,7 +113,7 @@ __device__ __forceinline__ bool ldl6(double (&a)[21], double (&dinv)[6])
     for (int j = 0; j < 6; j++) {
         const double dj = a[tri(j, j)];
         ok = ok && (dj > 0.0);
-        const double r = 1.0 / dj;
+        const double r = frcp(dj);
         dinv[j] = r;
         double col[6];
 #pragma unroll
@@ -111,7 +128,6 @@ __device__ __forceinline__ bool ldl6(double (&a)[21], double (&dinv)[6])
     }
     return ok;
 }
-
 // x <- L^-1 x  (unit lower, packed)
 __device__ __forceinline__ void fsub6(const double (&l)[21], double (&x)[6])
 {
@@ -128,13 +144,103 @@ __device__ __forceinline__ void bsub6(const double (&l)[21], double (&x)[6])
 #pragma unroll
         for (int i = 0; i < j; i++) x[i] = fma(-l[tri(j, i)], x[j], x[i]);
 }
-// x <- L x
-__device__ __forceinline__ void lmul6(const double (&l)[21], double (&x)[6])
+
+// adjugate (packed 00,10,11,20,21,22) and determinant of the symmetric 3x3 [[a,b,d],[b,c,e],[d,e,f]]
+__device__ __forceinline__ void adj3(double a, double b, double c, double d, double e, double f, double (&A)[6], double &det)
+{
+    A[0] = fma(c, f, -(e * e)); A[1] = fma(d, e, -(b * f)); A[2] = fma(a, f, -(d * d));
+    A[3] = fma(b, e, -(c * d)); A[4] = fma(b, d, -(a * e)); A[5] = fma(a, c, -(b * b));
+    det = fma(a, A[0], fma(b, A[1], d * A[3]));
+}
+
+// Inverse of a symmetric positive definite 6x6 (packed lower, 21) through its 3x3 blocks M = [[A,B'],[B,C]] in
+// closed form: two reciprocals on the dependent chain instead of the six of an LDL' (measured: the reciprocal
+// chain was the largest single item of the v3 profile).  Returns false if a leading minor is not positive.
+__device__ __forceinline__ bool inv6(const double (&m)[21], double (&o)[21])
+{
+    double aA[6], detA;
+    adj3(m[0], m[1], m[2], m[3], m[4], m[5], aA, detA);
+    const double r = frcp(detA);
+    const double B[3][3] = {{m[6], m[7], m[8]}, {m[10], m[11], m[12]}, {m[15], m[16], m[17]}};
+    double X0[3][3];                                   // B adj(A)
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        X0[i][0] = fma(B[i][0], aA[0], fma(B[i][1], aA[1], B[i][2] * aA[3]));
+        X0[i][1] = fma(B[i][0], aA[1], fma(B[i][1], aA[2], B[i][2] * aA[4]));
+        X0[i][2] = fma(B[i][0], aA[3], fma(B[i][1], aA[4], B[i][2] * aA[5]));
+    }
+    // Schur complement C - r X0 B'
+    double Sc[6];
+    {
+        const double Cm[6] = {m[9], m[13], m[14], m[18], m[19], m[20]};
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+#pragma unroll
+            for (int j = 0; j <= i; j++) {
+                const double g = fma(X0[i][0], B[j][0], fma(X0[i][1], B[j][1], X0[i][2] * B[j][2]));
+                Sc[tri(i, j)] = fma(-r, g, Cm[tri(i, j)]);
+            }
+    }
+    double aS[6], detS;
+    adj3(Sc[0], Sc[1], Sc[2], Sc[3], Sc[4], Sc[5], aS, detS);
+    const double r2 = frcp(detS);
+    const double aSf[3][3] = {{aS[0], aS[1], aS[3]}, {aS[1], aS[2], aS[4]}, {aS[3], aS[4], aS[5]}};
+    double Y0[3][3];                                   // adj(Sc) X0
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j < 3; j++) Y0[i][j] = fma(aSf[i][0], X0[0][j], fma(aSf[i][1], X0[1][j], aSf[i][2] * X0[2][j]));
+    const double rr2 = r * r2, rrr2 = r * rr2;
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j <= i; j++) {
+            const double w = fma(X0[0][i], Y0[0][j], fma(X0[1][i], Y0[1][j], X0[2][i] * Y0[2][j]));
+            o[tri(i, j)] = fma(rrr2, w, r * aA[tri(i, j)]);
+            o[tri(3 + i, 3 + j)] = r2 * aS[tri(i, j)];
+        }
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j < 3; j++) o[tri(3 + i, j)] = -rr2 * Y0[i][j];
+    return (m[0] > 0.0) && (aA[5] > 0.0) && (detA > 0.0) && (Sc[0] > 0.0) && (aS[5] > 0.0) && (detS > 0.0);
+}
+
+// 16-byte shared-memory accesses: p must be 16-byte aligned (every row / packed block of WLay is)
+__device__ __forceinline__ void ld6(const double *p, double (&v)[6])
+{
+    const double2 *q = reinterpret_cast<const double2 *>(p);
+    const double2 a = q[0], b = q[1], c = q[2];
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y;
+}
+__device__ __forceinline__ void st6(double *p, const double (&v)[6])
+{
+    double2 *q = reinterpret_cast<double2 *>(p);
+    q[0] = make_double2(v[0], v[1]); q[1] = make_double2(v[2], v[3]); q[2] = make_double2(v[4], v[5]);
+}
+__device__ __forceinline__ void ld22(const double *p, double (&v)[22])
+{
+    const double2 *q = reinterpret_cast<const double2 *>(p);
+#pragma unroll
+    for (int i = 0; i < 11; i++) { const double2 a = q[i]; v[2 * i] = a.x; v[2 * i + 1] = a.y; }
+}
+__device__ __forceinline__ double dot6(const double (&a)[6], const double (&b)[6])
+{
+    const double e = fma(a[4], b[4], fma(a[2], b[2], a[0] * b[0])), o = fma(a[5], b[5], fma(a[3], b[3], a[1] * b[1]));
+    return e + o;
+}
+
+// y = M x for a packed symmetric 6x6 in registers (S = 21, or 22 with the pad)
+template <int S>
+__device__ __forceinline__ void symmv6(const double (&M)[S], const double (&x)[6], double (&y)[6])
 {
 #pragma unroll
-    for (int i = 5; i >= 1; i--)
+    for (int i = 0; i < 6; i++) {
+        double acc = M[tri(i, 0)] * x[0];
 #pragma unroll
-        for (int j = 0; j < i; j++) x[i] = fma(l[tri(i, j)], x[j], x[i]);
+        for (int j = 1; j < 6; j++) acc = fma(M[i >= j ? tri(i, j) : tri(j, i)], x[j], acc);
+        y[i] = acc;
+    }
 }
 
 // (Phi x)[c] and (Phi' x)[c] for a 6-vector in registers, Phi = dt blockdiag(Rz, I)   (mpc.cpp:199,210)
@@ -228,7 +334,7 @@ __device__ __forceinline__ void assemble_stage(double *sm, const DevParams &P, c
         t[2] = J[6] * tt[0] + J[7] * tt[1] + J[8] * tt[2];
         t[3] = C.bv * tf[0]; t[4] = C.bv * tf[1]; t[5] = C.bv * tf[2];
         if (WITH_S) {
-            double *S = sm + L_::oS + 21 * k;
+            double *S = sm + L_::oS + L_::SST * k;
             // omega-omega = J Stt J'
             double JS[9];
 #pragma unroll
@@ -259,134 +365,120 @@ __device__ __forceinline__ void assemble_stage(double *sm, const DevParams &P, c
 }
 
 
-// Backward Riccati sweep: for k = N-1..0 factor stage k against P_{k+1} and store Gamma' | Psi | P12 | P22.
-// Returns false if a pivot was not positive.
+// Backward Riccati sweep: for k = N-1..0 factor stage k against P_{k+1} and store G2 | Psi | Gamma; P12 | P22 of
+// P_{k+1} are written straight into the stage slot by the previous step.  Per stage, with Pi = P22^-1 (closed form)
+// and T = Pi + S_k = L D L' (every lane, registers):  Gamma = T^-1 Pi, A21 = Gamma P21, A22 = Gamma P22 -- lane =
+// column of [ I | P21 | P22 ] (18 lanes), one 6x6 mat-vec and two substitutions each; then Psi = P12 S Gamma,
+// A11 = P11 - P12 S A21.
+// P11 stays in the registers of the six A21 lanes (one column each).  Returns false if a minor was not positive.
 template <int N, int NC>
 __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, const StageC &C, int lane)
 {
     using L_ = WLay<N, NC>;
-    double *Pc = sm + L_::oP, *Ex = sm + L_::oEx;
-    const int grp = lane / 6, cb = lane - 6 * grp;
-    // Phi column cb:  (M Phi)[:,cb] = ga M[:,ja] + gb M[:,jb]   and   (Phi' x)[cb] likewise
+    double *Ex = sm + L_::oEx;
+    const int grp = lane < 18 ? lane / 6 : 2, cb = lane % 6;    // lanes >= 18 shadow group 2 and never store
+    const bool act = lane < 18;
+    // Phi column cb:  (M Phi)[:,cb] = ga M[:,ja] + gb M[:,jb]
     const double ga = cb == 0 ? C.F.dc : (cb == 1 ? -C.F.dsn : C.F.dt), gb = cb == 0 ? C.F.dsn : (cb == 1 ? C.F.dc : 0.0);
     const int ja = cb < 2 ? 0 : cb, jb = cb < 2 ? 1 : cb;
-    const double sq1 = P.scale * P.q[cb], sq2 = P.scale * P.q[6 + cb];
+    double sq1 = 0.0, sq2 = 0.0;
+#pragma unroll
+    for (int i = 0; i < 6; i++) if (cb == i) { sq1 = P.scale * P.q[i]; sq2 = P.scale * P.q[6 + i]; }
+    asm volatile("" : "+d"(sq1), "+d"(sq2));                    // keep them in registers (no re-derivation per stage)
+    int o22[6];                                                 // offsets of column cb inside a packed symmetric 6x6
+#pragma unroll
+    for (int i = 0; i < 6; i++) o22[i] = trs(i, cb);
     // P_N = s Q
-    for (int e = lane; e < 93; e += 32) {
-        double v = 0.0;
-        if (e < 36) { if (e / 6 == e % 6) v = P.scale * P.q[e / 6]; }
-        else if (e >= 72) {
-            const int t = e - 72;
-            if (t == 0 || t == 2 || t == 5 || t == 9 || t == 14 || t == 20) {
-                const int d = t == 0 ? 0 : t == 2 ? 1 : t == 5 ? 2 : t == 9 ? 3 : t == 14 ? 4 : 5;
-                v = P.scale * P.q[6 + d];
+    {
+        double *St = sm + L_::oRic + (N - 1) * L_::STG;
+        for (int e = lane; e < 58; e += 32) {
+            double v = 0.0;
+            if (e >= 36) {
+#pragma unroll
+                for (int d = 0; d < 6; d++) if (e - 36 == tri(d, d)) v = P.scale * P.q[6 + d];
             }
+            St[(e < 36 ? L_::sP12 : L_::sP22 - 36) + e] = v;
         }
-        Pc[e] = v;
     }
+    double p11[6];                                              // column cb of P11 (meaningful in group 1)
+#pragma unroll
+    for (int i = 0; i < 6; i++) p11[i] = i == cb ? sq1 : 0.0;
     __syncwarp();
     bool ok = true;
 #pragma unroll 1
     for (int k = N - 1; k >= 0; k--) {
         double *St = sm + L_::oRic + k * L_::STG;
-        for (int e = lane; e < 57; e += 32) St[72 + e] = Pc[36 + e];       // keep P12 | P22 of P_{k+1} for the solves
-        double L1[21], d1[6], Sr[21];
-#pragma unroll
-        for (int e = 0; e < 21; e++) { L1[e] = Pc[72 + e]; Sr[e] = sm[L_::oS + 21 * k + e]; }
-        ok = ldl6(L1, d1) && ok;
-        // K = D^-1 + L' S L
-        double Kr[21];
+        const double *Sk = sm + L_::oS + L_::SST * k;
+        // Pi = P22^-1 in closed form (P22 is well conditioned: adjugate blocks are accurate enough), T = Pi + S_k by
+        // LDL' (T spans the full range of the barrier weights: the closed form stalls the interior point there --
+        // measured at N = 40, nc = 8; tests/test_ipm_model_cpu.py keeps the experiment)
+        double Pi[21], T[21], dT[6];
         {
-            double SL[36];
+            double ld[22];
+            ld22(St + L_::sP22, ld);
 #pragma unroll
-            for (int i = 0; i < 6; i++)
+            for (int e = 0; e < 21; e++) T[e] = ld[e];
+            ok = inv6(T, Pi) && ok;
+            ld22(Sk, ld);
 #pragma unroll
-                for (int b = 0; b < 6; b++) {
-                    double acc = Sr[i >= b ? tri(i, b) : tri(b, i)];
-#pragma unroll
-                    for (int j = b + 1; j < 6; j++) acc = fma(Sr[i >= j ? tri(i, j) : tri(j, i)], L1[tri(j, b)], acc);
-                    SL[6 * i + b] = acc;
-                }
-#pragma unroll
-            for (int a = 0; a < 6; a++)
-#pragma unroll
-                for (int b = 0; b <= a; b++) {
-                    double acc = SL[6 * a + b];
-#pragma unroll
-                    for (int i = a + 1; i < 6; i++) acc = fma(L1[tri(i, a)], SL[6 * i + b], acc);
-                    Kr[tri(a, b)] = acc;
-                }
-#pragma unroll
-            for (int a = 0; a < 6; a++) Kr[tri(a, a)] += d1[a];
+            for (int e = 0; e < 21; e++) T[e] = Pi[e] + ld[e];
         }
-        double d2[6];
-        ok = ldl6(Kr, d2) && ok;
-        // column pipeline: Gamma [ I | P21 | P22 ]  ->  Gamma | A21 | A22     (lane = column, 18 lanes)
+        ok = ldl6(T, dT) && ok;
+        // column pipeline: Gamma [ I | P21 | P22 ] -> Gamma | A21 | A22,  Gamma = T^-1 Pi
         double col[6];
-        if (lane < 18) {
+        {
+            double c[6];
+            if (grp == 1) ld6(St + L_::sP12 + 6 * cb, c);
+            else {
 #pragma unroll
-            for (int i = 0; i < 6; i++)
-                col[i] = grp == 0 ? (i == cb ? 1.0 : 0.0) : (grp == 1 ? Pc[36 + 6 * cb + i] : Pc[72 + trs(i, cb)]);
-            fsub6(L1, col);
+                for (int i = 0; i < 6; i++) c[i] = grp == 0 ? (i == cb ? 1.0 : 0.0) : St[L_::sP22 + o22[i]];
+            }
+            symmv6(Pi, c, col);
+            fsub6(T, col);
 #pragma unroll
-            for (int i = 0; i < 6; i++) col[i] *= d1[i];
-            fsub6(Kr, col);
-#pragma unroll
-            for (int i = 0; i < 6; i++) col[i] *= d2[i];
-            bsub6(Kr, col);
-            lmul6(L1, col);
+            for (int i = 0; i < 6; i++) col[i] *= dT[i];
+            bsub6(T, col);
         }
-        double a11[6];
-        if (lane < 12) {
-            double v[6], wv[6];
+        double wv[6];                                           // P12 S col  (groups 0 and 1)
+        {
+            double v[6], ld[22], row[6];
+            ld22(Sk, ld);
+            symmv6(ld, col, v);
+#pragma unroll
+            for (int i = 0; i < 6; i++) { ld6(St + L_::sP12 + 6 * i, row); wv[i] = dot6(row, v); }
+        }
+        double *Sn = St - L_::STG;                              // slot of stage k-1: receives P12 | P22 of P_k
+        if (grp == 0) {
+            double pw[6];
+            phiT6(C.F, wv, pw);
+#pragma unroll
+            for (int i = 0; i < 6; i++) { St[L_::sPsi + 6 * i + cb] = wv[i]; St[L_::sG2 + 6 * i + cb] = col[i] - pw[i]; St[L_::sGam + 6 * i + cb] = col[i]; }
+        } else if (grp == 1 && k > 0) {
+            // A11[:,cb] = P11[:,cb] - P12 S A21[:,cb];  row cb of the next P12 = A12[cb,:] + (A11 Phi)[cb,:] (A11 symmetric)
+            double a11[6], pa[6];
+#pragma unroll
+            for (int i = 0; i < 6; i++) a11[i] = p11[i] - wv[i];
+            phiT6(C.F, a11, pa);
 #pragma unroll
             for (int i = 0; i < 6; i++) {
-                double acc = 0.0;
-#pragma unroll
-                for (int j = 0; j < 6; j++) acc = fma(Sr[i >= j ? tri(i, j) : tri(j, i)], col[j], acc);
-                v[i] = acc;
+                Ex[6 * i + cb] = col[i];
+                pa[i] += col[i];
+                p11[i] = a11[i] + (i == cb ? sq1 : 0.0);
             }
-#pragma unroll
-            for (int i = 0; i < 6; i++) {
-                double acc = 0.0;
-#pragma unroll
-                for (int j = 0; j < 6; j++) acc = fma(Pc[36 + 6 * i + j], v[j], acc);
-                wv[i] = acc;
-            }
-            if (grp == 0) {
-                double pw[6];
-                phiT6(C.F, wv, pw);
-#pragma unroll
-                for (int i = 0; i < 6; i++) { St[36 + 6 * i + cb] = wv[i]; St[6 * i + cb] = col[i] - pw[i]; St[129 + 6 * i + cb] = col[i]; }
-            } else {
-#pragma unroll
-                for (int i = 0; i < 6; i++) { a11[i] = Pc[6 * i + cb] - wv[i]; Ex[6 * i + cb] = a11[i]; Ex[36 + 6 * i + cb] = col[i]; }
-            }
-        } else if (lane < 18) {
-#pragma unroll
-            for (int i = 0; i < 6; i++) Ex[72 + 6 * i + cb] = col[i];
+            st6(Sn + L_::sP12 + 6 * cb, pa);
         }
         __syncwarp();
         if (k > 0) {
-            // P_k = s Q + Abar' Ptilde Abar
-            if (lane < 18) {
-                double m12[6];
+            // P22 of P_k, column cb = s Q2 + A22 + Phi' M12 + A21 Phi      (group 2)
+            if (act && grp == 2) {
+                double m12[6], pm[6];
 #pragma unroll
-                for (int i = 0; i < 6; i++) m12[i] = Ex[36 + 6 * cb + i] + ga * Ex[6 * i + ja] + gb * Ex[6 * i + jb];
-                if (grp == 0) {
+                for (int i = 0; i < 6; i++) m12[i] = Sn[L_::sP12 + 6 * i + cb];
+                phiT6(C.F, m12, pm);
 #pragma unroll
-                    for (int i = 0; i < 6; i++) Pc[36 + 6 * i + cb] = m12[i];
-                } else if (grp == 1) {
-#pragma unroll
-                    for (int i = 0; i < 6; i++) Pc[6 * i + cb] = a11[i] + (i == cb ? sq1 : 0.0);
-                } else {
-                    double pm[6];
-                    phiT6(C.F, m12, pm);
-#pragma unroll
-                    for (int i = 0; i < 6; i++) {
-                        const double val = col[i] + pm[i] + ga * Ex[36 + 6 * i + ja] + gb * Ex[36 + 6 * i + jb] + (i == cb ? sq2 : 0.0);
-                        if (i >= cb) Pc[72 + tri(i, 0) + cb] = val;
-                    }
+                for (int i = 0; i < 6; i++) {
+                    const double val = col[i] + pm[i] + ga * Ex[6 * i + ja] + gb * Ex[6 * i + jb] + (i == cb ? sq2 : 0.0);
+                    if (i >= cb) Sn[L_::sP22 + o22[i]] = val;
                 }
             }
             __syncwarp();
@@ -397,127 +489,125 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
 
 
 // Solve (M^-1 + S) y = t with the stored stage factors.  In: t in vA.  Out: zeta~ = Bm^T y in vA (what the
-// per-contact step needs: W_c^T y = zeta~_tau x r + zeta~_F).  G2 below denotes the stored Gamma - Phi^T Psi.
+// per-contact step needs: W_c^T y = zeta~_tau x r + zeta~_F).  The two sequential sweeps run on 12 lanes (one state
+// component each) and exchange the 12-vector through shared memory once per stage (42 cycles measured for
+// STS + sync + LDS against 27 for one dependent shuffle, but 8 instructions instead of 16-28 SHFL).
 template <int N, int NC>
 __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int lane)
 {
     using L_ = WLay<N, NC>;
-    double *vA = sm + L_::oVa, *vB = sm + L_::oVb, *vC = sm + L_::oVc;
+    double *vA = sm + L_::oVa, *vB = sm + L_::oVb, *vC = sm + L_::oVc, *vD = sm + L_::oVd, *pbuf = sm + L_::oPb;
     const PhiC F = C.F;
     // ---- pre (lane = stage): gt = Gamma^T t, c1 = P12 gt, c2 = Phi^T c1 + P22 gt
     for (int k = lane; k < N; k += 32) {
         const double *St = sm + L_::oRic + k * L_::STG;
-        double t[6], gt[6], c1[6], c2[6], pc1[6];
+        double t[6], gt[6], c1[6], c2[6], pc1[6], row[6], p22[22];
+        ld6(vA + 6 * k, t);
+        ld6(St + L_::sGam, row);
 #pragma unroll
-        for (int i = 0; i < 6; i++) t[i] = vA[6 * k + i];
+        for (int j = 0; j < 6; j++) gt[j] = row[j] * t[0];
 #pragma unroll
-        for (int j = 0; j < 6; j++) {
-            double acc = 0.0;
+        for (int i = 1; i < 6; i++) {
+            ld6(St + L_::sGam + 6 * i, row);
 #pragma unroll
-            for (int i = 0; i < 6; i++) acc = fma(St[129 + 6 * i + j], t[i], acc);
-            gt[j] = acc;
+            for (int j = 0; j < 6; j++) gt[j] = fma(row[j], t[i], gt[j]);
         }
 #pragma unroll
-        for (int i = 0; i < 6; i++) {
-            double a1 = 0.0, a2 = 0.0;
-#pragma unroll
-            for (int j = 0; j < 6; j++) {
-                a1 = fma(St[72 + 6 * i + j], gt[j], a1);
-                a2 = fma(St[108 + (i >= j ? tri(i, j) : tri(j, i))], gt[j], a2);
-            }
-            c1[i] = a1; c2[i] = a2;
-        }
+        for (int i = 0; i < 6; i++) { ld6(St + L_::sP12 + 6 * i, row); c1[i] = dot6(row, gt); }
+        ld22(St + L_::sP22, p22);
+        symmv6(p22, gt, c2);
         phiT6(F, c1, pc1);
 #pragma unroll
-        for (int i = 0; i < 6; i++) { vA[6 * k + i] = gt[i]; vB[6 * k + i] = c1[i]; vC[6 * k + i] = c2[i] + pc1[i]; }
+        for (int i = 0; i < 6; i++) c2[i] += pc1[i];
+        st6(vA + 6 * k, gt); st6(vB + 6 * k, c1); st6(vC + 6 * k, c2);
     }
+    const int r6 = lane % 6;
+    if (lane < 6) { vD[6 * (N - 1) + r6] = 0.0; pbuf[6 * (N & 1) + r6] = 0.0; }     // zero terminal co-state
     __syncwarp();
-    // ---- backward sweep (lane r < 12 holds p_r):  p1 <- p1 - Psi p2 + c1 ;  p2 <- Phi^T p1 + G2 p2 + c2
-    const int r6 = lane < 6 ? lane : (lane < 12 ? lane - 6 : 0);
     // Phi column r6 (for Phi^T x) and Phi row r6 (for Phi x)
     const double ga = r6 == 0 ? F.dc : (r6 == 1 ? -F.dsn : F.dt), gb = r6 == 0 ? F.dsn : (r6 == 1 ? F.dc : 0.0);
     const double fa = r6 == 0 ? F.dc : (r6 == 1 ? F.dsn : F.dt), fb = r6 == 0 ? -F.dsn : (r6 == 1 ? F.dc : 0.0);
     const int ja = r6 < 2 ? 0 : r6, jb = r6 < 2 ? 1 : r6;
+    // ---- backward sweep (lane r < 6: p1_r, lane 6+r: p2_r; lanes >= 12 shadow lanes 6..11 and never store):
+    //      p1 <- p1 - Psi p2 + c1 ;  p2 <- Phi^T p1 + G2 p2 + c2 ;  vD[k] keeps the p2 that stage k receives
     {
-        double p = 0.0;
+        double pown = 0.0;
 #pragma unroll 2
         for (int k = N - 1; k >= 0; k--) {
             const double *St = sm + L_::oRic + k * L_::STG;
-            const double *row = St + (lane < 6 ? 36 : 0) + 6 * r6;        // Psi row (lanes 0-5) / G2 row (6-11)
-            const double cadd = lane < 6 ? vB[6 * k + r6] : vC[6 * k + r6];
-            double acc0 = 0.0, acc1 = 0.0;
-#pragma unroll
-            for (int j = 0; j < 6; j += 2) {
-                acc0 = fma(row[j], __shfl_sync(kFullMask, p, 6 + j), acc0);
-                acc1 = fma(row[j + 1], __shfl_sync(kFullMask, p, 7 + j), acc1);
-            }
-            const double pa = __shfl_sync(kFullMask, p, ja), pb = __shfl_sync(kFullMask, p, jb);
-            if (lane >= 6 && lane < 12) vC[6 * k + r6] = p;               // p2 of P_{k+1}, for b_k and the output
-            const double acc = acc0 + acc1;
-            p = lane < 6 ? (p - acc + cadd) : (ga * pa + gb * pb + acc + cadd);
+            double row[6], p2[6];
+            ld6(St + (lane < 6 ? L_::sPsi : L_::sG2) + 6 * r6, row);
+            ld6(vD + 6 * k, p2);
+            const double cadd = (lane < 6 ? vB : vC)[6 * k + r6];
+            const double *pp = pbuf + 6 * ((k + 1) & 1);
+            const double pa = pp[ja], pb = pp[jb];
+            const double acc = dot6(row, p2);
+            pown = lane < 6 ? (pown - acc + cadd) : fma(ga, pa, fma(gb, pb, acc + cadd));
+            if (lane < 6) pbuf[6 * (k & 1) + r6] = pown;
+            else if (lane < 12 && k > 0) vD[6 * (k - 1) + r6] = pown;
+            __syncwarp();
         }
     }
-    __syncwarp();
     // ---- b_k = gt_k - S_k Gamma p2   (lane = stage)
     for (int k = lane; k < N; k += 32) {
-        const double *St = sm + L_::oRic + k * L_::STG, *S = sm + L_::oS + 21 * k;
-        double p2[6], g[6];
+        const double *St = sm + L_::oRic + k * L_::STG;
+        double p2[6], g[6], row[6], sk[22], sg[6], b[6];
+        ld6(vD + 6 * k, p2);
 #pragma unroll
-        for (int i = 0; i < 6; i++) p2[i] = vC[6 * k + i];
+        for (int i = 0; i < 6; i++) { ld6(St + L_::sGam + 6 * i, row); g[i] = dot6(row, p2); }
+        ld22(sm + L_::oS + L_::SST * k, sk);
+        symmv6(sk, g, sg);
+        ld6(vA + 6 * k, b);
 #pragma unroll
-        for (int i = 0; i < 6; i++) {
-            double acc = 0.0;
-#pragma unroll
-            for (int j = 0; j < 6; j++) acc = fma(St[129 + 6 * i + j], p2[j], acc);
-            g[i] = acc;
-        }
-#pragma unroll
-        for (int i = 0; i < 6; i++) {
-            double acc = vA[6 * k + i];
-#pragma unroll
-            for (int j = 0; j < 6; j++) acc = fma(-S[i >= j ? tri(i, j) : tri(j, i)], g[j], acc);
-            vA[6 * k + i] = acc;
-        }
+        for (int i = 0; i < 6; i++) b[i] -= sg[i];
+        st6(vA + 6 * k, b);
     }
+    if (lane < 6) vB[r6] = 0.0;                     // y1 after stage 0 (y2 after stage 0 is b_0, already in vA)
     __syncwarp();
-    // ---- forward sweep (lane r < 12 holds y_r):  y1 <- y1 + Phi y2 ;  y2 <- b + G2^T y2 - Psi^T y1
+    // ---- forward sweep:  y1 <- y1 + Phi y2 ;  y2 <- b + G2^T y2 - Psi^T y1   (old values on the right)
     {
-        double y = 0.0;
+        double yown = lane < 6 ? 0.0 : vA[r6];
 #pragma unroll 2
-        for (int k = 0; k < N; k++) {
+        for (int k = 1; k < N; k++) {
             const double *St = sm + L_::oRic + k * L_::STG;
+            double y1[6], y2[6];
+            ld6(vB + 6 * (k - 1), y1); ld6(vA + 6 * (k - 1), y2);
             const double bk = vA[6 * k + r6];
-            double acc0 = 0.0, acc1 = 0.0;
+            double acc0 = bk, acc1 = 0.0;
 #pragma unroll
             for (int i = 0; i < 6; i++) {
-                acc0 = fma(St[6 * i + r6], __shfl_sync(kFullMask, y, 6 + i), acc0);
-                acc1 = fma(-St[36 + 6 * i + r6], __shfl_sync(kFullMask, y, i), acc1);
+                acc0 = fma(St[L_::sG2 + 6 * i + r6], y2[i], acc0);
+                acc1 = fma(St[L_::sPsi + 6 * i + r6], y1[i], acc1);
             }
-            const double ya = __shfl_sync(kFullMask, y, 6 + ja), yb = __shfl_sync(kFullMask, y, 6 + jb);
-            y = lane < 6 ? (y + fa * ya + fb * yb) : (bk + acc0 + acc1);
-            if (lane < 6) vB[6 * k + r6] = y;
-            else if (lane < 12) vA[6 * k + r6] = y;
+            const double ya = vA[6 * (k - 1) + ja], yb = vA[6 * (k - 1) + jb];
+            yown = lane < 6 ? fma(fa, ya, fma(fb, yb, yown)) : (acc0 - acc1);
+            if (lane < 6) vB[6 * k + r6] = yown;
+            else if (lane < 12) vA[6 * k + r6] = yown;
+            __syncwarp();
         }
     }
-    __syncwarp();
     // ---- output (lane = stage): y_k = P12^T y1 + P22 y2 + p2 ; zeta~ = Bm^T y_k
     for (int k = lane; k < N; k += 32) {
         const double *St = sm + L_::oRic + k * L_::STG;
-        double y1[6], y2[6], z[6];
+        double y1[6], y2[6], z[6], row[6], p22[22], q[6];
+        ld6(vB + 6 * k, y1); ld6(vA + 6 * k, y2); ld6(vD + 6 * k, z);
+        ld22(St + L_::sP22, p22);
+        symmv6(p22, y2, q);
 #pragma unroll
-        for (int i = 0; i < 6; i++) { y1[i] = vB[6 * k + i]; y2[i] = vA[6 * k + i]; }
+        for (int i = 0; i < 6; i++) z[i] += q[i];
 #pragma unroll
-        for (int i = 0; i < 6; i++) {
-            double acc = vC[6 * k + i];
+        for (int j = 0; j < 6; j++) {
+            ld6(St + L_::sP12 + 6 * j, row);
 #pragma unroll
-            for (int j = 0; j < 6; j++) acc = fma(St[72 + 6 * j + i], y1[j], fma(St[108 + (i >= j ? tri(i, j) : tri(j, i))], y2[j], acc));
-            z[i] = acc;
+            for (int i = 0; i < 6; i++) z[i] = fma(row[i], y1[j], z[i]);
         }
         const double *J = C.J;
-        vA[6 * k + 0] = J[0] * z[0] + J[3] * z[1] + J[6] * z[2];
-        vA[6 * k + 1] = J[1] * z[0] + J[4] * z[1] + J[7] * z[2];
-        vA[6 * k + 2] = J[2] * z[0] + J[5] * z[1] + J[8] * z[2];
-        vA[6 * k + 3] = C.bv * z[3]; vA[6 * k + 4] = C.bv * z[4]; vA[6 * k + 5] = C.bv * z[5];
+        double o[6];
+        o[0] = J[0] * z[0] + J[3] * z[1] + J[6] * z[2];
+        o[1] = J[1] * z[0] + J[4] * z[1] + J[7] * z[2];
+        o[2] = J[2] * z[0] + J[5] * z[1] + J[8] * z[2];
+        o[3] = C.bv * z[3]; o[4] = C.bv * z[4]; o[5] = C.bv * z[5];
+        st6(vA + 6 * k, o);
     }
     __syncwarp();
 }
@@ -605,7 +695,7 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
 {
     using L_ = WLay<N, NC>;
     constexpr int NU = 3 * NC, NV = NU * N, NCN = NC * N;
-    extern __shared__ double sm_all[];
+    extern __shared__ __align__(16) double sm_all[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     double *sm = sm_all + (size_t)warp * L_::oEnd;
     const long long b = (long long)blockIdx.x * (blockDim.x >> 5) + warp;
@@ -734,16 +824,16 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
             double *Ds = Dst + 9 * c;
 #pragma unroll
             for (int j = 0; j < 6; j++) {
-                const double si = 1.0 / s6[j];
+                const double si = frcp(s6[j]);
                 p_gap += s6[j] * l6[j];
                 D[j] = l6[j] * si;
                 Ds[j] = si;
             }
             // Dblk = sr I + Cb' D Cb = [[a,0,e],[0,b,f],[e,f,cc]] ; LDL' with a cancellation-free Schur term
-            const double ia = 1.0 / (sr + D[0] + D[1]), ib = 1.0 / (sr + D[2] + D[3]);
+            const double ia = frcp(sr + D[0] + D[1]), ib = frcp(sr + D[2] + D[3]);
             const double d2 = sr + D[4] + D[5] + mu * mu * ((sr * (D[0] + D[1]) + 4.0 * D[0] * D[1]) * ia +
                                                             (sr * (D[2] + D[3]) + 4.0 * D[2] * D[3]) * ib);
-            const double id2 = 1.0 / d2;
+            const double id2 = frcp(d2);
             Ds[6] = ia; Ds[7] = ib; Ds[8] = id2;
             double Di[6];
             contact_dinv(D[0], D[1], D[2], D[3], ia, ib, id2, mu, Di);
@@ -784,10 +874,10 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
                 p_sum += dsi * dli;
             }
         }
-        const double a_aff = fmin(1.0, 1.0 / wmax(p_rmax));
+        const double a_aff = fmin(1.0, frcp(wmax(p_rmax)));
         // sum (s + a ds)(lam + a dl) = (1 - a) s'lam + a^2 ds'dl for the affine direction
         const double g_aff = ((1.0 - a_aff) * gap * m_ineq + a_aff * a_aff * wsum(p_sum)) / m_ineq;
-        double sig = g_aff / gap;
+        double sig = g_aff * frcp(gap);
         sig = sig * sig * sig;
         const double sigma_gap = sig * gap;
         // (5) corrector right-hand side: t = Dblk^-1 (-grad f + Cb'q),  q = (ds dl - sigma mu)/s
@@ -831,12 +921,12 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
             for (int j = 0; j < 6; j++) {
                 const double dsi = -(X[3 * j] * rt[0] + X[3 * j + 1] * rt[1] + X[3 * j + 2] * rt[2]);
                 const double x = dsi * Ds[j];
-                const double rl = 1.0 + x + q6[j] / l6[j];
+                const double rl = 1.0 + x + q6[j] * frcp(l6[j]);
                 p_rmax = fmax(p_rmax, fmax(-x, rl));
                 dsv[6 * c + j] = dsi; dlv[6 * c + j] = -l6[j] * rl;
             }
         }
-        const double alpha = fmin(1.0, 0.995 / wmax(p_rmax));
+        const double alpha = fmin(1.0, 0.995 * frcp(wmax(p_rmax)));
         // (7) step (same lane -> same contacts as in (6): no barrier needed)
         for (int i = lane; i < n_stance; i += 32) {
             const int c = stIdx[i];
@@ -860,6 +950,20 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
     // here w = W u, X = state response, gf = grad f(u) are consistent with the returned u
     bad_bounds = __any_sync(kFullMask, bad_bounds);
     if (bad_bounds && status == G1MPC_SOLVED) status = G1MPC_BAD_BOUNDS;
+    // The slacks are carried by the iteration (ds = -Cb du), not recomputed from u, so after ~25 iterations u can sit
+    // ~1e-9 N outside an active row (measured at N = 40, nc = 8).  Clamp the returned point back into the pyramid:
+    // the change is six orders below the 1e-3 N parity tolerance and makes primal feasibility exact.
+    if (status != G1MPC_NUMERICAL) {
+        for (int i = lane; i < n_stance; i += 32) {
+            const int c = stIdx[i];
+            const double cf = cfl[c], lo = P.fz_min * cf, hi = P.fz_max * cf;
+            const double fz = fmin(fmax(u[3 * c + 2], lo), hi), lim = mu * fz;
+            u[3 * c] = fmin(fmax(u[3 * c], -lim), lim);
+            u[3 * c + 1] = fmin(fmax(u[3 * c + 1], -lim), lim);
+            u[3 * c + 2] = fz;
+        }
+        __syncwarp();
+    }
     double *gu = io.u_opt + b * NV;
     for (int i = lane; i < NV; i += 32) gu[i] = u[i];
     if (io.status && lane == 0) io.status[b] = status;

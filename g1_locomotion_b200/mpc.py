@@ -126,6 +126,39 @@ class BatchedMPC:
         _lib.check(rc, "g1mpc_emit_qp_batch")
         return out
 
+    # -- the callers either side of the path ---------------------------------
+    def walk_inputs(self, x0, contacts_now, sim_time, x_opt_prev, x_ref=None, want_landing=False):
+        """What the demo node builds before updateMPC (mpc_to_wbid_node.cpp:385-470) for a batch of CUDA tensors.
+        x_ref is in/out (None = zeros, as after initMatrices).  Returns x_ref, contact, c_horizon, p_com[, landing]."""
+        B, N = x0.shape[0], self.N
+        px0 = self._chk(x0, (B, NS), "x0"); pc = self._chk(contacts_now, (B, 12), "contacts_now")
+        pt = self._chk(sim_time, (B,), "sim_time"); pxo = self._chk(x_opt_prev, (B, N, NS), "x_opt_prev")
+        if x_ref is None:
+            x_ref = torch.zeros(B, N, NS, device=self.device, dtype=torch.float64)
+        pxr = self._chk(x_ref, (B, N, NS), "x_ref")
+        mk = lambda *s: torch.empty(*s, device=self.device, dtype=torch.float64)
+        contact, c_hor, p_com = mk(B, N, 4), mk(B, N, 12), mk(B, N, 3)
+        landing = mk(B, 2) if want_landing else None
+        stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        with torch.cuda.device(self.device):
+            rc = self._lib.g1mpc_walk_inputs_batch(self._h, B, px0, pc, pt, pxo, pxr, C.c_void_p(contact.data_ptr()),
+                                                   C.c_void_p(c_hor.data_ptr()), C.c_void_p(p_com.data_ptr()),
+                                                   C.c_void_p(landing.data_ptr()) if want_landing else None, stream)
+        _lib.check(rc, "g1mpc_walk_inputs_batch")
+        return (x_ref, contact, c_hor, p_com, landing) if want_landing else (x_ref, contact, c_hor, p_com)
+
+    def wbid_refs(self, u_opt, x_opt, foot_positions, wbid_mass):
+        """WBID.setReference's derived references (wbid.py:244-297) for a batch -> [B,42] (layout: g1mpc_b200.h)."""
+        B, N = u_opt.shape[0], self.N
+        pu = self._chk(u_opt, (B, N, self.nu), "u_opt"); px = self._chk(x_opt, (B, N, NS), "x_opt")
+        pf = self._chk(foot_positions, (B, 4, 3), "foot_positions")
+        refs = torch.empty(B, 42, device=self.device, dtype=torch.float64)
+        stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        with torch.cuda.device(self.device):
+            rc = self._lib.g1mpc_wbid_refs_batch(self._h, B, pu, px, pf, float(wbid_mass), C.c_void_p(refs.data_ptr()), stream)
+        _lib.check(rc, "g1mpc_wbid_refs_batch")
+        return refs
+
     # -- host API (the reference-facing call: numpy in, numpy out, copies inside) -----------------
     def update_host(self, x0, x_ref, contact, c_horizon, p_com, x_current=None, one_rollout=False, x_opt=None):
         f = lambda a, shape: np.ascontiguousarray(np.asarray(a, dtype=np.float64).reshape(shape))

@@ -31,7 +31,7 @@ extern "C" {
 #endif
 
 #define G1MPC_NUM_STATES 13
-#define G1MPC_ABI_VERSION 1
+#define G1MPC_ABI_VERSION 2
 
 typedef enum g1mpc_error {
     G1MPC_OK = 0,
@@ -106,6 +106,33 @@ int g1mpc_update_host(g1mpc_handle *h, int64_t B, const double *x0, const double
                       const double *contact, const double *c_horizon, const double *p_com,
                       const double *x_current, int one_rollout, double *u_opt, double *x_opt,
                       int32_t *status, int32_t *iters, double *resid);
+
+/*
+ * SURVEY 8f-1 -- what the demo node builds before every updateMPC call, for a batch (device pointers):
+ * MPCNode::update's reference trajectory (g1_mpc/src/mpc_to_wbid_node.cpp:403-435) and p_com extraction (:461-468),
+ * callbackSrbdCurrent's tiling of the current contact points over the horizon (:50-60), and gaitPlanner (:71-320):
+ * table window by gait_phase = floor(sim_time/dt) (:82-127,171-187) plus the Raibert footstep overwrite of the
+ * swing-foot rows (:205-309, RaibertHeuristic :507-524) read from the previous solve's x_opt.
+ *   x0 [B,13], contacts_now [B,12] (4 points x xyz), sim_time [B], x_opt_prev [B,N,13]  ->
+ *   x_ref [B,N,13] IN/OUT (the node only writes columns 2,3,4,5,8,9,12; the rest keeps the caller's values),
+ *   contact [B,N,4], c_horizon [B,N,12], p_com [B,N,3], landing [B,2] or NULL (landing_position x,y as published, :257-270).
+ * Needs num_contacts == 4 and horizon <= 10 (the node's table has 20 rows).
+ */
+int g1mpc_walk_inputs_batch(g1mpc_handle *h, int64_t B, const double *x0, const double *contacts_now,
+                            const double *sim_time, const double *x_opt_prev, double *x_ref, double *contact,
+                            double *c_horizon, double *p_com, double *landing, void *stream);
+
+/*
+ * SURVEY 8f-2 -- what the WBID layer derives from one solve, WBID.setReference(t, x_opt[1], u_opt0, feet)
+ * (g1_mujoco_sim/src/wbid.py:231-297, call site ros_run_simulation.py:409), for a batch (device pointers):
+ *   refs [B,42] = R(9, euler_matrix of x_opt[1][0:3]) | base velocity (v, omega) | base acceleration reference
+ *   (0,0,0, I_torso^-1 sum r_i x omega) | CoM position, velocity, acceleration reference (sum_forces/mass + g, with
+ *   sum_forces = rows of reshape(u_opt0,(3,4)) exactly as coded, wbid.py:290) | wrench-task references (u_opt0).
+ *   foot_positions [B,4,3]; wbid_mass = model.getMass() of the whole-body model.
+ */
+#define G1MPC_WBID_REFS 42
+int g1mpc_wbid_refs_batch(g1mpc_handle *h, int64_t B, const double *u_opt, const double *x_opt,
+                          const double *foot_positions, double wbid_mass, double *refs, void *stream);
 
 /* Dynamic shared memory (bytes) and threads per CTA of the solve kernel for this handle's shape. */
 int g1mpc_kernel_info(const g1mpc_handle *h, int32_t *smem_bytes, int32_t *threads, int32_t *ctas_per_sm);
