@@ -106,6 +106,13 @@ class ClockSampler:
                 "samples": len(self.samples)}
 
 
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def cpu_reference_pass(preset, batch, nthreads):
     """One pass of the CPU restatement over `batch` -> seconds."""
     from oracle import oracle
@@ -124,7 +131,7 @@ def run_reference(args, rank, world):
     preset = presets.get_preset("cpp_node")
     sample_B = 256
     batch = [a[:sample_B] for a in inputs.walking_batch(preset, sample_B)]
-    cores = oracle.num_threads()
+    cores = host_threads()         # torchrun exports OMP_NUM_THREADS=1: the reference arm uses every host thread anyway
     for _ in range(max(args.warmup, 1)):
         cpu_reference_pass(preset, batch, cores)
     times = [cpu_reference_pass(preset, batch, cores) for _ in range(args.steps)]
@@ -311,7 +318,7 @@ def extras(solver, preset, dev):
 def cpu_baseline(preset, host_batch):
     from oracle import oracle
     oracle.build_lib()
-    cores = oracle.num_threads()
+    cores = host_threads()
     sample = [a[:256] for a in host_batch]
     cpu_reference_pass(preset, [a[:32] for a in host_batch], cores)
     t1 = cpu_reference_pass(preset, [a[:32] for a in host_batch], 1) / 32

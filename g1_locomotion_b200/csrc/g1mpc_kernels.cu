@@ -313,8 +313,9 @@ struct g1mpc_handle {
     const KernelEntry *kernel;
     int warps_per_block = 1;
     int ctas_per_sm = 0;
-    // host-API staging
-    cudaStream_t stream = nullptr;
+    // host-API staging: kPipe chunk streams
+    static constexpr int kPipe = 4;
+    cudaStream_t pipe[kPipe] = {nullptr, nullptr, nullptr, nullptr};
     char *h_stage = nullptr, *d_stage = nullptr;
     size_t stage_bytes = 0;
 };
@@ -366,8 +367,10 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
     if (e != cudaSuccess) { g_last_error = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
     cudaFuncSetAttribute((const void *)srbd_mpc_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->ctas_per_sm, (const void *)ke->fn, kWarpThreads * h->warps_per_block, ke->smem * h->warps_per_block);
-    e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
-    if (e != cudaSuccess) { g_last_error = "cudaStreamCreate failed"; g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
+    for (int i = 0; i < g1mpc_handle::kPipe; i++) {
+        e = cudaStreamCreateWithFlags(&h->pipe[i], cudaStreamNonBlocking);
+        if (e != cudaSuccess) { g_last_error = "cudaStreamCreate failed"; g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
+    }
     *out = h;
     return G1MPC_OK;
 }
@@ -378,7 +381,7 @@ void g1mpc_destroy(g1mpc_handle *h)
     cudaSetDevice(h->device);
     if (h->h_stage) cudaFreeHost(h->h_stage);
     if (h->d_stage) cudaFree(h->d_stage);
-    if (h->stream) cudaStreamDestroy(h->stream);
+    for (int i = 0; i < g1mpc_handle::kPipe; i++) if (h->pipe[i]) cudaStreamDestroy(h->pipe[i]);
     delete h;
 }
 
@@ -438,12 +441,17 @@ int g1mpc_update_host(g1mpc_handle *h, int64_t B, const double *x0, const double
     if (B == 0) return G1MPC_OK;
     CUDA_TRY(cudaSetDevice(h->device));
     const size_t N = h->params.horizon, NC = h->params.num_contacts, NU = 3 * NC;
-    // packed input block | packed output block
-    const size_t n_x0 = B * NS, n_xr = B * N * NS, n_ct = B * N * NC, n_ch = B * N * NU, n_pc = B * N * 3, n_xc = B * NS;
-    const size_t n_u = B * N * NU, n_xo = B * N * NS, n_res = B * 4;
-    const size_t in_d = n_x0 + n_xr + n_ct + n_ch + n_pc + n_xc + n_xo;   // x_opt travels in: it is in/out
-    const size_t out_d = n_u + n_xo + n_res;
-    const size_t bytes = sizeof(double) * (in_d + out_d) + sizeof(int32_t) * 2 * B + 64;
+    // The batch is cut into up to kPipe chunks, each with its own stream: pack chunk c+1 into pinned memory while chunk
+    // c is copied and solved, unpack chunk c while later chunks are still in flight.  One H2D and one D2H per chunk:
+    //   chunk block = x0 | x_ref | contact | c_horizon | p_com | x_current | x_opt (in/out) | u_opt | resid | status | iters
+    // x_opt only travels host->device when the reference would leave some of its rows untouched (no x_current: row 0;
+    // one_rollout: rows 2..; mpc.cpp:427-446).
+    const bool xopt_in = (x_current == nullptr) || one_rollout;
+    const int nchunk = B >= 512 ? g1mpc_handle::kPipe : (B >= 128 ? 2 : 1);
+    const size_t cap = ((size_t)B + nchunk - 1) / nchunk;
+    const size_t d_in = NS + N * NS + N * NC + N * NU + N * 3 + NS, d_xo = N * NS, d_out = N * NU + 4;   // doubles per problem
+    const size_t stride = ((sizeof(double) * (d_in + d_xo + d_out) + 2 * sizeof(int32_t)) * cap + 255) & ~(size_t)255;
+    const size_t bytes = stride * nchunk;
     if (bytes > h->stage_bytes) {
         if (h->h_stage) cudaFreeHost(h->h_stage);
         if (h->d_stage) cudaFree(h->d_stage);
@@ -452,33 +460,48 @@ int g1mpc_update_host(g1mpc_handle *h, int64_t B, const double *x0, const double
         CUDA_TRY(cudaMalloc((void **)&h->d_stage, bytes));
         h->stage_bytes = bytes;
     }
-    double *hs = (double *)h->h_stage, *dsg = (double *)h->d_stage;
-    size_t o = 0;
-    const size_t o_x0 = o; memcpy(hs + o, x0, sizeof(double) * n_x0); o += n_x0;
-    const size_t o_xr = o; memcpy(hs + o, x_ref, sizeof(double) * n_xr); o += n_xr;
-    const size_t o_ct = o; memcpy(hs + o, contact, sizeof(double) * n_ct); o += n_ct;
-    const size_t o_ch = o; memcpy(hs + o, c_horizon, sizeof(double) * n_ch); o += n_ch;
-    const size_t o_pc = o; memcpy(hs + o, p_com, sizeof(double) * n_pc); o += n_pc;
-    const size_t o_xc = o; if (x_current) memcpy(hs + o, x_current, sizeof(double) * n_xc); o += n_xc;
-    // outputs: u | x_opt | resid | status | iters   (x_opt first so the in/out copy is part of the H2D block)
-    const size_t o_xo = o; memcpy(hs + o, x_opt, sizeof(double) * n_xo); o += n_xo;
-    const size_t h2d_d = o;
-    const size_t o_u = o; o += n_u;
-    const size_t o_res = o; o += n_res;
-    int32_t *hs_i = (int32_t *)(hs + o), *ds_i = (int32_t *)(dsg + o);
-    CUDA_TRY(cudaMemcpyAsync(dsg, hs, sizeof(double) * h2d_d, cudaMemcpyHostToDevice, h->stream));
-    int rc = g1mpc_solve_batch(h, B, dsg + o_x0, dsg + o_xr, dsg + o_ct, dsg + o_ch, dsg + o_pc,
-                               x_current ? dsg + o_xc : nullptr, one_rollout, dsg + o_u, dsg + o_xo, ds_i, ds_i + B,
-                               dsg + o_res, nullptr, h->stream);
-    if (rc) return rc;
-    CUDA_TRY(cudaMemcpyAsync(hs + o_xo, dsg + o_xo, sizeof(double) * (n_xo + n_u + n_res) + sizeof(int32_t) * 2 * B,
-                             cudaMemcpyDeviceToHost, h->stream));
-    CUDA_TRY(cudaStreamSynchronize(h->stream));
-    memcpy(u_opt, hs + o_u, sizeof(double) * n_u);
-    memcpy(x_opt, hs + o_xo, sizeof(double) * n_xo);
-    if (resid) memcpy(resid, hs + o_res, sizeof(double) * n_res);
-    if (status) memcpy(status, hs_i, sizeof(int32_t) * B);
-    if (iters) memcpy(iters, hs_i + B, sizeof(int32_t) * B);
+    struct Off { size_t x0, xr, ct, ch, pc, xc, xo, u, res, st; } o[g1mpc_handle::kPipe];
+    size_t nbs[g1mpc_handle::kPipe];
+    for (int c = 0; c < nchunk; c++) {
+        const size_t b0 = cap * c, nb = b0 < (size_t)B ? (((size_t)B - b0) < cap ? ((size_t)B - b0) : cap) : 0;
+        nbs[c] = nb;
+        if (nb == 0) continue;
+        double *hs = (double *)(h->h_stage + stride * c), *ds = (double *)(h->d_stage + stride * c);
+        Off &f = o[c];
+        size_t q = 0;
+        f.x0 = q; memcpy(hs + q, x0 + b0 * NS, sizeof(double) * nb * NS); q += nb * NS;
+        f.xr = q; memcpy(hs + q, x_ref + b0 * N * NS, sizeof(double) * nb * N * NS); q += nb * N * NS;
+        f.ct = q; memcpy(hs + q, contact + b0 * N * NC, sizeof(double) * nb * N * NC); q += nb * N * NC;
+        f.ch = q; memcpy(hs + q, c_horizon + b0 * N * NU, sizeof(double) * nb * N * NU); q += nb * N * NU;
+        f.pc = q; memcpy(hs + q, p_com + b0 * N * 3, sizeof(double) * nb * N * 3); q += nb * N * 3;
+        f.xc = q; if (x_current) memcpy(hs + q, x_current + b0 * NS, sizeof(double) * nb * NS); q += nb * NS;
+        f.xo = q; if (xopt_in) memcpy(hs + q, x_opt + b0 * N * NS, sizeof(double) * nb * N * NS); q += nb * N * NS;
+        f.u = q; q += nb * N * NU;
+        f.res = q; q += nb * 4;
+        f.st = q;                                              // int32 status[nb] | iters[nb]
+        cudaStream_t sp = h->pipe[c];
+        CUDA_TRY(cudaMemcpyAsync(ds, hs, sizeof(double) * (xopt_in ? f.u : f.xo), cudaMemcpyHostToDevice, sp));
+        int32_t *ds_i = (int32_t *)(ds + f.st);
+        int rc = g1mpc_solve_batch(h, (int64_t)nb, ds + f.x0, ds + f.xr, ds + f.ct, ds + f.ch, ds + f.pc,
+                                   x_current ? ds + f.xc : nullptr, one_rollout, ds + f.u, ds + f.xo, ds_i, ds_i + nb,
+                                   ds + f.res, nullptr, sp);
+        if (rc) return rc;
+        CUDA_TRY(cudaMemcpyAsync(hs + f.xo, ds + f.xo, sizeof(double) * (f.st - f.xo) + sizeof(int32_t) * 2 * nb,
+                                 cudaMemcpyDeviceToHost, sp));
+    }
+    for (int c = 0; c < nchunk; c++) {
+        const size_t b0 = cap * c, nb = nbs[c];
+        if (nb == 0) continue;
+        CUDA_TRY(cudaStreamSynchronize(h->pipe[c]));
+        const double *hs = (const double *)(h->h_stage + stride * c);
+        const Off &f = o[c];
+        memcpy(u_opt + b0 * N * NU, hs + f.u, sizeof(double) * nb * N * NU);
+        memcpy(x_opt + b0 * N * NS, hs + f.xo, sizeof(double) * nb * N * NS);
+        if (resid) memcpy(resid + b0 * 4, hs + f.res, sizeof(double) * nb * 4);
+        const int32_t *hs_i = (const int32_t *)(hs + f.st);
+        if (status) memcpy(status + b0, hs_i, sizeof(int32_t) * nb);
+        if (iters) memcpy(iters + b0, hs_i + nb, sizeof(int32_t) * nb);
+    }
     return G1MPC_OK;
 }
 

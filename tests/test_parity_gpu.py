@@ -238,3 +238,24 @@ def test_full_size_properties_65536():
     assert float(res[:, 0].max()) <= 1e-10 and float(res[:, 2].max()) <= 1e-9
     assert torch.equal(x[:, 0], ins[0])
     print("iters: mean %.2f max %d" % (float(info["iters"].double().mean()), int(info["iters"].max())))
+
+
+@pytest.mark.parametrize("B,use_xc,one", [(600, True, False), (130, False, False), (515, True, True)])
+def test_host_api_chunk_pipeline_equals_device_api(B, use_xc, one):
+    """g1mpc_update_host cuts large batches into chunks on separate streams (ragged last chunk included); results and
+    the in/out semantics of x_opt must be those of the one-launch device call."""
+    preset = presets.get_preset("cpp_node")
+    batch = [t.numpy() for t in inputs.random_batch(preset, B, seed=21)]
+    s = _solver(preset)
+    ins = _dev(batch)
+    x_prev = np.random.default_rng(0).normal(size=(B, 10, 13))
+    xd = torch.as_tensor(x_prev).cuda()
+    u, x, info = s.update_batch(*ins, x_current=ins[0] if use_xc else None, one_rollout=one, x_opt=xd)
+    uh, xh, infoh = s.update_host(*batch, x_current=batch[0] if use_xc else None, one_rollout=one, x_opt=x_prev)
+    assert np.array_equal(uh, u.cpu().numpy()) and np.array_equal(xh, x.cpu().numpy())
+    assert np.array_equal(infoh["status"], info["status"].cpu().numpy()) and np.array_equal(infoh["iters"], info["iters"].cpu().numpy())
+    assert np.array_equal(infoh["resid"], info["resid"].cpu().numpy())
+    if not use_xc:
+        assert np.array_equal(xh[:, 0], x_prev[:, 0])
+    if one:
+        assert np.array_equal(xh[:, 2:], x_prev[:, 2:])
