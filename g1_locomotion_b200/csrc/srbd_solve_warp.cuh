@@ -926,7 +926,10 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
                 dsv[6 * c + j] = dsi; dlv[6 * c + j] = -l6[j] * rl;
             }
         }
-        const double alpha = fmin(1.0, 0.995 * frcp(wmax(p_rmax)));
+        // fraction to the boundary: 0.995 while the predictor is blocked, -> 1 quadratically once it is not (a_aff -> 1),
+        // so that the last iterations are not held at a factor 200 per step (one iteration fewer on every preset)
+        const double eta = fmin(0.99999, fmax(0.995, 1.0 - (1.0 - a_aff) * (1.0 - a_aff)));
+        const double alpha = fmin(1.0, eta * frcp(wmax(p_rmax)));
         // (7) step (same lane -> same contacts as in (6): no barrier needed)
         for (int i = lane; i < n_stance; i += 32) {
             const int c = stIdx[i];

@@ -251,7 +251,7 @@ def solve_ipm(prob, gap_tol=1e-10, max_iter=40, linear="riccati"):
                 g_aff = float(((s[st] + a_aff * ds[st]) * (lam[st] + a_aff * dl[st])).sum() / m_ineq)
                 sigma_gap = (g_aff / gap) ** 3 * gap
             else:
-                alpha = min(1.0, 0.995 * amin)
+                alpha = min(1.0, min(0.99999, max(0.995, 1.0 - (1.0 - a_aff) ** 2)) * amin)
         u[st] += alpha * du[st]; lam[st] += alpha * dl[st]; s[st] += alpha * ds[st]
         it += 1
 
