@@ -31,8 +31,8 @@ METRIC = "batched MPC build+solve/sec (N=10, whole box, device-timed)"
 UNIT = "problems/s"
 BATCH = 1024
 # dram__bytes_read.sum + dram__bytes_write.sum of one solve launch at B=1024 from the committed `ncu --set full`
-# capture (profiles/r1_v2_ncu_full_summary.csv): inputs are read once, the 2 MB of outputs stay in L2.
-NCU_TRAFFIC_BYTES = 2860032
+# capture (profiles/r1_v4_ncu_full_summary.csv): inputs are read once, the 2 MB of outputs stay in L2.
+NCU_TRAFFIC_BYTES = 2827264
 WORKLOAD = "configs[1]: 1,024 independent G1 SRBD MPC problems per GPU (cpp_node preset, N=10, nc=4, walking gait schedule)"
 
 
@@ -40,7 +40,7 @@ def algorithmic_flops(N, nc, iters_mean, stance_mean):
     """USEFUL FP64 flops (FMA = 2) of the stage-wise interior point per problem -- each quantity counted once,
     not once per lane that recomputes it; term by term in DESIGN.md section 5.
     stance_mean = mean number of stance contacts per problem (swing contacts are eliminated)."""
-    per_stage_factor = 2 * 146 + 250 + 18 * 150 + 12 * 144 + 300      # 2 LDL' 6x6, L'SL, 18-column pipeline, S./P12. products, P update
+    per_stage_factor = 320 + 170 + 42 + 18 * 140 + 12 * 144 + 300     # closed-form P22^-1, LDL' of Pi+S, 18-column pipeline, S./P12. products, P update
     per_stage_solve = 330 + 290 + 190 + 130                            # pre, two sweeps, b_k, multiplier output (per solve)
     per_stage_grad = 100 + 9 * nc                                      # wrench, rollout, adjoint
     per_contact = 120 + 90 + 100 + 60 + 130 + 30                       # gradient/D-state, S_k share, predictor, corrector rhs, step, update
