@@ -11,7 +11,7 @@ LIB_PATH = os.environ.get("G1MPC_B200_LIB") or os.path.join(_HERE, "libg1mpc_b20
 _lib = None
 
 EXPORTS = ["g1mpc_create", "g1mpc_destroy", "g1mpc_solve_batch", "g1mpc_emit_qp_batch", "g1mpc_update_host",
-           "g1mpc_walk_inputs_batch", "g1mpc_wbid_refs_batch", "g1mpc_kernel_info", "g1mpc_fp64_peak_tflops", "g1mpc_last_error", "g1mpc_abi_version"]
+           "g1mpc_walk_inputs_batch", "g1mpc_wbid_refs_batch", "g1mpc_closed_loop_batch", "g1mpc_kernel_info", "g1mpc_fp64_peak_tflops", "g1mpc_last_error", "g1mpc_abi_version"]
 
 
 class G1mpcParams(C.Structure):
@@ -58,6 +58,8 @@ def load():
     lib.g1mpc_walk_inputs_batch.restype = C.c_int
     lib.g1mpc_wbid_refs_batch.argtypes = [vp, i64, dp, dp, dp, C.c_double, dp, vp]
     lib.g1mpc_wbid_refs_batch.restype = C.c_int
+    lib.g1mpc_closed_loop_batch.argtypes = [vp, i64, C.c_int32] + [dp] * 8 + [i32p, vp]
+    lib.g1mpc_closed_loop_batch.restype = C.c_int
     lib.g1mpc_kernel_info.argtypes = [vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     lib.g1mpc_kernel_info.restype = C.c_int
     lib.g1mpc_fp64_peak_tflops.argtypes = [C.c_int, C.POINTER(C.c_double)]

@@ -318,6 +318,9 @@ struct g1mpc_handle {
     cudaStream_t pipe[kPipe] = {nullptr, nullptr, nullptr, nullptr};
     char *h_stage = nullptr, *d_stage = nullptr;
     size_t stage_bytes = 0;
+    // closed-loop workspace
+    char *d_loop = nullptr;
+    size_t loop_bytes = 0;
 };
 
 extern "C" {
@@ -381,6 +384,7 @@ void g1mpc_destroy(g1mpc_handle *h)
     cudaSetDevice(h->device);
     if (h->h_stage) cudaFreeHost(h->h_stage);
     if (h->d_stage) cudaFree(h->d_stage);
+    if (h->d_loop) cudaFree(h->d_loop);
     for (int i = 0; i < g1mpc_handle::kPipe; i++) if (h->pipe[i]) cudaStreamDestroy(h->pipe[i]);
     delete h;
 }
@@ -540,6 +544,43 @@ int g1mpc_wbid_refs_batch(g1mpc_handle *h, int64_t B, const double *u_opt, const
     adaptors::wbid_refs_kernel<<<(unsigned)((B + 127) / 128), 128, 0, (cudaStream_t)stream>>>(u_opt, x_opt, foot_positions, refs, (long long)B,
                                                                                               h->params.horizon, wbid_mass);
     CUDA_TRY(cudaGetLastError());
+    return G1MPC_OK;
+}
+
+int g1mpc_closed_loop_batch(g1mpc_handle *h, int64_t B, int32_t ticks, double *x0, double *contacts_now, double *sim_time,
+                            double *x_ref, double *x_opt, double *u_opt, double *traj_x, double *traj_u, int32_t *status_any,
+                            void *stream)
+{
+    if (!h || B < 0 || ticks < 0 || (B > 0 && (!x0 || !contacts_now || !sim_time || !x_ref || !x_opt || !u_opt))) {
+        g_last_error = "g1mpc_closed_loop_batch: bad argument"; return G1MPC_ERR_INVALID_ARGUMENT;
+    }
+    if (h->params.num_contacts != 4 || h->params.horizon > 10) {
+        g_last_error = "g1mpc_closed_loop_batch: the node's gait table needs num_contacts == 4 and horizon <= 10";
+        return G1MPC_ERR_UNSUPPORTED_SHAPE;
+    }
+    if (B == 0 || ticks == 0) return G1MPC_OK;
+    CUDA_TRY(cudaSetDevice(h->device));
+    const size_t N = h->params.horizon;
+    // workspace: contact [B,N,4] | c_horizon [B,N,12] | p_com [B,N,3] | status [B] int32 | iters [B] int32
+    const size_t need = sizeof(double) * (size_t)B * N * 19 + sizeof(int32_t) * 2 * (size_t)B;
+    if (need > h->loop_bytes) {
+        CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+        if (h->d_loop) cudaFree(h->d_loop);
+        h->d_loop = nullptr; h->loop_bytes = 0;
+        CUDA_TRY(cudaMalloc((void **)&h->d_loop, need));
+        h->loop_bytes = need;
+    }
+    double *contact = (double *)h->d_loop, *c_hor = contact + (size_t)B * N * 4, *p_com = c_hor + (size_t)B * N * 12;
+    int32_t *status = (int32_t *)(p_com + (size_t)B * N * 3), *iters = status + B;
+    for (int t = 0; t < ticks; t++) {
+        int rc = g1mpc_walk_inputs_batch(h, B, x0, contacts_now, sim_time, x_opt, x_ref, contact, c_hor, p_com, nullptr, stream);
+        if (rc) return rc;
+        rc = g1mpc_solve_batch(h, B, x0, x_ref, contact, c_hor, p_com, x0, 0, u_opt, x_opt, status, iters, nullptr, nullptr, stream);
+        if (rc) return rc;
+        adaptors::advance_kernel<<<(unsigned)((B + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+            x0, contacts_now, sim_time, x_opt, u_opt, c_hor, status, traj_x, traj_u, status_any, (long long)B, (int)N, t, ticks, h->params.dt);
+        CUDA_TRY(cudaGetLastError());
+    }
     return G1MPC_OK;
 }
 

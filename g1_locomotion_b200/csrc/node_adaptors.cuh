@@ -151,4 +151,25 @@ __global__ void __launch_bounds__(128) wbid_refs_kernel(const double *u_opt, con
     for (int i = 0; i < 12; i++) o[30 + i] = u0[i];
 }
 
+// Closed loop of many walkers: the SRBD model itself is the plant.  After a solve, record the tick, then
+//   x0 <- x_opt[1] (the first rollout step, mpc.cpp:436-441 = A x0 + B_0 u_0), contact points <- row 1 of the planner's
+//   c_horizon (stance feet stay, a foot due to land sits at its Raibert point), sim_time += dt.
+// The previous x_opt stays where it is: the next walk_inputs call reads it for the Raibert rule (:238-243).
+__global__ void __launch_bounds__(128) advance_kernel(double *x0, double *contacts_now, double *sim_time, const double *x_opt,
+                                                       const double *u_opt, const double *c_hor, const int32_t *status,
+                                                       double *traj_x, double *traj_u, int32_t *status_any, long long B, int N,
+                                                       int tick, int ticks, double dt)
+{
+    const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const double *x1 = x_opt + (b * N + 1) * NS, *u0 = u_opt + b * (N * 12), *c1 = c_hor + (b * N + 1) * 12;
+    double *x = x0 + b * NS;
+    if (traj_x) for (int i = 0; i < NS; i++) traj_x[(b * ticks + tick) * NS + i] = x[i];
+    if (traj_u) for (int i = 0; i < 12; i++) traj_u[(b * ticks + tick) * 12 + i] = u0[i];
+    for (int i = 0; i < NS; i++) x[i] = x1[i];
+    for (int i = 0; i < 12; i++) contacts_now[b * 12 + i] = c1[i];
+    sim_time[b] = __dadd_rn(sim_time[b], dt);
+    if (status_any) status_any[b] = (tick == 0 ? 0 : status_any[b]) | status[b];
+}
+
 } // namespace adaptors

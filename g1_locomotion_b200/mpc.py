@@ -159,6 +159,29 @@ class BatchedMPC:
         _lib.check(rc, "g1mpc_wbid_refs_batch")
         return refs
 
+    def closed_loop(self, x0, contacts_now, sim_time, ticks, x_ref=None, x_opt=None, record=True):
+        """`ticks` control periods of B walkers on the device (g1mpc_closed_loop_batch).  x0, contacts_now,
+        sim_time are advanced in place.  Returns dict(traj_x[B,ticks,13], traj_u[B,ticks,12], status_any[B], u_opt, x_opt, x_ref)."""
+        B, N = x0.shape[0], self.N
+        px0 = self._chk(x0, (B, NS), "x0"); pc = self._chk(contacts_now, (B, 12), "contacts_now")
+        pt = self._chk(sim_time, (B,), "sim_time")
+        mk = lambda *s: torch.zeros(*s, device=self.device, dtype=torch.float64)
+        x_ref = mk(B, N, NS) if x_ref is None else x_ref
+        x_opt = mk(B, N, NS) if x_opt is None else x_opt
+        pxr = self._chk(x_ref, (B, N, NS), "x_ref"); pxo = self._chk(x_opt, (B, N, NS), "x_opt")
+        u_opt = mk(B, N, 12)
+        traj_x = mk(B, ticks, NS) if record else None
+        traj_u = mk(B, ticks, 12) if record else None
+        status_any = torch.zeros(B, device=self.device, dtype=torch.int32)
+        stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        with torch.cuda.device(self.device):
+            rc = self._lib.g1mpc_closed_loop_batch(self._h, B, int(ticks), px0, pc, pt, pxr, pxo, C.c_void_p(u_opt.data_ptr()),
+                                                   C.c_void_p(traj_x.data_ptr()) if record else None,
+                                                   C.c_void_p(traj_u.data_ptr()) if record else None,
+                                                   C.c_void_p(status_any.data_ptr()), stream)
+        _lib.check(rc, "g1mpc_closed_loop_batch")
+        return dict(traj_x=traj_x, traj_u=traj_u, status_any=status_any, u_opt=u_opt, x_opt=x_opt, x_ref=x_ref)
+
     # -- host API (the reference-facing call: numpy in, numpy out, copies inside) -----------------
     def update_host(self, x0, x_ref, contact, c_horizon, p_com, x_current=None, one_rollout=False, x_opt=None):
         f = lambda a, shape: np.ascontiguousarray(np.asarray(a, dtype=np.float64).reshape(shape))

@@ -31,7 +31,7 @@ extern "C" {
 #endif
 
 #define G1MPC_NUM_STATES 13
-#define G1MPC_ABI_VERSION 2
+#define G1MPC_ABI_VERSION 3
 
 typedef enum g1mpc_error {
     G1MPC_OK = 0,
@@ -133,6 +133,19 @@ int g1mpc_walk_inputs_batch(g1mpc_handle *h, int64_t B, const double *x0, const 
 #define G1MPC_WBID_REFS 42
 int g1mpc_wbid_refs_batch(g1mpc_handle *h, int64_t B, const double *u_opt, const double *x_opt,
                           const double *foot_positions, double wbid_mass, double *refs, void *stream);
+
+/*
+ * SURVEY 8f-3 -- closed loop of B walkers for `ticks` control periods, all on the device (three launches per tick:
+ * g1mpc_walk_inputs_batch -> g1mpc_solve_batch with x_current = x0, full rollout -> advance).  The SRBD model is the
+ * plant, in the manner of the reference's own SRBD-only loop (g1_mpc/scripts/main.py:222-326, which feeds a rollout row
+ * back as the next x0): x0 <- x_opt[1], contact points <- row 1 of the planner's c_horizon, sim_time += dt.
+ * In/out: x0 [B,13], contacts_now [B,12], sim_time [B], x_ref [B,N,13], x_opt [B,N,13] (the previous solve; zeros at
+ * start), u_opt [B,N,12] (last tick's forces on return).  Optional outputs: traj_x [B,ticks,13] (state at the start of
+ * each tick), traj_u [B,ticks,12] (first-step forces applied), status_any [B] (OR of the per-tick solver statuses).
+ */
+int g1mpc_closed_loop_batch(g1mpc_handle *h, int64_t B, int32_t ticks, double *x0, double *contacts_now,
+                            double *sim_time, double *x_ref, double *x_opt, double *u_opt, double *traj_x,
+                            double *traj_u, int32_t *status_any, void *stream);
 
 /* Dynamic shared memory (bytes) and threads per CTA of the solve kernel for this handle's shape. */
 int g1mpc_kernel_info(const g1mpc_handle *h, int32_t *smem_bytes, int32_t *threads, int32_t *ctas_per_sm);

@@ -103,3 +103,25 @@ def wbid_set_reference(x_opt1, u_opt0, foot_positions_curr, mass):
 def wbid_refs_flat(x_opt1, u_opt0, feet, mass):
     d = wbid_set_reference(x_opt1, u_opt0, feet, mass)
     return np.concatenate([d["R"].ravel(), d["velocity"], d["acceleration"], d["com_pos"], d["com_vel"], d["com_acc"], d["wrench"]])
+
+
+def closed_loop(orc, preset, x0, contacts_now, sim_time, ticks):
+    """SURVEY 8f-3 on the CPU for ONE walker: node inputs -> reference build (oracle.build) -> exact QP minimiser
+    (oracle.qp_exact) -> reference rollout (mpc.cpp:427-446) -> x0 <- x_opt[1], contact points <- c_horizon[1], t += dt.
+    Returns traj_x[ticks,13], traj_u[ticks,12]."""
+    N, dt = preset["horizon"], preset["dt"]
+    g = preset.get("gravity", -9.80665)
+    p = orc.params_from_dict(preset)
+    x0 = np.array(x0, float); cur = np.array(contacts_now, float); t = float(sim_time)
+    x_ref = np.zeros((N, 13)); x_opt = np.zeros((N, 13))
+    tx, tu = np.zeros((ticks, 13)), np.zeros((ticks, 12))
+    for k in range(ticks):
+        x_ref, contact, c_hor, p_com, _ = node_update_inputs(x0, cur, t, x_opt, x_ref, dt, N, g)
+        m = orc.build(p, x0, x_ref, contact, c_hor, p_com)
+        xs, _, cert = orc.qp_exact(p, m["H"], m["g"], contact)
+        assert cert["rc"] == 0, cert
+        u = xs.reshape(N, 12)
+        x_opt = orc.rollout(p, m["A"], m["Bd"], u, x0, False, x_opt=x_opt.copy())
+        tx[k], tu[k] = x0, u[0]
+        x0, cur, t = x_opt[1].copy(), c_hor[1].copy(), t + dt
+    return tx, tu

@@ -86,3 +86,31 @@ def test_adaptors_reject_unsupported_shapes():
     with pytest.raises(RuntimeError):
         s.wbid_refs(torch.zeros(1, 10, 24, device="cuda", dtype=torch.float64), torch.zeros(1, 10, 13, device="cuda", dtype=torch.float64),
                     torch.zeros(1, 4, 3, device="cuda", dtype=torch.float64), 35.0)
+
+
+def test_closed_loop_matches_cpu_composition(orc):
+    """12 ticks of 6 walkers on the device == the same loop composed on the CPU from the node restatement, the
+    reference build, the exact QP minimiser and the reference rollout.  Forces within 2e-3 N, states within 1e-6."""
+    from g1_locomotion_b200 import BatchedMPC
+    from oracle import node_oracle as no
+    preset = presets.get_preset("cpp_node")
+    s = BatchedMPC(preset)
+    B, T, dt = 6, 12, preset["dt"]
+    rng = np.random.default_rng(8)
+    x0 = np.zeros((B, 13))
+    x0[:, 3] = 0.05 + 0.1 * np.arange(B); x0[:, 4] = 7.44339342e-05; x0[:, 5] = 5.97983255e-01; x0[:, 9] = 0.35
+    x0[:, 12] = np.float32(-9.80665)
+    x0[:, :12] += rng.normal(0, 0.003, (B, 12))
+    cur = np.zeros((B, 4, 3))
+    cur[:, :, 0] = x0[:, 3:4] + np.array([-0.0293, 0.1406, -0.0293, 0.1406])
+    cur[:, :, 1] = np.array([0.118508, 0.118508, -0.118508, -0.118508])
+    t0 = (np.array([0, 3, 7, 12, 18, 26]) + 0.5) * dt
+    out = s.closed_loop(_dev(x0), _dev(cur.reshape(B, 12)), _dev(t0), T)
+    torch.cuda.synchronize()
+    assert int(out["status_any"].abs().sum()) == 0
+    tx, tu = out["traj_x"].cpu().numpy(), out["traj_u"].cpu().numpy()
+    for b in range(B):
+        wx, wu = no.closed_loop(orc, preset, x0[b], cur[b].ravel(), t0[b], T)
+        assert np.abs(tx[b] - wx).max() <= 1e-6, (b, np.abs(tx[b] - wx).max())
+        assert np.abs(tu[b] - wu).max() <= 2e-3, (b, np.abs(tu[b] - wu).max())
+    assert np.array_equal(tx[:, 0], x0)
