@@ -105,14 +105,13 @@ __device__ __forceinline__ double frcp(double d)
 }
 
 // LDL' of a symmetric positive definite 6x6 held packed (21) in registers; afterwards a[tri(i,j)], i>j, holds
-// the unit-lower factor and dinv[j] = 1/d_j.  Returns false on a non-positive pivot.
-__device__ __forceinline__ bool ldl6(double (&a)[21], double (&dinv)[6])
+// the unit-lower factor and dinv[j] = 1/d_j.  `neg` collects the sign bits of the pivots (negative => not positive definite).
+__device__ __forceinline__ void ldl6(double (&a)[21], double (&dinv)[6], int &neg)
 {
-    bool ok = true;
 #pragma unroll
     for (int j = 0; j < 6; j++) {
         const double dj = a[tri(j, j)];
-        ok = ok && (dj > 0.0);
+        neg |= __double2hiint(dj);                   // sign bit of any pivot; a zero pivot shows up as Inf/NaN later
         const double r = frcp(dj);
         dinv[j] = r;
         double col[6];
@@ -126,7 +125,6 @@ __device__ __forceinline__ bool ldl6(double (&a)[21], double (&dinv)[6])
             a[tri(i, j)] = lij;
         }
     }
-    return ok;
 }
 // x <- L^-1 x  (unit lower, packed)
 __device__ __forceinline__ void fsub6(const double (&l)[21], double (&x)[6])
@@ -155,8 +153,8 @@ __device__ __forceinline__ void adj3(double a, double b, double c, double d, dou
 
 // Inverse of a symmetric positive definite 6x6 (packed lower, 21) through its 3x3 blocks M = [[A,B'],[B,C]] in
 // closed form: two reciprocals on the dependent chain instead of the six of an LDL' (measured: the reciprocal
-// chain was the largest single item of the v3 profile).  Returns false if a leading minor is not positive.
-__device__ __forceinline__ bool inv6(const double (&m)[21], double (&o)[21])
+// chain was the largest single item of the v3 profile).  `neg` collects the sign bits of the leading minors.
+__device__ __forceinline__ void inv6(const double (&m)[21], double (&o)[21], int &neg)
 {
     double aA[6], detA;
     adj3(m[0], m[1], m[2], m[3], m[4], m[5], aA, detA);
@@ -203,7 +201,7 @@ __device__ __forceinline__ bool inv6(const double (&m)[21], double (&o)[21])
     for (int i = 0; i < 3; i++)
 #pragma unroll
         for (int j = 0; j < 3; j++) o[tri(3 + i, j)] = -rr2 * Y0[i][j];
-    return (m[0] > 0.0) && (aA[5] > 0.0) && (detA > 0.0) && (Sc[0] > 0.0) && (aS[5] > 0.0) && (detS > 0.0);
+    neg |= __double2hiint(m[0]) | __double2hiint(aA[5]) | __double2hiint(detA) | __double2hiint(Sc[0]) | __double2hiint(aS[5]) | __double2hiint(detS);
 }
 
 // 16-byte shared-memory accesses: p must be 16-byte aligned (every row / packed block of WLay is)
@@ -404,7 +402,7 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
 #pragma unroll
     for (int i = 0; i < 6; i++) p11[i] = i == cb ? sq1 : 0.0;
     __syncwarp();
-    bool ok = true;
+    int neg = 0;
 #pragma unroll 1
     for (int k = N - 1; k >= 0; k--) {
         double *St = sm + L_::oRic + k * L_::STG;
@@ -418,12 +416,12 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
             ld22(St + L_::sP22, ld);
 #pragma unroll
             for (int e = 0; e < 21; e++) T[e] = ld[e];
-            ok = inv6(T, Pi) && ok;
+            inv6(T, Pi, neg);
             ld22(Sk, ld);
 #pragma unroll
             for (int e = 0; e < 21; e++) T[e] = Pi[e] + ld[e];
         }
-        ok = ldl6(T, dT) && ok;
+        ldl6(T, dT, neg);
         // column pipeline: Gamma [ I | P21 | P22 ] -> Gamma | A21 | A22,  Gamma = T^-1 Pi
         double col[6];
         {
@@ -484,7 +482,7 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
             __syncwarp();
         }
     }
-    return ok;
+    return neg >= 0;
 }
 
 
