@@ -26,7 +26,8 @@ def build(force=False, extra=""):
     """Compile csrc/g1mpc_kernels.cu for sm_100a into the package directory (nvcc cross-compiles without a GPU)."""
     src = os.path.join(_HERE, "csrc", "g1mpc_kernels.cu")
     hdr = os.path.join(_HERE, "..", "include", "g1mpc_b200.h")
-    stale = (not os.path.exists(LIB_PATH)) or os.path.getmtime(LIB_PATH) < max(os.path.getmtime(src), os.path.getmtime(hdr))
+    deps = [src, hdr] + [os.path.join(_HERE, "csrc", f) for f in ("srbd_solve_warp.cuh", "node_adaptors.cuh")]
+    stale = (not os.path.exists(LIB_PATH)) or os.path.getmtime(LIB_PATH) < max(os.path.getmtime(d) for d in deps)
     if force or stale:
         cmd = ["make", "-C", os.path.join(_HERE, "csrc"), "-B", "../libg1mpc_b200.so"]
         if extra:
