@@ -259,3 +259,26 @@ def test_host_api_chunk_pipeline_equals_device_api(B, use_xc, one):
         assert np.array_equal(xh[:, 0], x_prev[:, 0])
     if one:
         assert np.array_equal(xh[:, 2:], x_prev[:, 2:])
+
+
+def test_config1_walking_replay_single_solves(orc):
+    """Config 1: consecutive ticks of the walking demo, ONE problem per call through the reference-facing `MPC` class
+    (mpc_to_wbid_node.cpp:494 calls updateMPC once per tick); every tick against the exact minimiser."""
+    from g1_locomotion_b200 import MPC
+    preset = presets.get_preset("cpp_node")
+    ticks = inputs.walking_replay(preset, n_ticks=24)
+    p = orc.params_from_dict(preset)
+    m = MPC.cpp_node()
+    m.init_matrices()
+    worst = 0.0
+    for t in range(24):
+        x0, x_ref, contact, c_hor, p_com = [a[t] for a in ticks]
+        m.x0 = x0.copy(); m.x_ref_hor = x_ref.copy()
+        u, x = m.update(contact, c_hor, p_com, x_current=x0.copy(), one_rollout=False)
+        q = orc.build(p, x0, x_ref, contact, c_hor, p_com)
+        xs, _, cert = orc.qp_exact(p, q["H"], q["g"], contact)
+        assert cert["rc"] == 0
+        worst = max(worst, np.abs(u.ravel() - xs).max())
+        want = orc.rollout(p, q["A"], q["Bd"], u, x0, False, x_opt=np.zeros((10, 13)))
+        assert rel_err(x, want) <= MAT_TOL
+    assert worst <= GRF_TOL, worst
