@@ -23,6 +23,19 @@
 
 namespace v2 {
 
+// optional per-phase cycle counters (development builds: -DG1MPC_PHASE_CLOCKS; written over the first 8 entries of y_opt)
+#ifdef G1MPC_PHASE_CLOCKS
+#define PH_DECL long long ph_t[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; long long ph_last = clock64();
+#define PH(i) { const long long ph_now = clock64(); ph_t[i] += ph_now - ph_last; ph_last = ph_now; }
+#define PH_PARAMS , long long (&ph_t)[16], long long &ph_last
+#define PH_ARGS , ph_t, ph_last
+#else
+#define PH_DECL
+#define PH(i)
+#define PH_PARAMS
+#define PH_ARGS
+#endif
+
 constexpr unsigned kFullMask = 0xffffffffu;
 
 __device__ __forceinline__ double wsum(double v)
@@ -383,9 +396,9 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
 #pragma unroll
     for (int i = 0; i < 6; i++) if (cb == i) { sq1 = P.scale * P.q[i]; sq2 = P.scale * P.q[6 + i]; }
     asm volatile("" : "+d"(sq1), "+d"(sq2));                    // keep them in registers (no re-derivation per stage)
-    int o22[6];                                                 // offsets of column cb inside a packed symmetric 6x6
+    int oc[6];                                                  // stage-slot offsets of this lane's column of [ I | P21 | P22 ]
 #pragma unroll
-    for (int i = 0; i < 6; i++) o22[i] = trs(i, cb);
+    for (int i = 0; i < 6; i++) oc[i] = grp == 1 ? L_::sP12 + 6 * cb + i : L_::sP22 + trs(i, cb);   // (group 0: loaded, not used)
     // P_N = s Q
     {
         double *St = sm + L_::oRic + (N - 1) * L_::STG;
@@ -410,6 +423,13 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
         // Pi = P22^-1 in closed form (P22 is well conditioned: adjugate blocks are accurate enough), T = Pi + S_k by
         // LDL' (T spans the full range of the barrier weights: the closed form stalls the interior point there --
         // measured at N = 40, nc = 8; tests/test_ipm_model_cpu.py keeps the experiment)
+        double c[6];                                            // issued first: nothing below depends on it until the mat-vec
+#pragma unroll
+        for (int i = 0; i < 6; i++) c[i] = St[oc[i]];
+        if (grp == 0) {
+#pragma unroll
+            for (int i = 0; i < 6; i++) c[i] = i == cb ? 1.0 : 0.0;
+        }
         double Pi[21], T[21], dT[6];
         {
             double ld[22];
@@ -425,12 +445,6 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
         // column pipeline: Gamma [ I | P21 | P22 ] -> Gamma | A21 | A22,  Gamma = T^-1 Pi
         double col[6];
         {
-            double c[6];
-            if (grp == 1) ld6(St + L_::sP12 + 6 * cb, c);
-            else {
-#pragma unroll
-                for (int i = 0; i < 6; i++) c[i] = grp == 0 ? (i == cb ? 1.0 : 0.0) : St[L_::sP22 + o22[i]];
-            }
             symmv6(Pi, c, col);
             fsub6(T, col);
 #pragma unroll
@@ -459,24 +473,27 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
             phiT6(C.F, a11, pa);
 #pragma unroll
             for (int i = 0; i < 6; i++) {
-                Ex[6 * i + cb] = col[i];
                 pa[i] += col[i];
                 p11[i] = a11[i] + (i == cb ? sq1 : 0.0);
             }
+            st6(Ex + 6 * cb, col);                              // A21 column cb, contiguous
             st6(Sn + L_::sP12 + 6 * cb, pa);
         }
         __syncwarp();
         if (k > 0) {
             // P22 of P_k, column cb = s Q2 + A22 + Phi' M12 + A21 Phi      (group 2)
-            if (act && grp == 2) {
-                double m12[6], pm[6];
+            // (every lane runs the arithmetic -- no divergence; only group 2 holds A22 in `col` and stores)
+            {
+                double m12[6], pm[6], ca[6], cbv[6];
 #pragma unroll
                 for (int i = 0; i < 6; i++) m12[i] = Sn[L_::sP12 + 6 * i + cb];
+                ld6(Ex + 6 * ja, ca); ld6(Ex + 6 * jb, cbv);
                 phiT6(C.F, m12, pm);
+                const bool st2 = act && grp == 2;
 #pragma unroll
                 for (int i = 0; i < 6; i++) {
-                    const double val = col[i] + pm[i] + ga * Ex[6 * i + ja] + gb * Ex[6 * i + jb] + (i == cb ? sq2 : 0.0);
-                    if (i >= cb) Sn[L_::sP22 + o22[i]] = val;
+                    const double val = fma(ga, ca[i], fma(gb, cbv[i], col[i] + pm[i])) + (i == cb ? sq2 : 0.0);
+                    if (st2 && i >= cb) Sn[oc[i]] = val;
                 }
             }
             __syncwarp();
@@ -491,7 +508,7 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
 // component each) and exchange the 12-vector through shared memory once per stage (42 cycles measured for
 // STS + sync + LDS against 27 for one dependent shuffle, but 8 instructions instead of 16-28 SHFL).
 template <int N, int NC>
-__device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int lane)
+__device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int lane PH_PARAMS)
 {
     using L_ = WLay<N, NC>;
     double *vA = sm + L_::oVa, *vB = sm + L_::oVb, *vC = sm + L_::oVc, *vD = sm + L_::oVd, *pbuf = sm + L_::oPb;
@@ -519,6 +536,7 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
         for (int i = 0; i < 6; i++) c2[i] += pc1[i];
         st6(vA + 6 * k, gt); st6(vB + 6 * k, c1); st6(vC + 6 * k, c2);
     }
+    PH(8)
     const int r6 = lane % 6;
     if (lane < 6) { vD[6 * (N - 1) + r6] = 0.0; pbuf[6 * (N & 1) + r6] = 0.0; }     // zero terminal co-state
     __syncwarp();
@@ -540,12 +558,14 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
             const double *pp = pbuf + 6 * ((k + 1) & 1);
             const double pa = pp[ja], pb = pp[jb];
             const double acc = dot6(row, p2);
-            pown = lane < 6 ? (pown - acc + cadd) : fma(ga, pa, fma(gb, pb, acc + cadd));
+            const double base = lane < 6 ? pown + cadd : fma(ga, pa, fma(gb, pb, cadd));     // off the dot-product chain
+            pown = lane < 6 ? base - acc : base + acc;
             if (lane < 6) pbuf[6 * (k & 1) + r6] = pown;
             else if (lane < 12 && k > 0) vD[6 * (k - 1) + r6] = pown;
             __syncwarp();
         }
     }
+    PH(9)
     // ---- b_k = gt_k - S_k Gamma p2   (lane = stage)
     for (int k = lane; k < N; k += 32) {
         const double *St = sm + L_::oRic + k * L_::STG;
@@ -562,6 +582,7 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
     }
     if (lane < 6) vB[r6] = 0.0;                     // y1 after stage 0 (y2 after stage 0 is b_0, already in vA)
     __syncwarp();
+    PH(10)
     // ---- forward sweep:  y1 <- y1 + Phi y2 ;  y2 <- b + G2^T y2 - Psi^T y1   (old values on the right)
     {
         double yown = lane < 6 ? 0.0 : vA[r6];
@@ -584,6 +605,7 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
             __syncwarp();
         }
     }
+    PH(11)
     // ---- output (lane = stage): y_k = P12^T y1 + P22 y2 + p2 ; zeta~ = Bm^T y_k
     for (int k = lane; k < N; k += 32) {
         const double *St = sm + L_::oRic + k * L_::STG;
@@ -608,6 +630,7 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
         st6(vA + 6 * k, o);
     }
     __syncwarp();
+    PH(12)
 }
 
 
@@ -779,14 +802,17 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
     const double m_ineq = 6.0 * (double)(n_stance > 0 ? n_stance : 1);
     __syncwarp();
 
+    PH_DECL
     int status = G1MPC_MAX_ITER, it = 0;
     double gap = 0.0, rdmax = 0.0;
     bool lam_init = false;
 
 #pragma unroll 1
     for (it = 0;; it++) {
+        PH(7)
         // (1) gradient: V <- Bm^T (M W u + h)
         gradient_sweeps<N, NC>(sm, P, C, lane);
+        PH(0)
         const double *Vt = sm + L_::oV;
         // (2) per stance contact: grad f, dual residual, gap, reciprocals and D-state of the 3x3 block,
         //     predictor t = -Dblk^-1 grad f
@@ -845,13 +871,17 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         if (it >= P.max_iter) { status = G1MPC_MAX_ITER; break; }
         __syncwarp();
 
+        PH(1)
         // (3) S_k, t_k, then the backward Riccati sweep (shared by predictor and corrector)
         assemble_stage<N, NC, true>(sm, P, C, lane);
         __syncwarp();
+        PH(2)
         if (!factor_stages<N, NC>(sm, P, C, lane)) { status = G1MPC_NUMERICAL; break; }
+        PH(3)
         // (4) predictor.  With x = ds/s:  dl = -lam (1 + x), and the largest feasible step is
         //     1 / max_i max(-x_i, 1 + x_i)  -- no division per constraint.
-        solve_stages<N, NC>(sm, C, lane);
+        solve_stages<N, NC>(sm, C, lane PH_ARGS);
+        PH(4)
         const double *zt = sm + L_::oVa;
         double p_rmax = 0.0, p_sum = 0.0;
         for (int i = lane; i < n_stance; i += 32) {
@@ -898,7 +928,9 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         __syncwarp();
         assemble_stage<N, NC, false>(sm, P, C, lane);
         __syncwarp();
-        solve_stages<N, NC>(sm, C, lane);
+        PH(5)
+        solve_stages<N, NC>(sm, C, lane PH_ARGS);
+        PH(4)
         // (6) combined direction, step length (the stage storage is dead now: ds | dl live there).
         //     dl = -lam (1 + x + q/lam)
         p_rmax = 0.0;
@@ -940,6 +972,7 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
             }
         }
         __syncwarp();
+        PH(6)
     }
 
     // ---- outputs ------------------------------------------------------------------------------------
@@ -1010,6 +1043,9 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
             for (int i = 0; i < 5; i++) gy[5 * c + i] = y5[i];
         }
     }
+#ifdef G1MPC_PHASE_CLOCKS
+    if (io.y_opt && lane == 0) { __syncwarp(1u); for (int i = 0; i < 16; i++) io.y_opt[b * (5 * NCN) + i] = (double)ph_t[i]; }
+#endif
     // rollout (mpc.cpp:427-446) in closed form; x_opt is in/out
     {
         double *gx = io.x_opt + b * (N * NS);

@@ -282,3 +282,32 @@ def test_config1_walking_replay_single_solves(orc):
         want = orc.rollout(p, q["A"], q["Bd"], u, x0, False, x_opt=np.zeros((10, 13)))
         assert rel_err(x, want) <= MAT_TOL
     assert worst <= GRF_TOL, worst
+
+
+def test_config5_full_size_shard_of_2pow20():
+    """Config 5: 2^20 problems cut into the 8 contiguous shards of a box; one rank's shard (131,072 problems, generated on
+    the device with the shard's own seed) through the same driver the multi-GPU run uses.  Size-independent properties."""
+    from g1_locomotion_b200 import sharding
+    preset = presets.get_preset("cpp_node")
+    total, world, rank = 1 << 20, 8, 5
+    lo, hi = sharding.shard_range(total, rank, world)
+    assert hi - lo == total // world and sum(sharding.shard_sizes(total, world)) == total
+    s = _solver(preset)
+    make = lambda a, b: inputs.random_batch(preset, b - a, seed=13 + rank, device="cuda")
+    keep = {}
+
+    def solve(*ins):
+        keep["ins"] = ins
+        return s.update_batch(*ins, x_current=ins[0])
+    # single process: the "gather" of one shard is the shard itself
+    payload, u, x, info = sharding.solve_sharded(solve, lambda a, b: make(lo, hi), hi - lo)
+    B = hi - lo
+    assert payload.shape == (B, 12 + 13)
+    assert int((info["status"] != 0).sum()) == 0
+    f = u.view(B, 10, 4, 3)
+    mu = preset["mu"]
+    assert float((f[..., 0].abs() - mu * f[..., 2]).max()) <= 0.0 and float((f[..., 1].abs() - mu * f[..., 2]).max()) <= 0.0
+    ct = keep["ins"][2]
+    assert torch.all(f[ct == 0] == 0)
+    assert torch.equal(payload[:, :12], u[:, 0]) and torch.equal(payload[:, 12:], x[:, 1])
+    assert float(info["resid"][:, 0].max()) <= 1e-10 and float(info["resid"][:, 2].max()) == 0.0
