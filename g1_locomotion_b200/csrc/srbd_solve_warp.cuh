@@ -545,23 +545,31 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
     const double fa = r6 == 0 ? F.dc : (r6 == 1 ? F.dsn : F.dt), fb = r6 == 0 ? -F.dsn : (r6 == 1 ? F.dc : 0.0);
     const int ja = r6 < 2 ? 0 : r6, jb = r6 < 2 ? 1 : r6;
     // ---- backward sweep (lane r < 6: p1_r, lane 6+r: p2_r; lanes >= 12 shadow lanes 6..11 and never store):
-    //      p1 <- p1 - Psi p2 + c1 ;  p2 <- Phi^T p1 + G2 p2 + c2 ;  vD[k] keeps the p2 that stage k receives
+    //      p1 <- p1 - Psi p2 + c1 ;  p2 <- Phi^T p1 + G2 p2 + c2 ;  vD[k] keeps the p2 that stage k receives.
+    //      Branch-free: one predicated store per step; the loads that do not depend on the recurrence (matrix row,
+    //      constant term) are issued one step ahead, before the barrier.
+    const bool lo6 = lane < 6;
     {
-        double pown = 0.0;
+        const double *rowp = sm + L_::oRic + (lo6 ? L_::sPsi : L_::sG2) + 6 * r6;      // + k STG
+        const double *cp = (lo6 ? vB : vC) + r6;                                        // + 6 k
+        double *dstp = lo6 ? pbuf + r6 : vD + r6 - 6;                                   // p1 -> pbuf[6 (k&1)], p2 -> vD[6 (k-1)]
+        const bool wr = lane < 12;
+        double pown = 0.0, row[6], cadd;
+        ld6(rowp + (N - 1) * L_::STG, row); cadd = cp[6 * (N - 1)];
 #pragma unroll 2
         for (int k = N - 1; k >= 0; k--) {
-            const double *St = sm + L_::oRic + k * L_::STG;
-            double row[6], p2[6];
-            ld6(St + (lane < 6 ? L_::sPsi : L_::sG2) + 6 * r6, row);
+            double p2[6];
             ld6(vD + 6 * k, p2);
-            const double cadd = (lane < 6 ? vB : vC)[6 * k + r6];
             const double *pp = pbuf + 6 * ((k + 1) & 1);
             const double pa = pp[ja], pb = pp[jb];
-            const double acc = dot6(row, p2);
-            const double base = lane < 6 ? pown + cadd : fma(ga, pa, fma(gb, pb, cadd));     // off the dot-product chain
-            pown = lane < 6 ? base - acc : base + acc;
-            if (lane < 6) pbuf[6 * (k & 1) + r6] = pown;
-            else if (lane < 12 && k > 0) vD[6 * (k - 1) + r6] = pown;
+            double acc = dot6(row, p2);
+            double b_lo = pown + cadd, b_hi = fma(ga, pa, fma(gb, pb, cadd));           // off the dot-product chain
+            // every lane computes both forms: without the barrier ptxas splits the warp into three divergent groups and
+            // runs the dot product twice (measured: 274 -> 444 cycles per step when it did)
+            asm volatile("" : "+d"(acc), "+d"(b_lo), "+d"(b_hi));
+            pown = lo6 ? b_lo - acc : b_hi + acc;
+            if (wr && (lo6 || k > 0)) dstp[lo6 ? 6 * (k & 1) : 6 * k] = pown;
+            if (k > 0) { ld6(rowp + (k - 1) * L_::STG, row); cadd = cp[6 * (k - 1)]; }
             __syncwarp();
         }
     }
@@ -585,23 +593,33 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
     PH(10)
     // ---- forward sweep:  y1 <- y1 + Phi y2 ;  y2 <- b + G2^T y2 - Psi^T y1   (old values on the right)
     {
-        double yown = lane < 6 ? 0.0 : vA[r6];
+        const double *g2p = sm + L_::oRic + L_::sG2 + r6, *psp = sm + L_::oRic + L_::sPsi + r6;   // column r6: + k STG + 6 i
+        double *dstp = (lo6 ? vB : vA) + r6;                                                      // + 6 k
+        const bool wr = lane < 12;
+        double yown = lo6 ? 0.0 : vA[r6];
+        double g2c[6], psc[6], bk;
+#pragma unroll
+        for (int i = 0; i < 6; i++) { g2c[i] = g2p[L_::STG + 6 * i]; psc[i] = psp[L_::STG + 6 * i]; }
+        bk = vA[6 + r6];
 #pragma unroll 2
         for (int k = 1; k < N; k++) {
-            const double *St = sm + L_::oRic + k * L_::STG;
             double y1[6], y2[6];
             ld6(vB + 6 * (k - 1), y1); ld6(vA + 6 * (k - 1), y2);
-            const double bk = vA[6 * k + r6];
-            double acc0 = bk, acc1 = 0.0;
-#pragma unroll
-            for (int i = 0; i < 6; i++) {
-                acc0 = fma(St[L_::sG2 + 6 * i + r6], y2[i], acc0);
-                acc1 = fma(St[L_::sPsi + 6 * i + r6], y1[i], acc1);
-            }
             const double ya = vA[6 * (k - 1) + ja], yb = vA[6 * (k - 1) + jb];
-            yown = lane < 6 ? fma(fa, ya, fma(fb, yb, yown)) : (acc0 - acc1);
-            if (lane < 6) vB[6 * k + r6] = yown;
-            else if (lane < 12) vA[6 * k + r6] = yown;
+            // four chains of three
+            const double a0 = fma(g2c[4], y2[4], fma(g2c[2], y2[2], fma(g2c[0], y2[0], bk)));
+            const double a1 = fma(g2c[5], y2[5], fma(g2c[3], y2[3], g2c[1] * y2[1]));
+            const double b0 = fma(psc[4], y1[4], fma(psc[2], y1[2], psc[0] * y1[0]));
+            const double b1 = fma(psc[5], y1[5], fma(psc[3], y1[3], psc[1] * y1[1]));
+            double v_lo = fma(fa, ya, fma(fb, yb, yown)), v_hi = (a0 + a1) - (b0 + b1);
+            asm volatile("" : "+d"(v_lo), "+d"(v_hi));          // both forms in every lane: no divergent split (see above)
+            yown = lo6 ? v_lo : v_hi;
+            if (wr) dstp[6 * k] = yown;
+            if (k + 1 < N) {
+#pragma unroll
+                for (int i = 0; i < 6; i++) { g2c[i] = g2p[(k + 1) * L_::STG + 6 * i]; psc[i] = psp[(k + 1) * L_::STG + 6 * i]; }
+                bk = vA[6 * (k + 1) + r6];
+            }
             __syncwarp();
         }
     }
