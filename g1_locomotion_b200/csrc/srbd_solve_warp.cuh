@@ -825,25 +825,34 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
     double gap = 0.0, rdmax = 0.0;
     bool lam_init = false;
 
+    // grad f is recomputed from u (two O(N) sweeps) only near the end; while the gap is large it is carried along with
+    // the step, grad f += alpha (s r du + W^T y), because the multiplier wrench of the corrector solve IS M W du.  The
+    // carried gradient drifts by ~1e-7 relative (the residual of the stage-wise solve), which the exact evaluations of
+    // the last iterations remove; the iteration that stops always runs on an exact one (tests/test_ipm_model_cpu.py).
+    bool exact = true;
+    const double exact_gap = 1e7 * P.gap_tol;
 #pragma unroll 1
     for (it = 0;; it++) {
         PH(7)
-        // (1) gradient: V <- Bm^T (M W u + h)
-        gradient_sweeps<N, NC>(sm, P, C, lane);
-        PH(0)
-        const double *Vt = sm + L_::oV;
-        // (2) per stance contact: grad f, dual residual, gap, reciprocals and D-state of the 3x3 block,
-        //     predictor t = -Dblk^-1 grad f
+    again:
         double p_gf = 0.0;
-        for (int i = lane; i < n_stance; i += 32) {
-            const int c = stIdx[i], k = c / NC;
-            const double *vk = Vt + 6 * k, *r = rr + 3 * c, *uc = u + 3 * c;
-            const double g0 = sr * uc[0] + (vk[1] * r[2] - vk[2] * r[1]) + vk[3];
-            const double g1 = sr * uc[1] + (vk[2] * r[0] - vk[0] * r[2]) + vk[4];
-            const double g2 = sr * uc[2] + (vk[0] * r[1] - vk[1] * r[0]) + vk[5];
-            gf[3 * c] = g0; gf[3 * c + 1] = g1; gf[3 * c + 2] = g2;
-            p_gf = fmax(p_gf, fmax(fabs(g0), fmax(fabs(g1), fabs(g2))));
+        if (exact) {
+            // (1) gradient: V <- Bm^T (M W u + h)
+            gradient_sweeps<N, NC>(sm, P, C, lane);
+            PH(0)
+            const double *Vt = sm + L_::oV;
+            for (int i = lane; i < n_stance; i += 32) {
+                const int c = stIdx[i], k = c / NC;
+                const double *vk = Vt + 6 * k, *r = rr + 3 * c, *uc = u + 3 * c;
+                const double g0 = sr * uc[0] + (vk[1] * r[2] - vk[2] * r[1]) + vk[3];
+                const double g1 = sr * uc[1] + (vk[2] * r[0] - vk[0] * r[2]) + vk[4];
+                const double g2 = sr * uc[2] + (vk[0] * r[1] - vk[1] * r[0]) + vk[5];
+                gf[3 * c] = g0; gf[3 * c + 1] = g1; gf[3 * c + 2] = g2;
+                p_gf = fmax(p_gf, fmax(fabs(g0), fmax(fabs(g1), fabs(g2))));
+            }
         }
+        // (2) per stance contact: dual residual, gap, reciprocals and D-state of the 3x3 block,
+        //     predictor t = -Dblk^-1 grad f
         if (!lam_init) {
             // lambda_0 = mu0 / s with mu0 tied to the gradient scale at the start point
             const double mu0 = fmax(1e-2, 0.1 * wmax(p_gf));
@@ -885,6 +894,7 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         }
         gap = wsum(p_gap) / m_ineq; rdmax = wmax(p_rd);
         if (!(gap == gap) || !(rdmax == rdmax) || isinf(gap) || isinf(rdmax)) { status = G1MPC_NUMERICAL; break; }
+        if (!exact && (gap <= P.gap_tol || it >= P.max_iter)) { exact = true; __syncwarp(); goto again; }   // never stop on a carried gradient
         if (gap <= P.gap_tol || n_stance == 0) { status = G1MPC_SOLVED; break; }
         if (it >= P.max_iter) { status = G1MPC_MAX_ITER; break; }
         __syncwarp();
@@ -956,9 +966,11 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
             const int c = stIdx[i], k = c / NC;
             const double *z = zt + 6 * k, *r = rr + 3 * c, *Ds = Dst + 9 * c, *l6 = lam + 6 * c, *q6 = prod + 6 * c;
             double rt[3], X[18], Di[6];
-            rt[0] = -gf[3 * c] + (q6[0] - q6[1]) - ((z[1] * r[2] - z[2] * r[1]) + z[3]);
-            rt[1] = -gf[3 * c + 1] + (q6[2] - q6[3]) - ((z[2] * r[0] - z[0] * r[2]) + z[4]);
-            rt[2] = -gf[3 * c + 2] + (-mu * (q6[0] + q6[1] + q6[2] + q6[3]) + q6[4] - q6[5]) - ((z[0] * r[1] - z[1] * r[0]) + z[5]);
+            const double wy0 = (z[1] * r[2] - z[2] * r[1]) + z[3], wy1 = (z[2] * r[0] - z[0] * r[2]) + z[4];     // W_c^T y
+            const double wy2 = (z[0] * r[1] - z[1] * r[0]) + z[5];
+            rt[0] = -gf[3 * c] + (q6[0] - q6[1]) - wy0;
+            rt[1] = -gf[3 * c + 1] + (q6[2] - q6[3]) - wy1;
+            rt[2] = -gf[3 * c + 2] + (-mu * (q6[0] + q6[1] + q6[2] + q6[3]) + q6[4] - q6[5]) - wy2;
             const double D0 = l6[0] * Ds[0], D1 = l6[1] * Ds[1], D2 = l6[2] * Ds[2], D3 = l6[3] * Ds[3];
             contact_dinv(D0, D1, D2, D3, Ds[6], Ds[7], Ds[8], mu, Di);
             contact_X(D0, D1, D2, D3, Ds[6], Ds[7], Ds[8], sr, mu, X);
@@ -973,6 +985,7 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
                 p_rmax = fmax(p_rmax, fmax(-x, rl));
                 dsv[6 * c + j] = dsi; dlv[6 * c + j] = -l6[j] * rl;
             }
+            prod[6 * c] = wy0; prod[6 * c + 1] = wy1; prod[6 * c + 2] = wy2;        // q is dead: keep W_c^T y for the gradient
         }
         // fraction to the boundary: 0.995 while the predictor is blocked, -> 1 quadratically once it is not (a_aff -> 1),
         // so that the last iterations are not held at a factor 200 per step (one iteration fewer on every preset)
@@ -982,13 +995,17 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         for (int i = lane; i < n_stance; i += 32) {
             const int c = stIdx[i];
 #pragma unroll
-            for (int p = 0; p < 3; p++) u[3 * c + p] += alpha * tv[3 * c + p];
+            for (int p = 0; p < 3; p++) {
+                u[3 * c + p] += alpha * tv[3 * c + p];
+                gf[3 * c + p] += alpha * fma(sr, tv[3 * c + p], prod[6 * c + p]);
+            }
 #pragma unroll
             for (int j = 0; j < 6; j++) {
                 lam[6 * c + j] += alpha * dlv[6 * c + j];
                 sl[6 * c + j] += alpha * dsv[6 * c + j];
             }
         }
+        exact = gap * (1.0 - alpha * (1.0 - sig)) < exact_gap;       // predicted gap of the next iterate
         __syncwarp();
         PH(6)
     }

@@ -198,10 +198,15 @@ def solve_ipm(prob, gap_tol=1e-10, max_iter=40, linear="riccati"):
     mu0 = max(1e-2, 0.1 * np.abs(gf[st]).max()) if st.any() else 0.0
     lam[st] = mu0 / s[st]
     it = 0
+    exact = True            # the kernel carries grad f along with the step while the gap is large (srbd_solve_warp.cuh)
     while True:
-        gf = grad(u)
+        if exact:
+            gf = grad(u)
         gap = float((s[st] * lam[st]).sum() / m_ineq) if st.any() else 0.0
         if gap <= gap_tol or not st.any() or it >= max_iter:
+            if not exact:
+                exact = True
+                continue
             return u, it, gap
         Dinv = np.zeros((N, nc, 3, 3)); X = np.zeros((N, nc, 6, 3)); S = np.zeros((N, 6, 6))
         for k in range(N):
@@ -236,10 +241,12 @@ def solve_ipm(prob, gap_tol=1e-10, max_iter=40, linear="riccati"):
                         tw[k] += Wk[k][:, 3 * j:3 * j + 3] @ (Dinv[k, j] @ rhs[k, j])
             y = lin_solve(tw)
             amin = 1e300
+            wy = np.zeros_like(u)
             for k in range(N):
                 for j in range(nc):
                     if st[k, j]:
-                        rt = rhs[k, j] - Wk[k][:, 3 * j:3 * j + 3].T @ y[k]
+                        wy[k, j] = Wk[k][:, 3 * j:3 * j + 3].T @ y[k]
+                        rt = rhs[k, j] - wy[k, j]
                         du[k, j] = Dinv[k, j] @ rt
                         ds[k, j] = -(X[k, j] @ rt)
                         dl[k, j] = -lam[k, j] - q[k, j] - (lam[k, j] / s[k, j]) * ds[k, j]
@@ -249,10 +256,14 @@ def solve_ipm(prob, gap_tol=1e-10, max_iter=40, linear="riccati"):
             if pas == 0:
                 a_aff = min(1.0, amin)
                 g_aff = float(((s[st] + a_aff * ds[st]) * (lam[st] + a_aff * dl[st])).sum() / m_ineq)
-                sigma_gap = (g_aff / gap) ** 3 * gap
+                sig = (g_aff / gap) ** 3
+                sigma_gap = sig * gap
             else:
                 alpha = min(1.0, min(0.99999, max(0.995, 1.0 - (1.0 - a_aff) ** 2)) * amin)
         u[st] += alpha * du[st]; lam[st] += alpha * dl[st]; s[st] += alpha * ds[st]
+        gf = gf.copy()
+        gf[st] += alpha * (sr * du[st] + wy[st])        # y = M W du: the carried gradient
+        exact = gap * (1.0 - alpha * (1.0 - sig)) < 1e7 * gap_tol
         it += 1
 
 
