@@ -29,7 +29,16 @@ namespace v2 {
 #define PH(i) { const long long ph_now = clock64(); ph_t[i] += ph_now - ph_last; ph_last = ph_now; }
 #define PH_PARAMS , long long (&ph_t)[16], long long &ph_last
 #define PH_ARGS , ph_t, ph_last
+#ifdef G1MPC_FACTOR_CLOCKS      // counters 8..12 split the factor stage instead of the solve
+#define PHF(i) PH(i)
+#define PHS(i)
 #else
+#define PHF(i)
+#define PHS(i) PH(i)
+#endif
+#else
+#define PHF(i)
+#define PHS(i)
 #define PH_DECL
 #define PH(i)
 #define PH_PARAMS
@@ -83,7 +92,8 @@ struct WLay {
     static constexpr int oE = ev(oSt + (NCN + 1) / 2);   // [N*12]  free-response error A^(k+1) x0 - xref_k (mpc.cpp:369-375)
     static constexpr int SST = 22;                  // S_k packed (21) + pad
     static constexpr int oS = oE + N * 12;          // [N*SST]
-    // per stage: G2 = Gamma - Phi^T Psi | Psi | P12 of P_{k+1} | Gamma | P22 of P_{k+1} (packed 21 + pad)
+    // per stage: G2 = Gamma - Phi^T Psi | Psi | P12 of P_{k+1} | Gamma | P22 of P_{k+1} (packed 21 + pad);
+    // G2, Psi and Gamma are stored by columns (the factor lanes own columns), P12 by rows
     // (Gamma is kept beside G2: rebuilding it as G2 + Phi^T Psi cancels badly on long horizons -- measured at N = 40)
     static constexpr int sG2 = 0, sPsi = 36, sP12 = 72, sGam = 108, sP22 = 144, STG = 166;
     static constexpr int oRic = oS + N * SST;       // [N*STG] ; after the corrector solve: ds | dl  (needs 12 NCN <= STG N)
@@ -130,11 +140,14 @@ __device__ __forceinline__ void ldl6(double (&a)[21], double (&dinv)[6], int &ne
         double col[6];
 #pragma unroll
         for (int i = j + 1; i < 6; i++) col[i] = a[tri(i, j)];
+        // the next pivot is the dependent chain: its update waits for r with one operation (the square is formed
+        // while the reciprocal runs), everything else has a whole reciprocal of slack
+        if (j < 5) a[tri(j + 1, j + 1)] = fma(-(col[j + 1] * col[j + 1]), r, a[tri(j + 1, j + 1)]);
 #pragma unroll
         for (int i = j + 1; i < 6; i++) {
             const double lij = col[i] * r;
 #pragma unroll
-            for (int c = j + 1; c <= i; c++) a[tri(i, c)] = fma(-lij, col[c], a[tri(i, c)]);
+            for (int c = j + 1; c <= i; c++) if (!(i == j + 1 && c == j + 1)) a[tri(i, c)] = fma(-lij, col[c], a[tri(i, c)]);
             a[tri(i, j)] = lij;
         }
     }
@@ -383,7 +396,7 @@ __device__ __forceinline__ void assemble_stage(double *sm, const DevParams &P, c
 // A11 = P11 - P12 S A21.
 // P11 stays in the registers of the six A21 lanes (one column each).  Returns false if a minor was not positive.
 template <int N, int NC>
-__device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, const StageC &C, int lane)
+__device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, const StageC &C, int lane PH_PARAMS)
 {
     using L_ = WLay<N, NC>;
     double *Ex = sm + L_::oEx;
@@ -396,9 +409,6 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
 #pragma unroll
     for (int i = 0; i < 6; i++) if (cb == i) { sq1 = P.scale * P.q[i]; sq2 = P.scale * P.q[6 + i]; }
     asm volatile("" : "+d"(sq1), "+d"(sq2));                    // keep them in registers (no re-derivation per stage)
-    int oc[6];                                                  // stage-slot offsets of this lane's column of [ I | P21 | P22 ]
-#pragma unroll
-    for (int i = 0; i < 6; i++) oc[i] = grp == 1 ? L_::sP12 + 6 * cb + i : L_::sP22 + trs(i, cb);   // (group 0: loaded, not used)
     // P_N = s Q
     {
         double *St = sm + L_::oRic + (N - 1) * L_::STG;
@@ -411,6 +421,13 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
             St[(e < 36 ? L_::sP12 : L_::sP22 - 36) + e] = v;
         }
     }
+    const double m1 = grp == 1 ? 1.0 : 0.0, e1 = 1.0 - m1;
+    const bool st2 = act && grp == 2;
+    // stage-slot offsets of the two column stores shared by groups 0 and 1 (group 1 writes into the slot of stage k-1 and
+    // into the exchange buffer)
+    const int offr = grp == 0 ? L_::sG2 + 6 * cb : L_::sP12 - L_::STG + 6 * cb;
+    double *pcol = grp == 0 ? sm + L_::oRic + (N - 1) * L_::STG + L_::sGam + 6 * cb : Ex + 6 * cb;
+    const int dcol = grp == 0 ? L_::STG : 0;
     double p11[6];                                              // column cb of P11 (meaningful in group 1)
 #pragma unroll
     for (int i = 0; i < 6; i++) p11[i] = i == cb ? sq1 : 0.0;
@@ -424,12 +441,9 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
         // LDL' (T spans the full range of the barrier weights: the closed form stalls the interior point there --
         // measured at N = 40, nc = 8; tests/test_ipm_model_cpu.py keeps the experiment)
         double c[6];                                            // issued first: nothing below depends on it until the mat-vec
+        ld6(St + L_::sP12 + 6 * cb, c);                         // column cb of P21 = row cb of P12 (group 1)
 #pragma unroll
-        for (int i = 0; i < 6; i++) c[i] = St[oc[i]];
-        if (grp == 0) {
-#pragma unroll
-            for (int i = 0; i < 6; i++) c[i] = i == cb ? 1.0 : 0.0;
-        }
+        for (int i = 0; i < 6; i++) c[i] = fma(m1, c[i], i == cb ? e1 : 0.0);      // groups 0, 2: unit vector (no branch)
         double Pi[21], T[21], dT[6];
         {
             double ld[22];
@@ -441,16 +455,23 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
 #pragma unroll
             for (int e = 0; e < 21; e++) T[e] = Pi[e] + ld[e];
         }
+        PHF(8)
         ldl6(T, dT, neg);
-        // column pipeline: Gamma [ I | P21 | P22 ] -> Gamma | A21 | A22,  Gamma = T^-1 Pi
+        PHF(9)
+        // column pipeline: Gamma [ I | P21 | P22 ] -> Gamma | A21 | A22,  Gamma = T^-1 Pi  (A22 = T^-1: Pi P22 = I exactly)
         double col[6];
         {
             symmv6(Pi, c, col);
+            if (grp == 2) {
+#pragma unroll
+                for (int i = 0; i < 6; i++) col[i] = c[i];
+            }
             fsub6(T, col);
 #pragma unroll
             for (int i = 0; i < 6; i++) col[i] *= dT[i];
             bsub6(T, col);
         }
+        PHF(10)
         double wv[6];                                           // P12 S col  (groups 0 and 1)
         {
             double v[6], ld[22], row[6];
@@ -459,45 +480,46 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
 #pragma unroll
             for (int i = 0; i < 6; i++) { ld6(St + L_::sP12 + 6 * i, row); wv[i] = dot6(row, v); }
         }
-        double *Sn = St - L_::STG;                              // slot of stage k-1: receives P12 | P22 of P_k
-        if (grp == 0) {
-            double pw[6];
-            phiT6(C.F, wv, pw);
+        PHF(11)
+        // One code path for groups 0 and 1 (no divergence), x = [group 1] P11[:,cb] - wv:
+        //   group 0: Psi[:,cb] = wv, G2[:,cb] = Gamma[:,cb] - Phi' wv = col + Phi' x, Gamma[:,cb] = col   (stored as columns)
+        //   group 1: A11[:,cb] = x;  row cb of the next P12 = A12[cb,:] + (A11 Phi)[cb,:] = col + Phi' x (A11 symmetric);
+        //            A21[:,cb] = col goes to the exchange buffer
+        {
+            double x[6], px[6];
 #pragma unroll
-            for (int i = 0; i < 6; i++) { St[L_::sPsi + 6 * i + cb] = wv[i]; St[L_::sG2 + 6 * i + cb] = col[i] - pw[i]; St[L_::sGam + 6 * i + cb] = col[i]; }
-        } else if (grp == 1 && k > 0) {
-            // A11[:,cb] = P11[:,cb] - P12 S A21[:,cb];  row cb of the next P12 = A12[cb,:] + (A11 Phi)[cb,:] (A11 symmetric)
-            double a11[6], pa[6];
-#pragma unroll
-            for (int i = 0; i < 6; i++) a11[i] = p11[i] - wv[i];
-            phiT6(C.F, a11, pa);
+            for (int i = 0; i < 6; i++) x[i] = fma(m1, p11[i], -wv[i]);
+            phiT6(C.F, x, px);
 #pragma unroll
             for (int i = 0; i < 6; i++) {
-                pa[i] += col[i];
-                p11[i] = a11[i] + (i == cb ? sq1 : 0.0);
+                px[i] += col[i];
+                p11[i] = i == cb ? x[i] + sq1 : x[i];           // (finite junk outside group 1, multiplied by m1 = 0)
             }
-            st6(Ex + 6 * cb, col);                              // A21 column cb, contiguous
-            st6(Sn + L_::sP12 + 6 * cb, pa);
+            const bool st01 = lane < 12 && (grp == 0 || k > 0);
+            if (st01) { st6(St + offr, px); st6(pcol, col); }
+            pcol -= dcol;
+            if (grp == 0) st6(St + L_::sPsi + 6 * cb, wv);
         }
+        double *Sn = St - L_::STG;                              // slot of stage k-1: receives P12 | P22 of P_k
         __syncwarp();
+        PHF(12)
         if (k > 0) {
             // P22 of P_k, column cb = s Q2 + A22 + Phi' M12 + A21 Phi      (group 2)
             // (every lane runs the arithmetic -- no divergence; only group 2 holds A22 in `col` and stores)
-            {
-                double m12[6], pm[6], ca[6], cbv[6];
+            double m12[6], pm[6], ca[6], cbv[6];
 #pragma unroll
-                for (int i = 0; i < 6; i++) m12[i] = Sn[L_::sP12 + 6 * i + cb];
-                ld6(Ex + 6 * ja, ca); ld6(Ex + 6 * jb, cbv);
-                phiT6(C.F, m12, pm);
-                const bool st2 = act && grp == 2;
+            for (int i = 0; i < 6; i++) m12[i] = Sn[L_::sP12 + 6 * i + cb];
+            ld6(Ex + 6 * ja, ca); ld6(Ex + 6 * jb, cbv);
+            phiT6(C.F, m12, pm);
+            double *dst = Sn + L_::sP22 + cb;                   // lower triangle: entry (i, cb), i >= cb, at tri(i,0) + cb
 #pragma unroll
-                for (int i = 0; i < 6; i++) {
-                    const double val = fma(ga, ca[i], fma(gb, cbv[i], col[i] + pm[i])) + (i == cb ? sq2 : 0.0);
-                    if (st2 && i >= cb) Sn[oc[i]] = val;
-                }
+            for (int i = 0; i < 6; i++) {
+                const double val = fma(ga, ca[i], fma(gb, cbv[i], col[i] + pm[i])) + (i == cb ? sq2 : 0.0);
+                if (st2 && i >= cb) dst[tri(i, 0)] = val;
             }
             __syncwarp();
         }
+        PHF(3)
     }
     return neg >= 0;
 }
@@ -518,15 +540,8 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
         const double *St = sm + L_::oRic + k * L_::STG;
         double t[6], gt[6], c1[6], c2[6], pc1[6], row[6], p22[22];
         ld6(vA + 6 * k, t);
-        ld6(St + L_::sGam, row);
 #pragma unroll
-        for (int j = 0; j < 6; j++) gt[j] = row[j] * t[0];
-#pragma unroll
-        for (int i = 1; i < 6; i++) {
-            ld6(St + L_::sGam + 6 * i, row);
-#pragma unroll
-            for (int j = 0; j < 6; j++) gt[j] = fma(row[j], t[i], gt[j]);
-        }
+        for (int j = 0; j < 6; j++) { ld6(St + L_::sGam + 6 * j, row); gt[j] = dot6(row, t); }      // (columns of Gamma are stored)
 #pragma unroll
         for (int i = 0; i < 6; i++) { ld6(St + L_::sP12 + 6 * i, row); c1[i] = dot6(row, gt); }
         ld22(St + L_::sP22, p22);
@@ -536,7 +551,7 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
         for (int i = 0; i < 6; i++) c2[i] += pc1[i];
         st6(vA + 6 * k, gt); st6(vB + 6 * k, c1); st6(vC + 6 * k, c2);
     }
-    PH(8)
+    PHS(8)
     const int r6 = lane % 6;
     if (lane < 6) { vD[6 * (N - 1) + r6] = 0.0; pbuf[6 * (N & 1) + r6] = 0.0; }     // zero terminal co-state
     __syncwarp();
@@ -550,12 +565,14 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
     //      constant term) are issued one step ahead, before the barrier.
     const bool lo6 = lane < 6;
     {
-        const double *rowp = sm + L_::oRic + (lo6 ? L_::sPsi : L_::sG2) + 6 * r6;      // + k STG
+        const double *rowp = sm + L_::oRic + (lo6 ? L_::sPsi : L_::sG2) + r6;          // row r6 of column storage: + k STG + 6 j
         const double *cp = (lo6 ? vB : vC) + r6;                                        // + 6 k
         double *dstp = lo6 ? pbuf + r6 : vD + r6 - 6;                                   // p1 -> pbuf[6 (k&1)], p2 -> vD[6 (k-1)]
         const bool wr = lane < 12;
         double pown = 0.0, row[6], cadd;
-        ld6(rowp + (N - 1) * L_::STG, row); cadd = cp[6 * (N - 1)];
+#pragma unroll
+        for (int j = 0; j < 6; j++) row[j] = rowp[(N - 1) * L_::STG + 6 * j];
+        cadd = cp[6 * (N - 1)];
 #pragma unroll 2
         for (int k = N - 1; k >= 0; k--) {
             double p2[6];
@@ -569,18 +586,26 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
             asm volatile("" : "+d"(acc), "+d"(b_lo), "+d"(b_hi));
             pown = lo6 ? b_lo - acc : b_hi + acc;
             if (wr && (lo6 || k > 0)) dstp[lo6 ? 6 * (k & 1) : 6 * k] = pown;
-            if (k > 0) { ld6(rowp + (k - 1) * L_::STG, row); cadd = cp[6 * (k - 1)]; }
+            if (k > 0) {
+#pragma unroll
+                for (int j = 0; j < 6; j++) row[j] = rowp[(k - 1) * L_::STG + 6 * j];
+                cadd = cp[6 * (k - 1)];
+            }
             __syncwarp();
         }
     }
-    PH(9)
+    PHS(9)
     // ---- b_k = gt_k - S_k Gamma p2   (lane = stage)
     for (int k = lane; k < N; k += 32) {
         const double *St = sm + L_::oRic + k * L_::STG;
         double p2[6], g[6], row[6], sk[22], sg[6], b[6];
         ld6(vD + 6 * k, p2);
 #pragma unroll
-        for (int i = 0; i < 6; i++) { ld6(St + L_::sGam + 6 * i, row); g[i] = dot6(row, p2); }
+        for (int j = 0; j < 6; j++) {                   // Gamma p2 from the stored columns
+            ld6(St + L_::sGam + 6 * j, row);
+#pragma unroll
+            for (int i = 0; i < 6; i++) g[i] = j == 0 ? row[i] * p2[0] : fma(row[i], p2[j], g[i]);
+        }
         ld22(sm + L_::oS + L_::SST * k, sk);
         symmv6(sk, g, sg);
         ld6(vA + 6 * k, b);
@@ -590,16 +615,15 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
     }
     if (lane < 6) vB[r6] = 0.0;                     // y1 after stage 0 (y2 after stage 0 is b_0, already in vA)
     __syncwarp();
-    PH(10)
+    PHS(10)
     // ---- forward sweep:  y1 <- y1 + Phi y2 ;  y2 <- b + G2^T y2 - Psi^T y1   (old values on the right)
     {
-        const double *g2p = sm + L_::oRic + L_::sG2 + r6, *psp = sm + L_::oRic + L_::sPsi + r6;   // column r6: + k STG + 6 i
+        const double *g2p = sm + L_::oRic + L_::sG2 + 6 * r6, *psp = sm + L_::oRic + L_::sPsi + 6 * r6;   // column r6: + k STG
         double *dstp = (lo6 ? vB : vA) + r6;                                                      // + 6 k
         const bool wr = lane < 12;
         double yown = lo6 ? 0.0 : vA[r6];
         double g2c[6], psc[6], bk;
-#pragma unroll
-        for (int i = 0; i < 6; i++) { g2c[i] = g2p[L_::STG + 6 * i]; psc[i] = psp[L_::STG + 6 * i]; }
+        ld6(g2p + L_::STG, g2c); ld6(psp + L_::STG, psc);
         bk = vA[6 + r6];
 #pragma unroll 2
         for (int k = 1; k < N; k++) {
@@ -615,15 +639,11 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
             asm volatile("" : "+d"(v_lo), "+d"(v_hi));          // both forms in every lane: no divergent split (see above)
             yown = lo6 ? v_lo : v_hi;
             if (wr) dstp[6 * k] = yown;
-            if (k + 1 < N) {
-#pragma unroll
-                for (int i = 0; i < 6; i++) { g2c[i] = g2p[(k + 1) * L_::STG + 6 * i]; psc[i] = psp[(k + 1) * L_::STG + 6 * i]; }
-                bk = vA[6 * (k + 1) + r6];
-            }
+            if (k + 1 < N) { ld6(g2p + (k + 1) * L_::STG, g2c); ld6(psp + (k + 1) * L_::STG, psc); bk = vA[6 * (k + 1) + r6]; }
             __syncwarp();
         }
     }
-    PH(11)
+    PHS(11)
     // ---- output (lane = stage): y_k = P12^T y1 + P22 y2 + p2 ; zeta~ = Bm^T y_k
     for (int k = lane; k < N; k += 32) {
         const double *St = sm + L_::oRic + k * L_::STG;
@@ -648,7 +668,7 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
         st6(vA + 6 * k, o);
     }
     __syncwarp();
-    PH(12)
+    PHS(12)
 }
 
 
@@ -904,7 +924,7 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         assemble_stage<N, NC, true>(sm, P, C, lane);
         __syncwarp();
         PH(2)
-        if (!factor_stages<N, NC>(sm, P, C, lane)) { status = G1MPC_NUMERICAL; break; }
+        if (!factor_stages<N, NC>(sm, P, C, lane PH_ARGS)) { status = G1MPC_NUMERICAL; break; }
         PH(3)
         // (4) predictor.  With x = ds/s:  dl = -lam (1 + x), and the largest feasible step is
         //     1 / max_i max(-x_i, 1 + x_i)  -- no division per constraint.

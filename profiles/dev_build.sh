@@ -6,3 +6,4 @@ F="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -
 mkdir -p ../../gpurun_in
 /usr/local/cuda/bin/nvcc $F -Xptxas -v -o ../../gpurun_in/libdev.so g1mpc_kernels.cu 2>&1 | grep -E "error|warning|Used 2[0-9][0-9]|spill stores" | grep -v " 0 bytes spill" || true
 /usr/local/cuda/bin/nvcc $F -DG1MPC_PHASE_CLOCKS -o ../../gpurun_in/libtiming.so g1mpc_kernels.cu
+/usr/local/cuda/bin/nvcc $F -DG1MPC_PHASE_CLOCKS -DG1MPC_FACTOR_CLOCKS -o ../../gpurun_in/libftiming.so g1mpc_kernels.cu

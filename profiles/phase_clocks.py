@@ -15,6 +15,9 @@ torch.cuda.synchronize()
 ph = info["y"][:, :16].cpu().numpy(); it = info["iters"].cpu().numpy()
 names = ["gradient", "passA", "assemble+S", "factor", "solve: misc", "passB+B2+assemble", "passC+step", "setup/loop",
          "solve: pre", "solve: backward", "solve: b", "solve: forward", "solve: output"]
+if os.environ.get("G1MPC_B200_LIB", "").endswith("libftiming.so"):      # -DG1MPC_FACTOR_CLOCKS: 8..12 split the factor stage
+    names[3] = "factor: P22 update"; names[4] = "solves (both)"
+    names[8:13] = ["factor: loads+inv6", "factor: ldl6", "factor: columns", "factor: P12 S col", "factor: stores"]
 print("B =", B, "iters", it[:8], "total cycles (problem 0): %d" % ph[0].sum())
 for i, n in enumerate(names):
     print("  %-20s %9.0f cycles/iter  %5.1f%%" % (n, (ph[:, i] / it).mean(), 100 * ph[:, i].sum() / ph.sum()))
