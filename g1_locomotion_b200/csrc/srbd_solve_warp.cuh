@@ -956,13 +956,18 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         double sig = g_aff * frcp(gap);
         sig = sig * sig * sig;
         const double sigma_gap = sig * gap;
+        // Safeguard: a predictor blocked almost at once (a_aff < 0.3) carries a second-order term that is far off
+        // (the affine step wants to go 1/a_aff times beyond the boundary); taken in full it can lock the iteration into a
+        // two-cycle (2 of 131,072 random problems of config 5 ran into max_iter that way).  Scaled by a_aff / 0.3 there;
+        // no effect on iterations with a_aff >= 0.3 (tests/test_ipm_model_cpu.py keeps the two problems).
+        const double w2 = fmin(1.0, a_aff * (1.0 / 0.3));
         // (5) corrector right-hand side: t = Dblk^-1 (-grad f + Cb'q),  q = (ds dl - sigma mu)/s
         for (int i = lane; i < n_stance; i += 32) {
             const int c = stIdx[i];
             const double *Ds = Dst + 9 * c, *l6 = lam + 6 * c;
             double q6[6], Di[6];
 #pragma unroll
-            for (int j = 0; j < 6; j++) q6[j] = (prod[6 * c + j] - sigma_gap) * Ds[j];
+            for (int j = 0; j < 6; j++) q6[j] = fma(w2, prod[6 * c + j], -sigma_gap) * Ds[j];
             const double r0 = -gf[3 * c] + (q6[0] - q6[1]);
             const double r1 = -gf[3 * c + 1] + (q6[2] - q6[3]);
             const double r2 = -gf[3 * c + 2] + (-mu * (q6[0] + q6[1] + q6[2] + q6[3]) + q6[4] - q6[5]);
@@ -1066,7 +1071,8 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         for (int c = lane; c < NCN; c += 32) {
             const double fx = u[3 * c], fy = u[3 * c + 1], fz = u[3 * c + 2];
             const double cf = cfl[c], lo = P.fz_min * cf, hi = fmax(P.fz_max * cf, lo);
-            pv = fmax(pv, fmax(fabs(fx) - mu * fz, fabs(fy) - mu * fz));
+            const double lim = __dmul_rn(mu, fz);                  // the rounded product the clamp above used (no FMA contraction)
+            pv = fmax(pv, fmax(fabs(fx) - lim, fabs(fy) - lim));
             pv = fmax(pv, fmax(fz - hi, lo - fz));
         }
         obj = wsum(obj); pv = wmax(pv);

@@ -232,7 +232,7 @@ def solve_ipm(prob, gap_tol=1e-10, max_iter=40, linear="riccati"):
         for pas in range(2):
             q = np.zeros_like(s)
             if pas == 1:
-                q[st] = (ds[st] * dl[st] - sigma_gap) / s[st]
+                q[st] = (min(1.0, a_aff / 0.3) * ds[st] * dl[st] - sigma_gap) / s[st]      # (safeguard: see the kernel)
             rhs = np.zeros_like(u); tw = np.zeros((N, 6))
             for k in range(N):
                 for j in range(nc):

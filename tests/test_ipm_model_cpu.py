@@ -61,3 +61,23 @@ def test_interior_point_model_reaches_exact_minimiser(orc, pname, over, gen):
         u, it, gap = solve_ipm(Problem(preset, *args), linear="stage")
         assert gap <= 1e-10 and it <= 25
         assert np.abs(u.ravel() - xs).max() <= GRF_TOL
+
+
+def _two_cycle_problems():
+    """Two of the 131,072 random problems of one config-5 shard (rank 5 of 8, seed 18, generated on the GPU) on which
+    the unsafeguarded Mehrotra iteration falls into a two-cycle (gap 8 <-> 18) and runs into max_iter."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "ipm_two_cycle_problems.npz"))
+    return [[z[k][b] for k in ("x0", "x_ref", "contact", "c_horizon", "p_com")] for b in range(len(z["shard_index"]))]
+
+
+def test_corrector_safeguard_breaks_the_two_cycle(orc):
+    preset = presets.get_preset("cpp_node")
+    p = orc.params_from_dict(preset)
+    for args in _two_cycle_problems():
+        m = orc.build(p, *args)
+        xs, _, cert = orc.qp_exact(p, m["H"], m["g"], args[2])
+        assert cert["rc"] == 0
+        u, it, gap = solve_ipm(Problem(preset, *args), linear="dense")
+        assert gap <= 1e-10 and it <= 25, (it, gap)
+        assert np.abs(u.ravel() - xs).max() <= GRF_TOL

@@ -311,3 +311,23 @@ def test_config5_full_size_shard_of_2pow20():
     assert torch.all(f[ct == 0] == 0)
     assert torch.equal(payload[:, :12], u[:, 0]) and torch.equal(payload[:, 12:], x[:, 1])
     assert float(info["resid"][:, 0].max()) <= 1e-10 and float(info["resid"][:, 2].max()) == 0.0
+
+
+def test_two_cycle_problems_of_config5_are_solved(orc):
+    """Regression: two random problems of a config-5 shard on which the plain predictor-corrector cycles (see
+    tests/test_ipm_model_cpu.py); with the safeguard they converge like the rest and match the exact minimiser."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "ipm_two_cycle_problems.npz"))
+    preset = presets.get_preset("cpp_node")
+    p = orc.params_from_dict(preset)
+    arrs = [z[k] for k in ("x0", "x_ref", "contact", "c_horizon", "p_com")]
+    s = _solver(preset)
+    ins = _dev(arrs)
+    u, x, info = s.update_batch(*ins, x_current=ins[0])
+    assert int((info["status"] != 0).sum()) == 0
+    assert int(info["iters"].max()) <= 25
+    for b in range(arrs[0].shape[0]):
+        m = orc.build(p, *[a[b] for a in arrs])
+        xs, _, cert = orc.qp_exact(p, m["H"], m["g"], arrs[2][b])
+        assert cert["rc"] == 0
+        assert np.abs(u[b].cpu().numpy().ravel() - xs).max() <= GRF_TOL
