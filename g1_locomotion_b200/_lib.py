@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("G1MPC_B200_LIB") or os.path.join(_HERE, "libg1mpc_b200.so")   # override: A/B runs of two builds
 _lib = None
 
-EXPORTS = ["g1mpc_create", "g1mpc_destroy", "g1mpc_solve_batch", "g1mpc_emit_qp_batch", "g1mpc_update_host",
+EXPORTS = ["g1mpc_create", "g1mpc_destroy", "g1mpc_solve_batch", "g1mpc_emit_qp_batch", "g1mpc_update_host", "g1mpc_update_host_begin", "g1mpc_update_host_end",
            "g1mpc_walk_inputs_batch", "g1mpc_wbid_refs_batch", "g1mpc_closed_loop_batch", "g1mpc_kernel_info", "g1mpc_fp64_peak_tflops", "g1mpc_last_error", "g1mpc_abi_version"]
 
 
@@ -55,6 +55,10 @@ def load():
     lib.g1mpc_emit_qp_batch.restype = C.c_int
     lib.g1mpc_update_host.argtypes = [vp, i64, dp, dp, dp, dp, dp, dp, C.c_int, dp, dp, i32p, i32p, dp]
     lib.g1mpc_update_host.restype = C.c_int
+    lib.g1mpc_update_host_begin.argtypes = [vp, C.c_int, i64, dp, dp, dp, dp, dp, dp, C.c_int, dp, dp, i32p, i32p, dp]
+    lib.g1mpc_update_host_begin.restype = C.c_int
+    lib.g1mpc_update_host_end.argtypes = [vp, C.c_int]
+    lib.g1mpc_update_host_end.restype = C.c_int
     lib.g1mpc_walk_inputs_batch.argtypes = [vp, i64] + [dp] * 9 + [vp]
     lib.g1mpc_walk_inputs_batch.restype = C.c_int
     lib.g1mpc_wbid_refs_batch.argtypes = [vp, i64, dp, dp, dp, C.c_double, dp, vp]

@@ -313,11 +313,19 @@ struct g1mpc_handle {
     const KernelEntry *kernel;
     int warps_per_block = 1;
     int ctas_per_sm = 0;
-    // host-API staging: kPipe chunk streams
-    static constexpr int kPipe = 4;
-    cudaStream_t pipe[kPipe] = {nullptr, nullptr, nullptr, nullptr};
-    char *h_stage = nullptr, *d_stage = nullptr;
-    size_t stage_bytes = 0;
+    // host-API staging: kSlots batches in flight, each cut into up to kPipe chunks with a stream of their own
+    static constexpr int kPipe = 4, kSlots = G1MPC_HOST_SLOTS;
+    struct Off { size_t x0, xr, ct, ch, pc, xc, xo, u, res, st; };
+    struct Slot {
+        cudaStream_t pipe[kPipe] = {nullptr, nullptr, nullptr, nullptr};
+        char *h_stage = nullptr, *d_stage = nullptr;
+        size_t stage_bytes = 0, stride = 0, cap = 0, nbs[kPipe] = {0, 0, 0, 0};
+        Off off[kPipe];
+        int nchunk = 0;
+        bool pending = false, staged_out = false;
+        double *u_opt = nullptr, *x_opt = nullptr, *resid = nullptr;     // caller's output buffers (unpacked in _end)
+        int32_t *status = nullptr, *iters = nullptr;
+    } slot[kSlots];
     // closed-loop workspace
     char *d_loop = nullptr;
     size_t loop_bytes = 0;
@@ -370,10 +378,11 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
     if (e != cudaSuccess) { g_last_error = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
     cudaFuncSetAttribute((const void *)srbd_mpc_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->ctas_per_sm, (const void *)ke->fn, kWarpThreads * h->warps_per_block, ke->smem * h->warps_per_block);
-    for (int i = 0; i < g1mpc_handle::kPipe; i++) {
-        e = cudaStreamCreateWithFlags(&h->pipe[i], cudaStreamNonBlocking);
-        if (e != cudaSuccess) { g_last_error = "cudaStreamCreate failed"; g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
-    }
+    for (int sl = 0; sl < g1mpc_handle::kSlots; sl++)
+        for (int i = 0; i < g1mpc_handle::kPipe; i++) {
+            e = cudaStreamCreateWithFlags(&h->slot[sl].pipe[i], cudaStreamNonBlocking);
+            if (e != cudaSuccess) { g_last_error = "cudaStreamCreate failed"; g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
+        }
     *out = h;
     return G1MPC_OK;
 }
@@ -382,10 +391,13 @@ void g1mpc_destroy(g1mpc_handle *h)
 {
     if (!h) return;
     cudaSetDevice(h->device);
-    if (h->h_stage) cudaFreeHost(h->h_stage);
-    if (h->d_stage) cudaFree(h->d_stage);
+    for (int sl = 0; sl < g1mpc_handle::kSlots; sl++) {
+        g1mpc_handle::Slot &S = h->slot[sl];
+        for (int i = 0; i < g1mpc_handle::kPipe; i++) if (S.pipe[i]) { cudaStreamSynchronize(S.pipe[i]); cudaStreamDestroy(S.pipe[i]); }
+        if (S.h_stage) cudaFreeHost(S.h_stage);
+        if (S.d_stage) cudaFree(S.d_stage);
+    }
     if (h->d_loop) cudaFree(h->d_loop);
-    for (int i = 0; i < g1mpc_handle::kPipe; i++) if (h->pipe[i]) cudaStreamDestroy(h->pipe[i]);
     delete h;
 }
 
@@ -435,78 +447,138 @@ int g1mpc_emit_qp_batch(g1mpc_handle *h, int64_t B, const double *x0, const doub
     return G1MPC_OK;
 }
 
-int g1mpc_update_host(g1mpc_handle *h, int64_t B, const double *x0, const double *x_ref, const double *contact,
-                      const double *c_horizon, const double *p_com, const double *x_current, int one_rollout,
-                      double *u_opt, double *x_opt, int32_t *status, int32_t *iters, double *resid)
+// true if cudaMemcpyAsync from/to p is a real asynchronous DMA (page-locked host memory: cudaMallocHost / cudaHostRegister)
+static bool host_pinned(const void *p)
 {
-    if (!h || B < 0 || (B > 0 && (!x0 || !x_ref || !contact || !c_horizon || !p_com || !u_opt || !x_opt))) {
-        g_last_error = "g1mpc_update_host: null argument"; return G1MPC_ERR_INVALID_ARGUMENT;
+    if (!p) return true;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+}
+
+int g1mpc_update_host_begin(g1mpc_handle *h, int slot, int64_t B, const double *x0, const double *x_ref, const double *contact,
+                            const double *c_horizon, const double *p_com, const double *x_current, int one_rollout,
+                            double *u_opt, double *x_opt, int32_t *status, int32_t *iters, double *resid)
+{
+    if (!h || slot < 0 || slot >= g1mpc_handle::kSlots || B < 0 ||
+        (B > 0 && (!x0 || !x_ref || !contact || !c_horizon || !p_com || !u_opt || !x_opt))) {
+        g_last_error = "g1mpc_update_host: null argument or slot out of range"; return G1MPC_ERR_INVALID_ARGUMENT;
     }
-    if (B == 0) return G1MPC_OK;
+    g1mpc_handle::Slot &S = h->slot[slot];
+    if (S.pending) { g_last_error = "g1mpc_update_host_begin: slot still in flight (call g1mpc_update_host_end first)"; return G1MPC_ERR_INVALID_ARGUMENT; }
+    S.nchunk = 0;
+    if (B == 0) { S.pending = true; return G1MPC_OK; }
     CUDA_TRY(cudaSetDevice(h->device));
     const size_t N = h->params.horizon, NC = h->params.num_contacts, NU = 3 * NC;
-    // The batch is cut into up to kPipe chunks, each with its own stream: pack chunk c+1 into pinned memory while chunk
-    // c is copied and solved, unpack chunk c while later chunks are still in flight.  One H2D and one D2H per chunk:
-    //   chunk block = x0 | x_ref | contact | c_horizon | p_com | x_current | x_opt (in/out) | u_opt | resid | status | iters
+    // The batch is cut into up to kPipe chunks, each with its own stream, so that the copies of one chunk overlap the
+    // solve of another.  Device block of a chunk:
+    //   x0 | x_ref | contact | c_horizon | p_com | x_current | x_opt (in/out) | u_opt | resid | status | iters
+    // Caller buffers that are page-locked are copied straight from / to where they lie (one DMA per array and chunk);
+    // pageable ones go through the slot's pinned staging block (pack -> one H2D, one D2H -> unpack in _end).
     // x_opt only travels host->device when the reference would leave some of its rows untouched (no x_current: row 0;
     // one_rollout: rows 2..; mpc.cpp:427-446).
     const bool xopt_in = (x_current == nullptr) || one_rollout;
+    const bool direct_in = host_pinned(x0) && host_pinned(x_ref) && host_pinned(contact) && host_pinned(c_horizon) &&
+                           host_pinned(p_com) && host_pinned(x_current) && (!xopt_in || host_pinned(x_opt));
+    const bool direct_out = host_pinned(u_opt) && host_pinned(x_opt) && host_pinned(status) && host_pinned(iters) && host_pinned(resid);
     const int nchunk = B >= 512 ? g1mpc_handle::kPipe : (B >= 128 ? 2 : 1);
     const size_t cap = ((size_t)B + nchunk - 1) / nchunk;
     const size_t d_in = NS + N * NS + N * NC + N * NU + N * 3 + NS, d_xo = N * NS, d_out = N * NU + 4;   // doubles per problem
     const size_t stride = ((sizeof(double) * (d_in + d_xo + d_out) + 2 * sizeof(int32_t)) * cap + 255) & ~(size_t)255;
     const size_t bytes = stride * nchunk;
-    if (bytes > h->stage_bytes) {
-        if (h->h_stage) cudaFreeHost(h->h_stage);
-        if (h->d_stage) cudaFree(h->d_stage);
-        h->h_stage = nullptr; h->d_stage = nullptr; h->stage_bytes = 0;
-        CUDA_TRY(cudaMallocHost((void **)&h->h_stage, bytes));
-        CUDA_TRY(cudaMalloc((void **)&h->d_stage, bytes));
-        h->stage_bytes = bytes;
+    if (bytes > S.stage_bytes) {
+        if (S.h_stage) cudaFreeHost(S.h_stage);
+        if (S.d_stage) cudaFree(S.d_stage);
+        S.h_stage = nullptr; S.d_stage = nullptr; S.stage_bytes = 0;
+        CUDA_TRY(cudaMallocHost((void **)&S.h_stage, bytes));
+        CUDA_TRY(cudaMalloc((void **)&S.d_stage, bytes));
+        S.stage_bytes = bytes;
     }
-    struct Off { size_t x0, xr, ct, ch, pc, xc, xo, u, res, st; } o[g1mpc_handle::kPipe];
-    size_t nbs[g1mpc_handle::kPipe];
+    S.stride = stride; S.cap = cap; S.staged_out = !direct_out;
+    S.u_opt = u_opt; S.x_opt = x_opt; S.resid = resid; S.status = status; S.iters = iters;
+    const size_t D = sizeof(double);
     for (int c = 0; c < nchunk; c++) {
         const size_t b0 = cap * c, nb = b0 < (size_t)B ? (((size_t)B - b0) < cap ? ((size_t)B - b0) : cap) : 0;
-        nbs[c] = nb;
+        S.nbs[c] = nb;
+        S.nchunk = c + 1;
         if (nb == 0) continue;
-        double *hs = (double *)(h->h_stage + stride * c), *ds = (double *)(h->d_stage + stride * c);
-        Off &f = o[c];
+        double *hs = (double *)(S.h_stage + stride * c), *ds = (double *)(S.d_stage + stride * c);
+        g1mpc_handle::Off &f = S.off[c];
         size_t q = 0;
-        f.x0 = q; memcpy(hs + q, x0 + b0 * NS, sizeof(double) * nb * NS); q += nb * NS;
-        f.xr = q; memcpy(hs + q, x_ref + b0 * N * NS, sizeof(double) * nb * N * NS); q += nb * N * NS;
-        f.ct = q; memcpy(hs + q, contact + b0 * N * NC, sizeof(double) * nb * N * NC); q += nb * N * NC;
-        f.ch = q; memcpy(hs + q, c_horizon + b0 * N * NU, sizeof(double) * nb * N * NU); q += nb * N * NU;
-        f.pc = q; memcpy(hs + q, p_com + b0 * N * 3, sizeof(double) * nb * N * 3); q += nb * N * 3;
-        f.xc = q; if (x_current) memcpy(hs + q, x_current + b0 * NS, sizeof(double) * nb * NS); q += nb * NS;
-        f.xo = q; if (xopt_in) memcpy(hs + q, x_opt + b0 * N * NS, sizeof(double) * nb * N * NS); q += nb * N * NS;
-        f.u = q; q += nb * N * NU;
-        f.res = q; q += nb * 4;
-        f.st = q;                                              // int32 status[nb] | iters[nb]
-        cudaStream_t sp = h->pipe[c];
-        CUDA_TRY(cudaMemcpyAsync(ds, hs, sizeof(double) * (xopt_in ? f.u : f.xo), cudaMemcpyHostToDevice, sp));
+        f.x0 = q; q += nb * NS;  f.xr = q; q += nb * N * NS;  f.ct = q; q += nb * N * NC;  f.ch = q; q += nb * N * NU;
+        f.pc = q; q += nb * N * 3;  f.xc = q; q += nb * NS;  f.xo = q; q += nb * N * NS;
+        f.u = q; q += nb * N * NU;  f.res = q; q += nb * 4;  f.st = q;      // int32 status[nb] | iters[nb]
+        cudaStream_t sp = S.pipe[c];
+        if (direct_in) {
+            CUDA_TRY(cudaMemcpyAsync(ds + f.x0, x0 + b0 * NS, D * nb * NS, cudaMemcpyHostToDevice, sp));
+            CUDA_TRY(cudaMemcpyAsync(ds + f.xr, x_ref + b0 * N * NS, D * nb * N * NS, cudaMemcpyHostToDevice, sp));
+            CUDA_TRY(cudaMemcpyAsync(ds + f.ct, contact + b0 * N * NC, D * nb * N * NC, cudaMemcpyHostToDevice, sp));
+            CUDA_TRY(cudaMemcpyAsync(ds + f.ch, c_horizon + b0 * N * NU, D * nb * N * NU, cudaMemcpyHostToDevice, sp));
+            CUDA_TRY(cudaMemcpyAsync(ds + f.pc, p_com + b0 * N * 3, D * nb * N * 3, cudaMemcpyHostToDevice, sp));
+            if (x_current) CUDA_TRY(cudaMemcpyAsync(ds + f.xc, x_current + b0 * NS, D * nb * NS, cudaMemcpyHostToDevice, sp));
+            if (xopt_in) CUDA_TRY(cudaMemcpyAsync(ds + f.xo, x_opt + b0 * N * NS, D * nb * N * NS, cudaMemcpyHostToDevice, sp));
+        } else {
+            memcpy(hs + f.x0, x0 + b0 * NS, D * nb * NS);
+            memcpy(hs + f.xr, x_ref + b0 * N * NS, D * nb * N * NS);
+            memcpy(hs + f.ct, contact + b0 * N * NC, D * nb * N * NC);
+            memcpy(hs + f.ch, c_horizon + b0 * N * NU, D * nb * N * NU);
+            memcpy(hs + f.pc, p_com + b0 * N * 3, D * nb * N * 3);
+            if (x_current) memcpy(hs + f.xc, x_current + b0 * NS, D * nb * NS);
+            if (xopt_in) memcpy(hs + f.xo, x_opt + b0 * N * NS, D * nb * N * NS);
+            CUDA_TRY(cudaMemcpyAsync(ds, hs, D * (xopt_in ? f.u : f.xo), cudaMemcpyHostToDevice, sp));
+        }
         int32_t *ds_i = (int32_t *)(ds + f.st);
         int rc = g1mpc_solve_batch(h, (int64_t)nb, ds + f.x0, ds + f.xr, ds + f.ct, ds + f.ch, ds + f.pc,
                                    x_current ? ds + f.xc : nullptr, one_rollout, ds + f.u, ds + f.xo, ds_i, ds_i + nb,
                                    ds + f.res, nullptr, sp);
         if (rc) return rc;
-        CUDA_TRY(cudaMemcpyAsync(hs + f.xo, ds + f.xo, sizeof(double) * (f.st - f.xo) + sizeof(int32_t) * 2 * nb,
-                                 cudaMemcpyDeviceToHost, sp));
+        if (direct_out) {
+            CUDA_TRY(cudaMemcpyAsync(x_opt + b0 * N * NS, ds + f.xo, D * nb * N * NS, cudaMemcpyDeviceToHost, sp));
+            CUDA_TRY(cudaMemcpyAsync(u_opt + b0 * N * NU, ds + f.u, D * nb * N * NU, cudaMemcpyDeviceToHost, sp));
+            if (resid) CUDA_TRY(cudaMemcpyAsync(resid + b0 * 4, ds + f.res, D * nb * 4, cudaMemcpyDeviceToHost, sp));
+            if (status) CUDA_TRY(cudaMemcpyAsync(status + b0, ds_i, sizeof(int32_t) * nb, cudaMemcpyDeviceToHost, sp));
+            if (iters) CUDA_TRY(cudaMemcpyAsync(iters + b0, ds_i + nb, sizeof(int32_t) * nb, cudaMemcpyDeviceToHost, sp));
+        } else {
+            CUDA_TRY(cudaMemcpyAsync(hs + f.xo, ds + f.xo, D * (f.st - f.xo) + sizeof(int32_t) * 2 * nb, cudaMemcpyDeviceToHost, sp));
+        }
     }
-    for (int c = 0; c < nchunk; c++) {
-        const size_t b0 = cap * c, nb = nbs[c];
+    S.pending = true;
+    return G1MPC_OK;
+}
+
+int g1mpc_update_host_end(g1mpc_handle *h, int slot)
+{
+    if (!h || slot < 0 || slot >= g1mpc_handle::kSlots) { g_last_error = "g1mpc_update_host_end: bad handle or slot"; return G1MPC_ERR_INVALID_ARGUMENT; }
+    g1mpc_handle::Slot &S = h->slot[slot];
+    if (!S.pending) { g_last_error = "g1mpc_update_host_end: nothing in flight on this slot"; return G1MPC_ERR_INVALID_ARGUMENT; }
+    S.pending = false;
+    CUDA_TRY(cudaSetDevice(h->device));
+    const size_t N = h->params.horizon, NC = h->params.num_contacts, NU = 3 * NC;
+    for (int c = 0; c < S.nchunk; c++) {
+        const size_t b0 = S.cap * c, nb = S.nbs[c];
         if (nb == 0) continue;
-        CUDA_TRY(cudaStreamSynchronize(h->pipe[c]));
-        const double *hs = (const double *)(h->h_stage + stride * c);
-        const Off &f = o[c];
-        memcpy(u_opt + b0 * N * NU, hs + f.u, sizeof(double) * nb * N * NU);
-        memcpy(x_opt + b0 * N * NS, hs + f.xo, sizeof(double) * nb * N * NS);
-        if (resid) memcpy(resid + b0 * 4, hs + f.res, sizeof(double) * nb * 4);
+        CUDA_TRY(cudaStreamSynchronize(S.pipe[c]));
+        if (!S.staged_out) continue;
+        const double *hs = (const double *)(S.h_stage + S.stride * c);
+        const g1mpc_handle::Off &f = S.off[c];
+        memcpy(S.u_opt + b0 * N * NU, hs + f.u, sizeof(double) * nb * N * NU);
+        memcpy(S.x_opt + b0 * N * NS, hs + f.xo, sizeof(double) * nb * N * NS);
+        if (S.resid) memcpy(S.resid + b0 * 4, hs + f.res, sizeof(double) * nb * 4);
         const int32_t *hs_i = (const int32_t *)(hs + f.st);
-        if (status) memcpy(status + b0, hs_i, sizeof(int32_t) * nb);
-        if (iters) memcpy(iters + b0, hs_i + nb, sizeof(int32_t) * nb);
+        if (S.status) memcpy(S.status + b0, hs_i, sizeof(int32_t) * nb);
+        if (S.iters) memcpy(S.iters + b0, hs_i + nb, sizeof(int32_t) * nb);
     }
     return G1MPC_OK;
+}
+
+int g1mpc_update_host(g1mpc_handle *h, int64_t B, const double *x0, const double *x_ref, const double *contact,
+                      const double *c_horizon, const double *p_com, const double *x_current, int one_rollout,
+                      double *u_opt, double *x_opt, int32_t *status, int32_t *iters, double *resid)
+{
+    if (h && h->slot[0].pending) { g_last_error = "g1mpc_update_host: slot 0 is in flight (g1mpc_update_host_begin without _end)"; return G1MPC_ERR_INVALID_ARGUMENT; }
+    int rc = g1mpc_update_host_begin(h, 0, B, x0, x_ref, contact, c_horizon, p_com, x_current, one_rollout, u_opt, x_opt, status, iters, resid);
+    if (rc) { if (h) h->slot[0].pending = false; return rc; }
+    return g1mpc_update_host_end(h, 0);
 }
 
 int g1mpc_walk_inputs_batch(g1mpc_handle *h, int64_t B, const double *x0, const double *contacts_now, const double *sim_time,

@@ -43,6 +43,7 @@ class BatchedMPC:
         self.nu = 3 * self.nc
         self._lib = _lib.load()
         self._h = C.c_void_p()
+        self._pinned_keep, self._inflight = [], {}
         cp = _c_params(self.params, gap_tol, max_iter)
         _lib.check(self._lib.g1mpc_create(C.byref(cp), self.device.index, C.byref(self._h)), "g1mpc_create")
 
@@ -199,6 +200,50 @@ class BatchedMPC:
                                          int(one_rollout), p(u_opt), p(x_opt), p(status), p(iters), p(resid))
         _lib.check(rc, "g1mpc_update_host")
         return u_opt, x_opt, dict(status=status, iters=iters, resid=resid)
+
+    HOST_SLOTS = 3      # G1MPC_HOST_SLOTS
+
+    def pinned(self, *shape, dtype=np.float64):
+        """numpy array in page-locked host memory (held by a torch tensor): the host API copies such buffers by DMA
+        straight from / to where they lie instead of staging them (include/g1mpc_b200.h, g1mpc_update_host)."""
+        t = torch.empty(*shape, dtype={np.float64: torch.float64, np.int32: torch.int32}[dtype], pin_memory=True)
+        a = t.numpy()
+        self._pinned_keep.append(t)
+        return a
+
+    def update_host_begin(self, slot, x0, x_ref, contact, c_horizon, p_com, x_current=None, one_rollout=False, out=None):
+        """First half of update_host on `slot` (g1mpc_update_host_begin): enqueue and return.  The inputs must be
+        C-contiguous float64 arrays of the batch shapes and stay untouched until update_host_end(slot).  `out`: dict
+        of preallocated arrays u_opt, x_opt (in/out), status, iters, resid (e.g. from out_buffers); a fresh one if None."""
+        B, N, nc, nu = x0.shape[0], self.N, self.nc, self.nu
+        if out is None:
+            out = self.out_buffers(B, pinned=False)
+        for a, shape in ((x0, (B, NS)), (x_ref, (B, N, NS)), (contact, (B, N, nc)), (c_horizon, (B, N, nu)), (p_com, (B, N, 3)),
+                         (out["u_opt"], (B, N, nu)), (out["x_opt"], (B, N, NS)), (out["resid"], (B, 4))):
+            if a.dtype != np.float64 or not a.flags.c_contiguous or a.shape != shape:
+                raise ValueError("update_host_begin needs C-contiguous float64 arrays of the batch shapes")
+        if x_current is not None and (x_current.dtype != np.float64 or not x_current.flags.c_contiguous or x_current.shape != (B, NS)):
+            raise ValueError("update_host_begin: x_current must be a C-contiguous float64 [B,13] array")
+        p = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+        rc = self._lib.g1mpc_update_host_begin(self._h, int(slot), B, p(x0), p(x_ref), p(contact), p(c_horizon), p(p_com),
+                                               p(x_current), int(one_rollout), p(out["u_opt"]), p(out["x_opt"]),
+                                               p(out["status"]), p(out["iters"]), p(out["resid"]))
+        _lib.check(rc, "g1mpc_update_host_begin")
+        self._inflight[int(slot)] = (out, (x0, x_ref, contact, c_horizon, p_com, x_current))     # keep the buffers alive
+        return out
+
+    def update_host_end(self, slot):
+        """Second half: wait for `slot`; returns (u_opt, x_opt, info) like update_host."""
+        _lib.check(self._lib.g1mpc_update_host_end(self._h, int(slot)), "g1mpc_update_host_end")
+        out, _ = self._inflight.pop(int(slot))
+        return out["u_opt"], out["x_opt"], dict(status=out["status"], iters=out["iters"], resid=out["resid"])
+
+    def out_buffers(self, B, pinned=True):
+        mk = (lambda *sh, dtype=np.float64: self.pinned(*sh, dtype=dtype)) if pinned else (lambda *sh, dtype=np.float64: np.zeros(sh, dtype))
+        o = dict(u_opt=mk(B, self.N, self.nu), x_opt=mk(B, self.N, NS), status=mk(B, dtype=np.int32), iters=mk(B, dtype=np.int32),
+                 resid=mk(B, 4))
+        o["x_opt"][...] = 0.0
+        return o
 
 
 class MPC:

@@ -31,7 +31,7 @@ extern "C" {
 #endif
 
 #define G1MPC_NUM_STATES 13
-#define G1MPC_ABI_VERSION 3
+#define G1MPC_ABI_VERSION 4
 
 typedef enum g1mpc_error {
     G1MPC_OK = 0,
@@ -98,14 +98,31 @@ int g1mpc_emit_qp_batch(g1mpc_handle *h, int64_t B, const double *x0, const doub
                         double *l, double *u, void *stream);
 
 /*
- * Same as g1mpc_solve_batch but every pointer is HOST memory: stages through pinned buffers owned by
- * the handle, copies host->device, solves, copies device->host and synchronises.  x_opt is in/out.
- * This is the call the reference-facing MPC.update()/updateMPC wrapper makes.
+ * Same as g1mpc_solve_batch but every pointer is HOST memory: copies host->device, solves, copies device->host and
+ * synchronises.  x_opt is in/out.  This is the call the reference-facing MPC.update()/updateMPC wrapper makes
+ * (g1_mpc/src/mpc.cpp:448-473 is called with Eigen matrices in host memory, mpc_to_wbid_node.cpp:494).
+ * Caller buffers that are page-locked (cudaMallocHost / cudaHostRegister) are copied straight from / to where they
+ * lie; pageable ones are staged through pinned buffers owned by the handle.
  */
 int g1mpc_update_host(g1mpc_handle *h, int64_t B, const double *x0, const double *x_ref,
                       const double *contact, const double *c_horizon, const double *p_com,
                       const double *x_current, int one_rollout, double *u_opt, double *x_opt,
                       int32_t *status, int32_t *iters, double *resid);
+
+/*
+ * The same call in two halves, for a host that feeds one batch after the other (a fleet of simulated walkers, or
+ * several controllers behind one GPU): _begin enqueues copy-in, solve and copy-out of a batch on the slot's streams
+ * and returns; _end waits for that slot and (for pageable output buffers) unpacks the results.  Slots
+ * 0 .. G1MPC_HOST_SLOTS-1 are independent, so batch i+1 can be on its way to the device while batch i is being solved.
+ * All buffers of a slot must stay valid and untouched between _begin and _end.  g1mpc_update_host == _begin + _end on
+ * slot 0.
+ */
+#define G1MPC_HOST_SLOTS 3
+int g1mpc_update_host_begin(g1mpc_handle *h, int slot, int64_t B, const double *x0, const double *x_ref,
+                            const double *contact, const double *c_horizon, const double *p_com,
+                            const double *x_current, int one_rollout, double *u_opt, double *x_opt,
+                            int32_t *status, int32_t *iters, double *resid);
+int g1mpc_update_host_end(g1mpc_handle *h, int slot);
 
 /*
  * SURVEY 8f-1 -- what the demo node builds before every updateMPC call, for a batch (device pointers):

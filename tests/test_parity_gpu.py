@@ -331,3 +331,40 @@ def test_two_cycle_problems_of_config5_are_solved(orc):
         xs, _, cert = orc.qp_exact(p, m["H"], m["g"], arrs[2][b])
         assert cert["rc"] == 0
         assert np.abs(u[b].cpu().numpy().ravel() - xs).max() <= GRF_TOL
+
+
+@pytest.mark.parametrize("pin", [True, False])
+def test_host_api_in_two_halves_equals_the_blocking_call(pin):
+    """g1mpc_update_host_begin/_end: three different batches in flight on the three slots, page-locked caller buffers
+    (copied by DMA where they lie) or pageable ones (staged); every slot returns what the blocking call returns, the
+    in/out semantics of x_opt included; a slot cannot be reused before its _end."""
+    preset = presets.get_preset("cpp_node")
+    s = _solver(preset)
+    Bs = [600, 130, 40]
+    batches = [[t.numpy() for t in inputs.random_batch(preset, B, seed=31 + i)] for i, B in enumerate(Bs)]
+    modes = [(True, False), (False, False), (True, True)]          # (x_current given, one_rollout)
+    x_prev = [np.random.default_rng(i).normal(size=(B, 10, 13)) for i, B in enumerate(Bs)]
+    want = [s.update_host(*b, x_current=b[0] if xc else None, one_rollout=one, x_opt=xp)
+            for b, (xc, one), xp in zip(batches, modes, x_prev)]
+    outs, held = [], []
+    for sl, (b, (xc, one), xp) in enumerate(zip(batches, modes, x_prev)):
+        if pin:
+            hb = []
+            for a in b:
+                p = s.pinned(*a.shape); p[...] = a; hb.append(p)
+            o = s.out_buffers(Bs[sl], pinned=True)
+        else:
+            hb, o = [np.ascontiguousarray(a) for a in b], s.out_buffers(Bs[sl], pinned=False)
+        o["x_opt"][...] = xp
+        held.append(hb)
+        outs.append(s.update_host_begin(sl, *hb, x_current=hb[0] if xc else None, one_rollout=one, out=o))
+    with pytest.raises(RuntimeError):
+        s.update_host_begin(1, *held[1], out=s.out_buffers(Bs[1], pinned=False))       # slot 1 is still in flight
+    for sl in (2, 0, 1):
+        u, x, info = s.update_host_end(sl)
+        wu, wx, winfo = want[sl]
+        assert np.array_equal(u, wu) and np.array_equal(x, wx)
+        assert np.array_equal(info["status"], winfo["status"]) and np.array_equal(info["iters"], winfo["iters"])
+        assert np.array_equal(info["resid"], winfo["resid"])
+    with pytest.raises(RuntimeError):
+        s.update_host_end(0)                                         # nothing in flight any more
