@@ -84,11 +84,12 @@ struct WLay {
     static constexpr int oSl = ev(oU + NCN * 3);        // [NCN*6] slacks
     static constexpr int oLam = oSl + NCN * 6;      // [NCN*6] multipliers
     static constexpr int oGf = oLam + NCN * 6;      // [NCN*3] grad f(u)
-    static constexpr int oDst = ev(oGf + NCN * 3);      // [NCN*9] 1/s (6), 1/a, 1/b, 1/d2 of the 3x3 block
-    static constexpr int oProd = ev(oDst + NCN * 9);    // [NCN*6] predictor ds*dl (Mehrotra second-order term), then q
-    static constexpr int oTv = oProd + NCN * 6;     // [NCN*3] Dblk^-1 rhs, then du
+    static constexpr int oDst = ev(oGf + NCN * 3);      // [NCN*3] 1/a, 1/b, 1/d2 of the 3x3 block (1/s is recomputed where needed)
+    static constexpr int oProd = ev(oDst + NCN * 3);    // [NCN*6] predictor ds*dl (Mehrotra second-order term), then q, then W_c^T y
+    static constexpr bool kTvInScratch = 3 * NCN <= 12 * N;     // Dblk^-1 rhs / du fit into vB|vC, dead whenever they are live
+    static constexpr int oTvOwn = oProd + NCN * 6;      // [NCN*3] Dblk^-1 rhs, then du (only when they do not fit into the scratch)
     // ---- per stage ----  (every region below starts on a 16-byte boundary: rows are read as double2)
-    static constexpr int oSt = oTv + NCN * 3;       // [(NCN+1)/2] int32 list of stance contacts (compacted)
+    static constexpr int oSt = ev(oTvOwn + (kTvInScratch ? 0 : NCN * 3));   // [(NCN+1)/2] int32 list of stance contacts (compacted)
     static constexpr int oE = ev(oSt + (NCN + 1) / 2);   // [N*12]  free-response error A^(k+1) x0 - xref_k (mpc.cpp:369-375)
     static constexpr int SST = 22;                  // S_k packed (21) + pad
     static constexpr int oS = oE + N * 12;          // [N*SST]
@@ -96,22 +97,26 @@ struct WLay {
     // G2, Psi and Gamma are stored by columns (the factor lanes own columns), P12 by rows
     // (Gamma is kept beside G2: rebuilding it as G2 + Phi^T Psi cancels badly on long horizons -- measured at N = 40)
     static constexpr int sG2 = 0, sPsi = 36, sP12 = 72, sGam = 108, sP22 = 144, STG = 166;
-    static constexpr int oRic = oS + N * SST;       // [N*STG] ; after the corrector solve: ds | dl  (needs 12 NCN <= STG N)
-    // ---- scratch, three users: gradient sweeps | factor exchange | solve vectors ----
-    static constexpr int oX = oRic + N * STG;       // gradient: w[N*6] X[N*12] L1[N*6] V[N*6]
-    static constexpr int oW = oX;                   //   w  [N*6]
-    static constexpr int oXs = oW + N * 6;          //   X  [N*12]
-    static constexpr int oL1 = oXs + N * 12;        //   L1 [N*6]
-    static constexpr int oV = oL1 + N * 6;          //   V  [N*6]  (then Bm' V in place)
+    static constexpr int oRic = oS + N * SST;       // [N*STG] stage factors.  The region is dead from the end of the corrector
+                                                    // solve to the next factorisation and then holds, one after the other:
+                                                    //   ds | dl  (needs 12 NCN <= STG N)   and the gradient sweeps' vectors
+    static constexpr int oW = oRic;                 //   gradient: w  [N*6]      (these four also survive the last iteration:
+    static constexpr int oXs = oW + N * 6;          //             X  [N*12]      the outputs read w, X and V)
+    static constexpr int oL1 = oXs + N * 12;        //             L1 [N*6]
+    static constexpr int oV = oL1 + N * 6;          //             V  [N*6]  (then Bm' V in place)
+    // ---- scratch of the solves and of the factor exchange ----
+    static constexpr int oX = oRic + N * STG;
     static constexpr int oVa = oX;                  // solve: vA [N*6]  t -> Gamma't -> b -> y2
     static constexpr int oVb = oVa + N * 6;         //        vB [N*6]  c1 -> y1
     static constexpr int oVc = oVb + N * 6;         //        vC [N*6]  c2' -> y (multiplier wrench, output of the solve)
     static constexpr int oVd = oVc + N * 6;         //        vD [N*6]  p2 of P_{k+1} (incoming co-state of stage k)
     static constexpr int oPb = oVd + N * 6;         //        p1 exchange, double buffered [12]
     static constexpr int oEx = oVd;                 // factor exchange: A21 [36] (dead before the solve starts)
-    static constexpr int scratch = (N * 30 > N * 24 + 12) ? ((N * 30 > 18 * N + 36) ? N * 30 : 18 * N + 36) : ((N * 24 + 12 > 18 * N + 36) ? N * 24 + 12 : 18 * N + 36);
+    static constexpr int oTv = kTvInScratch ? oVb : oTvOwn;     // written after a solve has delivered vA, read before the next one starts
+    static constexpr int scratch = (N * 24 + 12 > 18 * N + 36) ? N * 24 + 12 : 18 * N + 36;
     static constexpr int oEnd = ev(oX + scratch);
     static_assert(12 * NCN <= STG * N, "ds|dl alias the stage storage: needs num_contacts <= 10");
+    static_assert(30 * N <= STG * N, "gradient vectors alias the stage storage");
     static constexpr size_t bytes = sizeof(double) * (size_t)oEnd;
 };
 
@@ -332,8 +337,8 @@ __device__ __forceinline__ void assemble_stage(double *sm, const DevParams &P, c
             tf[0] += tv[0]; tf[1] += tv[1]; tf[2] += tv[2];
             if (WITH_S) {
                 double Di[6];
-                const double *Ds = sm + L_::oDst + 9 * c, *l6 = sm + L_::oLam + 6 * c;
-                contact_dinv(l6[0] * Ds[0], l6[1] * Ds[1], l6[2] * Ds[2], l6[3] * Ds[3], Ds[6], Ds[7], Ds[8], P.mu, Di);
+                const double *Ds = sm + L_::oDst + 3 * c, *l6 = sm + L_::oLam + 6 * c, *s6 = sm + L_::oSl + 6 * c;
+                contact_dinv(l6[0] * frcp(s6[0]), l6[1] * frcp(s6[1]), l6[2] * frcp(s6[2]), l6[3] * frcp(s6[3]), Ds[0], Ds[1], Ds[2], P.mu, Di);
                 const double D00 = Di[0], D01 = Di[1], D02 = Di[2], D11 = Di[3], D12 = Di[4], D22 = Di[5];
                 // RD = skew(r) Dinv
                 const double a00 = -r2 * D01 + r1 * D02, a01 = -r2 * D11 + r1 * D12, a02 = -r2 * D12 + r1 * D22;
@@ -892,20 +897,19 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
             const double r2 = g2 - mu * (l6[0] + l6[1] + l6[2] + l6[3]) + l6[4] - l6[5];
             p_rd = fmax(p_rd, fmax(fabs(r0), fmax(fabs(r1), fabs(r2))));
             double D[6];
-            double *Ds = Dst + 9 * c;
+            double *Ds = Dst + 3 * c;
 #pragma unroll
             for (int j = 0; j < 6; j++) {
                 const double si = frcp(s6[j]);
                 p_gap += s6[j] * l6[j];
                 D[j] = l6[j] * si;
-                Ds[j] = si;
             }
             // Dblk = sr I + Cb' D Cb = [[a,0,e],[0,b,f],[e,f,cc]] ; LDL' with a cancellation-free Schur term
             const double ia = frcp(sr + D[0] + D[1]), ib = frcp(sr + D[2] + D[3]);
             const double d2 = sr + D[4] + D[5] + mu * mu * ((sr * (D[0] + D[1]) + 4.0 * D[0] * D[1]) * ia +
                                                             (sr * (D[2] + D[3]) + 4.0 * D[2] * D[3]) * ib);
             const double id2 = frcp(d2);
-            Ds[6] = ia; Ds[7] = ib; Ds[8] = id2;
+            Ds[0] = ia; Ds[1] = ib; Ds[2] = id2;
             double Di[6];
             contact_dinv(D[0], D[1], D[2], D[3], ia, ib, id2, mu, Di);
             tv[3 * c] = -(Di[0] * g0 + Di[1] * g1 + Di[2] * g2);
@@ -934,16 +938,18 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         double p_rmax = 0.0, p_sum = 0.0;
         for (int i = lane; i < n_stance; i += 32) {
             const int c = stIdx[i], k = c / NC;
-            const double *z = zt + 6 * k, *r = rr + 3 * c, *Ds = Dst + 9 * c, *l6 = lam + 6 * c;
-            double rt[3], X[18];
+            const double *z = zt + 6 * k, *r = rr + 3 * c, *Ds = Dst + 3 * c, *l6 = lam + 6 * c;
+            double rt[3], X[18], si[6];
+#pragma unroll
+            for (int j = 0; j < 6; j++) si[j] = frcp(sl[6 * c + j]);
             rt[0] = -gf[3 * c] - ((z[1] * r[2] - z[2] * r[1]) + z[3]);
             rt[1] = -gf[3 * c + 1] - ((z[2] * r[0] - z[0] * r[2]) + z[4]);
             rt[2] = -gf[3 * c + 2] - ((z[0] * r[1] - z[1] * r[0]) + z[5]);
-            contact_X(l6[0] * Ds[0], l6[1] * Ds[1], l6[2] * Ds[2], l6[3] * Ds[3], Ds[6], Ds[7], Ds[8], sr, mu, X);
+            contact_X(l6[0] * si[0], l6[1] * si[1], l6[2] * si[2], l6[3] * si[3], Ds[0], Ds[1], Ds[2], sr, mu, X);
 #pragma unroll
             for (int j = 0; j < 6; j++) {
                 const double dsi = -(X[3 * j] * rt[0] + X[3 * j + 1] * rt[1] + X[3 * j + 2] * rt[2]);
-                const double x = dsi * Ds[j];
+                const double x = dsi * si[j];
                 const double dli = -l6[j] * (1.0 + x);
                 p_rmax = fmax(p_rmax, fmax(-x, 1.0 + x));
                 prod[6 * c + j] = dsi * dli;
@@ -964,14 +970,14 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         // (5) corrector right-hand side: t = Dblk^-1 (-grad f + Cb'q),  q = (ds dl - sigma mu)/s
         for (int i = lane; i < n_stance; i += 32) {
             const int c = stIdx[i];
-            const double *Ds = Dst + 9 * c, *l6 = lam + 6 * c;
-            double q6[6], Di[6];
+            const double *Ds = Dst + 3 * c, *l6 = lam + 6 * c;
+            double q6[6], Di[6], si[6];
 #pragma unroll
-            for (int j = 0; j < 6; j++) q6[j] = fma(w2, prod[6 * c + j], -sigma_gap) * Ds[j];
+            for (int j = 0; j < 6; j++) { si[j] = frcp(sl[6 * c + j]); q6[j] = fma(w2, prod[6 * c + j], -sigma_gap) * si[j]; }
             const double r0 = -gf[3 * c] + (q6[0] - q6[1]);
             const double r1 = -gf[3 * c + 1] + (q6[2] - q6[3]);
             const double r2 = -gf[3 * c + 2] + (-mu * (q6[0] + q6[1] + q6[2] + q6[3]) + q6[4] - q6[5]);
-            contact_dinv(l6[0] * Ds[0], l6[1] * Ds[1], l6[2] * Ds[2], l6[3] * Ds[3], Ds[6], Ds[7], Ds[8], mu, Di);
+            contact_dinv(l6[0] * si[0], l6[1] * si[1], l6[2] * si[2], l6[3] * si[3], Ds[0], Ds[1], Ds[2], mu, Di);
             tv[3 * c] = Di[0] * r0 + Di[1] * r1 + Di[2] * r2;
             tv[3 * c + 1] = Di[1] * r0 + Di[3] * r1 + Di[4] * r2;
             tv[3 * c + 2] = Di[2] * r0 + Di[4] * r1 + Di[5] * r2;
@@ -989,23 +995,25 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         p_rmax = 0.0;
         for (int i = lane; i < n_stance; i += 32) {
             const int c = stIdx[i], k = c / NC;
-            const double *z = zt + 6 * k, *r = rr + 3 * c, *Ds = Dst + 9 * c, *l6 = lam + 6 * c, *q6 = prod + 6 * c;
-            double rt[3], X[18], Di[6];
+            const double *z = zt + 6 * k, *r = rr + 3 * c, *Ds = Dst + 3 * c, *l6 = lam + 6 * c, *q6 = prod + 6 * c;
+            double rt[3], X[18], Di[6], si[6];
+#pragma unroll
+            for (int j = 0; j < 6; j++) si[j] = frcp(sl[6 * c + j]);
             const double wy0 = (z[1] * r[2] - z[2] * r[1]) + z[3], wy1 = (z[2] * r[0] - z[0] * r[2]) + z[4];     // W_c^T y
             const double wy2 = (z[0] * r[1] - z[1] * r[0]) + z[5];
             rt[0] = -gf[3 * c] + (q6[0] - q6[1]) - wy0;
             rt[1] = -gf[3 * c + 1] + (q6[2] - q6[3]) - wy1;
             rt[2] = -gf[3 * c + 2] + (-mu * (q6[0] + q6[1] + q6[2] + q6[3]) + q6[4] - q6[5]) - wy2;
-            const double D0 = l6[0] * Ds[0], D1 = l6[1] * Ds[1], D2 = l6[2] * Ds[2], D3 = l6[3] * Ds[3];
-            contact_dinv(D0, D1, D2, D3, Ds[6], Ds[7], Ds[8], mu, Di);
-            contact_X(D0, D1, D2, D3, Ds[6], Ds[7], Ds[8], sr, mu, X);
+            const double D0 = l6[0] * si[0], D1 = l6[1] * si[1], D2 = l6[2] * si[2], D3 = l6[3] * si[3];
+            contact_dinv(D0, D1, D2, D3, Ds[0], Ds[1], Ds[2], mu, Di);
+            contact_X(D0, D1, D2, D3, Ds[0], Ds[1], Ds[2], sr, mu, X);
             tv[3 * c] = Di[0] * rt[0] + Di[1] * rt[1] + Di[2] * rt[2];
             tv[3 * c + 1] = Di[1] * rt[0] + Di[3] * rt[1] + Di[4] * rt[2];
             tv[3 * c + 2] = Di[2] * rt[0] + Di[4] * rt[1] + Di[5] * rt[2];
 #pragma unroll
             for (int j = 0; j < 6; j++) {
                 const double dsi = -(X[3 * j] * rt[0] + X[3 * j + 1] * rt[1] + X[3 * j + 2] * rt[2]);
-                const double x = dsi * Ds[j];
+                const double x = dsi * si[j];
                 const double rl = 1.0 + x + q6[j] * frcp(l6[j]);
                 p_rmax = fmax(p_rmax, fmax(-x, rl));
                 dsv[6 * c + j] = dsi; dlv[6 * c + j] = -l6[j] * rl;
