@@ -343,8 +343,19 @@ def extras(solver, preset, dev):
         a.record(); solver.update_batch(*one, x_current=one[0], want_resid=False); b.record(); b.synchronize()
         if i >= 20:
             lat.append(a.elapsed_time(b) * 1e3)
+    # the same launch with the host kept ahead of the device (a 150 us spin kernel is queued first), so that the event pair
+    # brackets the kernel alone and not the ~25 us of Python/ctypes between the first event and the launch
+    dlat = []
+    for i in range(220):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda._sleep(300000)
+        a.record(); _, _, info1 = solver.update_batch(*one, x_current=one[0], want_resid=False); b.record(); b.synchronize()
+        if i >= 20:
+            dlat.append(a.elapsed_time(b) * 1e3)
     out["single_solve_us"] = {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)), "launches": len(lat),
-                              "timing": "CUDA events around one B=1 launch"}
+                              "timing": "CUDA events around one B=1 call of BatchedMPC.update_batch (host call overhead inside)",
+                              "device_p50": float(np.percentile(dlat, 50)), "device_p99": float(np.percentile(dlat, 99)),
+                              "device_timing": "same, launch queued behind a spin kernel: the kernel alone", "ipm_iters": int(info1["iters"][0])}
     return out
 
 

@@ -751,6 +751,38 @@ __device__ __forceinline__ void gradient_sweeps(double *sm, const DevParams &P, 
 }
 
 
+// Rollout (mpc.cpp:427-446) in closed form; x_opt (gx) is in/out.  Row i >= 1 is the free response of x_current over i
+// steps (A_c is nilpotent: base + i rate + i (i-1) quad per component) plus the response X to the wrenches, which the
+// last gradient evaluation left in shared memory (zero initial state, same recurrence as the reference's).
+// Not inlined: keeps the register allocation of the iteration loop independent of the epilogue.
+__device__ __noinline__ void rollout_rows(double *gx, const double *x_current, int last, double *fr, const double *Xs,
+                                          double dt, double cz, double sz, int lane)
+{
+    const double *xc = x_current ? x_current : gx;
+    if (lane < NS) {
+        const int r = lane;
+        const double base = xc[r];
+        double rate = 0.0, quad = 0.0;
+        if (r < 3) {
+            const double w0 = xc[6], w1 = xc[7], w2 = xc[8];
+            rate = dt * (r == 0 ? (cz * w0 - sz * w1) : (r == 1 ? (sz * w0 + cz * w1) : w2));
+        } else if (r < 6) {
+            rate = dt * xc[6 + r];
+            if (r == 5) quad = 0.5 * dt * dt * xc[12];
+        } else if (r == 11) rate = dt * xc[12];
+        fr[r] = base; fr[NS + r] = rate; fr[2 * NS + r] = quad;     // [3][13] base | rate | quad (the solve scratch is dead)
+        if (x_current) gx[r] = base;
+    }
+    __syncwarp();
+    for (int e = NS + lane; e < (last + 1) * NS; e += 32) {
+        const int i = e / NS, r = e % NS;
+        const double di = (double)i;
+        double val = fma(di * (di - 1.0), fr[2 * NS + r], fma(di, fr[NS + r], fr[r]));
+        if (r < 12) val += Xs[12 * (i - 1) + r];
+        gx[e] = val;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // fused solve kernel: blockDim.x = 32 * warps_per_block, warp -> problem
 // ------------------------------------------------------------------------------------------------
@@ -760,6 +792,9 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
     using L_ = WLay<N, NC>;
     constexpr int NU = 3 * NC, NV = NU * N, NCN = NC * N;
     extern __shared__ __align__(16) double sm_all[];
+#ifdef G1MPC_PHASE_CLOCKS
+    const long long ph_k0 = clock64();
+#endif
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     double *sm = sm_all + (size_t)warp * L_::oEnd;
     const long long b = (long long)blockIdx.x * (blockDim.x >> 5) + warp;
@@ -846,6 +881,9 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
     __syncwarp();
 
     PH_DECL
+#ifdef G1MPC_PHASE_CLOCKS
+    ph_t[13] = ph_last - ph_k0;                     // prologue: linearise, stage the inputs, start point
+#endif
     int status = G1MPC_MAX_ITER, it = 0;
     double gap = 0.0, rdmax = 0.0;
     bool lam_init = false;
@@ -1112,46 +1150,13 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
             for (int i = 0; i < 5; i++) gy[5 * c + i] = y5[i];
         }
     }
+    rollout_rows(io.x_opt + b * (N * NS), io.x_current ? io.x_current + b * NS : nullptr, io.one_rollout ? 1 : N - 1,
+                 sm + L_::oVa, sm + L_::oXs, P.dt, cz, sz, lane);
 #ifdef G1MPC_PHASE_CLOCKS
-    if (io.y_opt && lane == 0) { __syncwarp(1u); for (int i = 0; i < 16; i++) io.y_opt[b * (5 * NCN) + i] = (double)ph_t[i]; }
+    __syncwarp();
+    PH(14)                                          // epilogue: outputs + rollout
+    if (io.y_opt && lane == 0) { for (int i = 0; i < 16; i++) io.y_opt[b * (5 * NCN) + i] = (double)ph_t[i]; }
 #endif
-    // rollout (mpc.cpp:427-446) in closed form; x_opt is in/out
-    {
-        double *gx = io.x_opt + b * (N * NS);
-        const double *xc = io.x_current ? io.x_current + b * NS : gx;
-        const int last = io.one_rollout ? 1 : N - 1;
-        for (int e = lane; e < (last + 1) * NS; e += 32) {
-            const int i = e / NS, r = e % NS;
-            if (i == 0) { if (io.x_current) gx[r] = xc[r]; continue; }
-            const double dt = P.dt, di = (double)i;
-            double val;
-            if (r < 3) {        // theta_i = theta_c + dt Rz (i w_c + sum_{j<i-1} (i-1-j) ww_j)
-                double a0 = di * xc[6], a1 = di * xc[7], a2 = di * xc[8];
-                for (int j = 0; j + 1 < i; j++) {
-                    const double f = (double)(i - 1 - j);
-                    a0 += f * wv[6 * j]; a1 += f * wv[6 * j + 1]; a2 += f * wv[6 * j + 2];
-                }
-                const double rot = r == 0 ? (cz * a0 - sz * a1) : (r == 1 ? (sz * a0 + cz * a1) : a2);
-                val = xc[r] + dt * rot;
-            } else if (r < 6) { // p_i = p_c + dt (i v_c + C(i,2) dt g e_z + sum (i-1-j) wv_j)
-                const int ax = r - 3;
-                double a = di * xc[9 + ax];
-                if (ax == 2) a += 0.5 * di * (di - 1.0) * dt * xc[12];
-                for (int j = 0; j + 1 < i; j++) a += (double)(i - 1 - j) * wv[6 * j + 3 + ax];
-                val = xc[r] + dt * a;
-            } else if (r < 9) {
-                double a = xc[r];
-                for (int j = 0; j < i; j++) a += wv[6 * j + r - 6];
-                val = a;
-            } else if (r < 12) {
-                double a = xc[r];
-                if (r == 11) a += di * dt * xc[12];
-                for (int j = 0; j < i; j++) a += wv[6 * j + 3 + r - 9];
-                val = a;
-            } else val = xc[12];
-            gx[i * NS + r] = val;
-        }
-    }
 }
 
 } // namespace v2

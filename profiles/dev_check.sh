@@ -4,3 +4,4 @@ G1MPC_B200_LIB=gpurun_in/libdev.so python -m pytest tests/test_parity_gpu.py -m 
 G1MPC_B200_LIB=gpurun_in/libtiming.so python profiles/phase_clocks.py 1 2>&1 | cat
 G1MPC_B200_LIB=gpurun_in/libtiming.so python profiles/phase_clocks.py 1024 2>&1 | sed -n 1,9p
 G1MPC_B200_LIB=gpurun_in/libftiming.so python profiles/phase_clocks.py 1 2>&1 | grep factor
+G1MPC_B200_LIB=gpurun_in/libdev.so python profiles/dev_time.py 2>&1 | tail -2

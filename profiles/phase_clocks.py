@@ -14,7 +14,7 @@ for _ in range(3):
 torch.cuda.synchronize()
 ph = info["y"][:, :16].cpu().numpy(); it = info["iters"].cpu().numpy()
 names = ["gradient", "passA", "assemble+S", "factor", "solve: misc", "passB+B2+assemble", "passC+step", "setup/loop",
-         "solve: pre", "solve: backward", "solve: b", "solve: forward", "solve: output"]
+         "solve: pre", "solve: backward", "solve: b", "solve: forward", "solve: output", "prologue (whole solve)", "epilogue (whole solve)"]
 if os.environ.get("G1MPC_B200_LIB", "").endswith("libftiming.so"):      # -DG1MPC_FACTOR_CLOCKS: 8..12 split the factor stage
     names[3] = "factor: P22 update"; names[4] = "solves (both)"
     names[8:13] = ["factor: loads+inv6", "factor: ldl6", "factor: columns", "factor: P12 S col", "factor: stores"]
