@@ -172,7 +172,19 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL writes its version banner to stdout when the communicator comes up (NCCL_DEBUG=VERSION on the GPU boxes):
+        # send file descriptor 1 to stderr until it has, so that rank 0's stdout carries the one JSON line only
+        sys.stdout.flush()
+        saved_out = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.all_reduce(torch.zeros(1, device=dev))
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_out, 1)
+            os.close(saved_out)
     preset = presets.get_preset("cpp_node")
     N, nc = preset["horizon"], preset["num_contacts"]
     solver = BatchedMPC(preset, device=local_rank)
