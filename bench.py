@@ -348,6 +348,26 @@ def extras(solver, preset, dev):
     ms = e0.elapsed_time(e1) / 3
     out["config3_65536_random"] = {"problems_per_s": 65536 / (ms * 1e-3), "ms_per_launch": ms, "unsolved": int((info["status"] != 0).sum()),
                                    "ipm_iters_mean": float(info["iters"].double().mean())}
+    # config 4: horizon sweep with four corner contacts per foot (B = 4,096 / 1,024 / 256, seed 11)
+    from g1_locomotion_b200 import BatchedMPC, presets as _presets
+    sweep = {}
+    for n_h, b_h in ((10, 4096), (20, 1024), (40, 256)):
+        pr = _presets.get_preset("cpp_node", horizon=n_h, num_contacts=8)
+        sv = BatchedMPC(pr, device=dev.index)
+        ins_h = list(inputs.random_batch(pr, b_h, seed=11, device=dev))
+        for _ in range(2):
+            _, _, info_h = sv.update_batch(*ins_h, x_current=ins_h[0], want_resid=False)
+        torch.cuda.synchronize()
+        h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        h0.record()
+        for _ in range(3):
+            sv.update_batch(*ins_h, x_current=ins_h[0], want_resid=False)
+        h1.record(); torch.cuda.synchronize()
+        ms_h = h0.elapsed_time(h1) / 3
+        sweep["N%d_nc8_B%d" % (n_h, b_h)] = {"problems_per_s": b_h / (ms_h * 1e-3), "ms_per_launch": ms_h, "unsolved": int((info_h["status"] != 0).sum()),
+                                            "ipm_iters_mean": float(info_h["iters"].double().mean()), "kernel": sv.kernel_info()}
+        sv.close()
+    out["config4_horizon_sweep"] = sweep
     one = [t[:1].contiguous() for t in ins]
     lat = []
     for i in range(520):

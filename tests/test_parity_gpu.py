@@ -368,3 +368,27 @@ def test_host_api_in_two_halves_equals_the_blocking_call(pin):
         assert np.array_equal(info["resid"], winfo["resid"])
     with pytest.raises(RuntimeError):
         s.update_host_end(0)                                         # nothing in flight any more
+
+
+def test_empty_and_ragged_batches():
+    """B = 0 is a no-op on every entry point; batch sizes that do not fill a launch wave or a host chunk (1, 33, 127, 129,
+    513) give, problem by problem, exactly what the full batch gives."""
+    preset = presets.get_preset("cpp_node")
+    s = _solver(preset)
+    full = [t.numpy() for t in inputs.random_batch(preset, 513, seed=41)]
+    dfull = _dev(full)
+    u_all, x_all, info_all = s.update_batch(*dfull, x_current=dfull[0])
+    empty = [t[:0].contiguous() for t in dfull]
+    u0, x0_, info0 = s.update_batch(*empty, x_current=empty[0])
+    assert u0.shape == (0, 10, 12) and x0_.shape == (0, 10, 13) and info0["status"].numel() == 0
+    uh0, xh0, infoh0 = s.update_host(*[a[:0] for a in full], x_current=full[0][:0])
+    assert uh0.shape == (0, 10, 12) and infoh0["iters"].shape == (0,)
+    out = s.update_host_begin(2, *[np.ascontiguousarray(a[:0]) for a in full], x_current=np.ascontiguousarray(full[0][:0]))
+    assert s.update_host_end(2)[0].shape == (0, 10, 12)
+    for B in (1, 33, 127, 129, 513):
+        sub = [t[:B].contiguous() for t in dfull]
+        u, x, info = s.update_batch(*sub, x_current=sub[0])
+        assert torch.equal(u, u_all[:B]) and torch.equal(x, x_all[:B]) and torch.equal(info["iters"], info_all["iters"][:B])
+        uh, xh, infoh = s.update_host(*[a[:B] for a in full], x_current=full[0][:B])
+        assert np.array_equal(uh, u_all[:B].cpu().numpy()) and np.array_equal(xh, x_all[:B].cpu().numpy())
+        assert np.array_equal(infoh["status"], info_all["status"][:B].cpu().numpy())
