@@ -293,14 +293,21 @@ __global__ void fp64_peak_kernel(double *out, int iters)
     } while (0)
 
 typedef void (*solve_fn)(const DevParams, const BatchPtrs, long long);
-struct KernelEntry { int N, NC; solve_fn fn; size_t smem; };   // smem = bytes per warp (= per problem)
+struct KernelEntry { int N, NC; solve_fn fn; size_t smem; solve_fn fn2; };   // smem = bytes per problem; fn2 = two problems per warp (or null)
+// the two-problems-per-warp layout is compiled for the shapes whose stages fit the 16 lanes of a half-warp in one round
+template <int N, int NC>
+constexpr solve_fn two_per_warp()
+{
+    if constexpr (N <= 16 && NC == 4 && 2 * v2::WLay<N, NC>::bytes <= 227 * 1024) return v2::srbd_mpc_solve_warp_kernel<N, NC, 16>;
+    else return nullptr;
+}
 
 #ifdef G1MPC_DEV_SHAPE   /* development builds: only the bench shape */
 #define G1MPC_SHAPES(X) X(10, 4)
 #else
 #define G1MPC_SHAPES(X) X(10, 4) X(15, 4) X(20, 4) X(40, 4) X(10, 8) X(12, 8) X(20, 8) X(40, 8) X(5, 4) X(8, 4)
 #endif
-#define X_ENTRY(n, c) {n, c, v2::srbd_mpc_solve_warp_kernel<n, c>, v2::WLay<n, c>::bytes},
+#define X_ENTRY(n, c) {n, c, v2::srbd_mpc_solve_warp_kernel<n, c, 32>, v2::WLay<n, c>::bytes, two_per_warp<n, c>()},
 const KernelEntry kKernels[] = {G1MPC_SHAPES(X_ENTRY)};
 #undef X_ENTRY
 
@@ -313,6 +320,10 @@ struct g1mpc_handle {
     const KernelEntry *kernel;
     int warps_per_block = 1;
     int ctas_per_sm = 0;
+    // two problems per warp pay off once a scheduler would otherwise hold two warps: above 4 problems per SM
+    // (G1MPC_PPW=1|2 in the environment forces one layout -- tests compare the two bit for bit)
+    long long two_above = 0;
+    int force_ppw = 0;
     // host-API staging: kSlots batches in flight, each cut into up to kPipe chunks with a stream of their own
     static constexpr int kPipe = 4, kSlots = G1MPC_HOST_SLOTS;
     struct Off { size_t x0, xr, ct, ch, pc, xc, xo, u, res, st; };
@@ -378,6 +389,17 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
     if (e != cudaSuccess) { g_last_error = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
     cudaFuncSetAttribute((const void *)srbd_mpc_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->ctas_per_sm, (const void *)ke->fn, kWarpThreads * h->warps_per_block, ke->smem * h->warps_per_block);
+    if (ke->fn2) {
+        e = cudaFuncSetAttribute((const void *)ke->fn2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * ke->smem * h->warps_per_block));
+        if (e != cudaSuccess) { g_last_error = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
+    }
+    {
+        int sms = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        h->two_above = 4LL * sms;
+        const char *f = getenv("G1MPC_PPW");
+        h->force_ppw = f ? atoi(f) : 0;
+    }
     for (int sl = 0; sl < g1mpc_handle::kSlots; sl++)
         for (int i = 0; i < g1mpc_handle::kPipe; i++) {
             e = cudaStreamCreateWithFlags(&h->slot[sl].pipe[i], cudaStreamNonBlocking);
@@ -423,7 +445,11 @@ int g1mpc_solve_batch(g1mpc_handle *h, int64_t B, const double *x0, const double
     CUDA_TRY(cudaSetDevice(h->device));
     BatchPtrs io{x0, x_ref, contact, c_horizon, p_com, x_current, u_opt, x_opt, resid, y_opt, status, iters, one_rollout};
     const int wpb = h->warps_per_block;
-    h->kernel->fn<<<(unsigned)((B + wpb - 1) / wpb), kWarpThreads * wpb, h->kernel->smem * wpb, (cudaStream_t)stream>>>(h->dev, io, (long long)B);
+    const bool two = h->kernel->fn2 && (h->force_ppw == 2 || (h->force_ppw != 1 && B > h->two_above));
+    if (two)
+        h->kernel->fn2<<<(unsigned)((B + 2 * wpb - 1) / (2 * wpb)), kWarpThreads * wpb, 2 * h->kernel->smem * wpb, (cudaStream_t)stream>>>(h->dev, io, (long long)B);
+    else
+        h->kernel->fn<<<(unsigned)((B + wpb - 1) / wpb), kWarpThreads * wpb, h->kernel->smem * wpb, (cudaStream_t)stream>>>(h->dev, io, (long long)B);
     CUDA_TRY(cudaGetLastError());
     return G1MPC_OK;
 }

@@ -47,23 +47,35 @@ namespace v2 {
 
 constexpr unsigned kFullMask = 0xffffffffu;
 
+// Reductions over the HL (32 or 16) lanes that own one problem; lanes of the other half-warp never mix in (xor offsets < HL).
+template <int HL>
 __device__ __forceinline__ double wsum(double v)
 {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFullMask, v, o);
+    for (int o = HL / 2; o > 0; o >>= 1) v += __shfl_xor_sync(kFullMask, v, o);
     return v;
 }
+template <int HL>
 __device__ __forceinline__ double wmax(double v)
 {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(kFullMask, v, o));
+    for (int o = HL / 2; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(kFullMask, v, o));
     return v;
 }
+template <int HL>
 __device__ __forceinline__ double wmin(double v)
 {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(kFullMask, v, o));
+    for (int o = HL / 2; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(kFullMask, v, o));
     return v;
+}
+// Sum over the contacts of a problem in an order that does not depend on HL: contact i belongs to "virtual lane" i % 32;
+// with 16 lanes per problem the two virtual lanes of a lane are kept apart (v[0]: rounds 0, 2, ..; v[1]: rounds 1, 3, ..)
+// and added as the 32-lane butterfly's first step would add them, so both layouts give the same bits.
+template <int HL>
+__device__ __forceinline__ double wsum2(const double (&v)[2])
+{
+    return wsum<HL>(HL == 32 ? v[0] : v[0] + v[1]);
 }
 
 // packed lower-triangular index of a symmetric 6x6, i >= j
@@ -320,11 +332,11 @@ struct StageC {
 };
 
 // t_k = Bm sum_c [r x tv_c ; tv_c]  (lane k), optionally also S_k = Bm (sum_c W~ Dinv W~') Bm'
-template <int N, int NC, bool WITH_S>
+template <int N, int NC, int HL, bool WITH_S>
 __device__ __forceinline__ void assemble_stage(double *sm, const DevParams &P, const StageC &C, int lane)
 {
     using L_ = WLay<N, NC>;
-    for (int k = lane; k < N; k += 32) {
+    for (int k = lane; k < N; k += HL) {
         double tt[3] = {0, 0, 0}, tf[3] = {0, 0, 0};
         double Stt[6] = {0, 0, 0, 0, 0, 0}, Sff[6] = {0, 0, 0, 0, 0, 0}, Stf[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};   // tau-tau, F-F (sym), tau-F (full)
         for (int j = 0; j < NC; j++) {
@@ -400,12 +412,14 @@ __device__ __forceinline__ void assemble_stage(double *sm, const DevParams &P, c
 // column of [ I | P21 | P22 ] (18 lanes), one 6x6 mat-vec and two substitutions each; then Psi = P12 S Gamma,
 // A11 = P11 - P12 S A21.
 // P11 stays in the registers of the six A21 lanes (one column each).  Returns false if a minor was not positive.
-template <int N, int NC>
+template <int N, int NC, int HL>
 __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, const StageC &C, int lane PH_PARAMS)
 {
     using L_ = WLay<N, NC>;
     double *Ex = sm + L_::oEx;
-    const int grp = lane < 18 ? lane / 6 : 2, cb = lane % 6;    // lanes >= 18 shadow group 2 and never store
+    // HL = 32: lanes >= 18 shadow group 2 and never store.  HL = 16 (two problems per warp): groups 0 and 1 as before,
+    // lanes 12..15 are columns 0..3 of group 2, and lanes 4, 5 (group 0) take over the P22 update of columns 4, 5.
+    const int grp = lane < 18 ? lane / 6 : 2, cb = lane % 6;
     const bool act = lane < 18;
     // Phi column cb:  (M Phi)[:,cb] = ga M[:,ja] + gb M[:,jb]
     const double ga = cb == 0 ? C.F.dc : (cb == 1 ? -C.F.dsn : C.F.dt), gb = cb == 0 ? C.F.dsn : (cb == 1 ? C.F.dc : 0.0);
@@ -417,7 +431,7 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
     // P_N = s Q
     {
         double *St = sm + L_::oRic + (N - 1) * L_::STG;
-        for (int e = lane; e < 58; e += 32) {
+        for (int e = lane; e < 58; e += HL) {
             double v = 0.0;
             if (e >= 36) {
 #pragma unroll
@@ -427,7 +441,8 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
         }
     }
     const double m1 = grp == 1 ? 1.0 : 0.0, e1 = 1.0 - m1;
-    const bool st2 = act && grp == 2;
+    const bool cf2 = HL == 16 && grp == 0 && cb >= 4;           // closed-form A22 column (see the P22 update)
+    const bool st2 = (act && grp == 2) || cf2;
     // stage-slot offsets of the two column stores shared by groups 0 and 1 (group 1 writes into the slot of stage k-1 and
     // into the exchange buffer)
     const int offr = grp == 0 ? L_::sG2 + 6 * cb : L_::sP12 - L_::STG + 6 * cb;
@@ -512,6 +527,14 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
             // P22 of P_k, column cb = s Q2 + A22 + Phi' M12 + A21 Phi      (group 2)
             // (every lane runs the arithmetic -- no divergence; only group 2 holds A22 in `col` and stores)
             double m12[6], pm[6], ca[6], cbv[6];
+            if (HL == 16) {
+                // columns 4 and 5 of A22 = T^-1 = L^-T D^-1 L^-1: their lower parts, operation for operation what the
+                // column solve of e_4 / e_5 produces (so that both lane layouts give the same bits)
+                const double l54 = T[tri(5, 4)];
+                const double x5 = __dmul_rn(-l54, dT[5]), x44 = fma(-l54, x5, dT[4]);
+                col[4] = cf2 ? x44 : col[4];
+                col[5] = cf2 ? (cb == 4 ? x5 : dT[5]) : col[5];
+            }
 #pragma unroll
             for (int i = 0; i < 6; i++) m12[i] = Sn[L_::sP12 + 6 * i + cb];
             ld6(Ex + 6 * ja, ca); ld6(Ex + 6 * jb, cbv);
@@ -534,14 +557,14 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
 // per-contact step needs: W_c^T y = zeta~_tau x r + zeta~_F).  The two sequential sweeps run on 12 lanes (one state
 // component each) and exchange the 12-vector through shared memory once per stage (42 cycles measured for
 // STS + sync + LDS against 27 for one dependent shuffle, but 8 instructions instead of 16-28 SHFL).
-template <int N, int NC>
+template <int N, int NC, int HL>
 __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int lane PH_PARAMS)
 {
     using L_ = WLay<N, NC>;
     double *vA = sm + L_::oVa, *vB = sm + L_::oVb, *vC = sm + L_::oVc, *vD = sm + L_::oVd, *pbuf = sm + L_::oPb;
     const PhiC F = C.F;
     // ---- pre (lane = stage): gt = Gamma^T t, c1 = P12 gt, c2 = Phi^T c1 + P22 gt
-    for (int k = lane; k < N; k += 32) {
+    for (int k = lane; k < N; k += HL) {
         const double *St = sm + L_::oRic + k * L_::STG;
         double t[6], gt[6], c1[6], c2[6], pc1[6], row[6], p22[22];
         ld6(vA + 6 * k, t);
@@ -601,7 +624,7 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
     }
     PHS(9)
     // ---- b_k = gt_k - S_k Gamma p2   (lane = stage)
-    for (int k = lane; k < N; k += 32) {
+    for (int k = lane; k < N; k += HL) {
         const double *St = sm + L_::oRic + k * L_::STG;
         double p2[6], g[6], row[6], sk[22], sg[6], b[6];
         ld6(vD + 6 * k, p2);
@@ -650,7 +673,7 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
     }
     PHS(11)
     // ---- output (lane = stage): y_k = P12^T y1 + P22 y2 + p2 ; zeta~ = Bm^T y_k
-    for (int k = lane; k < N; k += 32) {
+    for (int k = lane; k < N; k += HL) {
         const double *St = sm + L_::oRic + k * L_::STG;
         double y1[6], y2[6], z[6], row[6], p22[22], q[6];
         ld6(vB + 6 * k, y1); ld6(vA + 6 * k, y2); ld6(vD + 6 * k, z);
@@ -679,7 +702,7 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
 
 // grad f(u) = s r u + W^T (M W u + h): per-stage wrench, state rollout, adjoint sweep (all O(N)), then the
 // per-stage co-state wrench in physical units (Bm^T v) is left in V for the per-contact pass.
-template <int N, int NC>
+template <int N, int NC, int HL>
 __device__ __forceinline__ void gradient_sweeps(double *sm, const DevParams &P, const StageC &C, int lane)
 {
     using L_ = WLay<N, NC>;
@@ -687,7 +710,7 @@ __device__ __forceinline__ void gradient_sweeps(double *sm, const DevParams &P, 
     const double *E = sm + L_::oE;
     const PhiC F = C.F;
     // w_k = Bm sum_c [r x f ; f]    (lane = stage)                                   (mpc.cpp:213-254)
-    for (int k = lane; k < N; k += 32) {
+    for (int k = lane; k < N; k += HL) {
         double tt[3] = {0, 0, 0}, tf[3] = {0, 0, 0};
         for (int j = 0; j < NC; j++) {
             const int c = k * NC + j;
@@ -738,7 +761,7 @@ __device__ __forceinline__ void gradient_sweeps(double *sm, const DevParams &P, 
         }
     }
     __syncwarp();
-    for (int k = lane; k < N; k += 32) {                          // V <- Bm^T V
+    for (int k = lane; k < N; k += HL) {                          // V <- Bm^T V
         double *v = V + 6 * k;
         const double *J = C.J;
         const double v0 = v[0], v1 = v[1], v2 = v[2];
@@ -756,7 +779,7 @@ __device__ __forceinline__ void gradient_sweeps(double *sm, const DevParams &P, 
 // last gradient evaluation left in shared memory (zero initial state, same recurrence as the reference's).
 // Not inlined: keeps the register allocation of the iteration loop independent of the epilogue.
 __device__ __noinline__ void rollout_rows(double *gx, const double *x_current, int last, double *fr, const double *Xs,
-                                          double dt, double cz, double sz, int lane)
+                                          double dt, double cz, double sz, int lane, int nl, bool write)
 {
     const double *xc = x_current ? x_current : gx;
     if (lane < NS) {
@@ -771,10 +794,10 @@ __device__ __noinline__ void rollout_rows(double *gx, const double *x_current, i
             if (r == 5) quad = 0.5 * dt * dt * xc[12];
         } else if (r == 11) rate = dt * xc[12];
         fr[r] = base; fr[NS + r] = rate; fr[2 * NS + r] = quad;     // [3][13] base | rate | quad (the solve scratch is dead)
-        if (x_current) gx[r] = base;
+        if (x_current && write) gx[r] = base;
     }
     __syncwarp();
-    for (int e = NS + lane; e < (last + 1) * NS; e += 32) {
+    for (int e = NS + lane; e < (write ? (last + 1) * NS : 0); e += nl) {
         const int i = e / NS, r = e % NS;
         const double di = (double)i;
         double val = fma(di * (di - 1.0), fr[2 * NS + r], fma(di, fr[NS + r], fr[r]));
@@ -784,21 +807,27 @@ __device__ __noinline__ void rollout_rows(double *gx, const double *x_current, i
 }
 
 // ------------------------------------------------------------------------------------------------
-// fused solve kernel: blockDim.x = 32 * warps_per_block, warp -> problem
+// fused solve kernel: blockDim.x = 32 * warps_per_block.  HL = 32: warp -> problem.  HL = 16: two problems per warp, one
+// per half-warp (the 6x6 inverse and LDL' of a stage, identical in every lane, are then issued once for two problems, and
+// at the bench batch size no scheduler holds two competing warps).  `lane` is the lane WITHIN the problem throughout; all
+// control flow stays warp-uniform (a half that has finished keeps executing with its state frozen), so every
+// __syncwarp / shuffle is reached by all 32 lanes.  Both layouts give the same bits per problem.
 // ------------------------------------------------------------------------------------------------
-template <int N, int NC>
+template <int N, int NC, int HL>
 __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParams P, const BatchPtrs io, long long B)
 {
     using L_ = WLay<N, NC>;
-    constexpr int NU = 3 * NC, NV = NU * N, NCN = NC * N;
+    constexpr int NU = 3 * NC, NV = NU * N, NCN = NC * N, PPW = 32 / HL;
     extern __shared__ __align__(16) double sm_all[];
 #ifdef G1MPC_PHASE_CLOCKS
     const long long ph_k0 = clock64();
 #endif
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    double *sm = sm_all + (size_t)warp * L_::oEnd;
-    const long long b = (long long)blockIdx.x * (blockDim.x >> 5) + warp;
-    if (b >= B) return;
+    const int lane = threadIdx.x & (HL - 1), half = (threadIdx.x & 31) / HL, warp = threadIdx.x >> 5;
+    double *sm = sm_all + (size_t)(warp * PPW + half) * L_::oEnd;
+    long long b = ((long long)blockIdx.x * (blockDim.x >> 5) + warp) * PPW + half;
+    if (b - half >= B) return;                     // whole warp out of range
+    const bool valid = b < B;                      // odd batch: the last half-warp repeats the last problem and writes nothing
+    if (!valid) b = B - 1;
     double *rr = sm + L_::oR, *cfl = sm + L_::oCf, *u = sm + L_::oU, *sl = sm + L_::oSl, *lam = sm + L_::oLam;
     double *gf = sm + L_::oGf, *Dst = sm + L_::oDst, *prod = sm + L_::oProd, *tv = sm + L_::oTv, *E = sm + L_::oE;
     double *dsv = sm + L_::oRic, *dlv = sm + L_::oRic + 6 * NCN;     // alias: valid only after the corrector solve
@@ -817,7 +846,7 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
     C.F.dc = P.dt * lin.c; C.F.dsn = P.dt * lin.s; C.F.dt = P.dt;
     const double cz = lin.c, sz = lin.s;
     int bad_bounds = 0, n_stance = 0;
-    for (int c0 = 0; c0 < NCN; c0 += 32) {
+    for (int c0 = 0; c0 < NCN; c0 += HL) {
         const int c = c0 + lane;
         bool st = false;
         if (c < NCN) {
@@ -830,7 +859,8 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         st = hi > lo;
         }
         // compacted list of stance contacts (order preserved)
-        const unsigned m = __ballot_sync(kFullMask, st);
+        const unsigned mw = __ballot_sync(kFullMask, st);
+        const unsigned m = HL == 32 ? mw : ((mw >> (half * HL)) & ((1u << (HL & 31)) - 1u));      // the bits of this problem's lanes
         if (st) stIdx[n_stance + __popc(m & ((1u << lane) - 1u))] = c;
         n_stance += __popc(m);
     }
@@ -840,7 +870,7 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
 #pragma unroll
         for (int i = 0; i < 13; i++) x0r[i] = gx0[i];
         const double g0 = x0r[12], dt = P.dt;
-        for (int k = lane; k < N; k += 32) {
+        for (int k = lane; k < N; k += HL) {
             const double kk = (double)(k + 1);
             const double *xr = gxr + k * NS;
             double *Ek = E + 12 * k;
@@ -856,7 +886,7 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
     }
     __syncwarp();
     // start point: weight shared by the stance contacts of each step, clamped into the interior
-    for (int c = lane; c < NCN; c += 32) {
+    for (int c = lane; c < NCN; c += HL) {
         const int k = c / NC;
         int ns = 0;
         for (int j = 0; j < NC; j++) { const double cj = cfl[k * NC + j]; ns += (P.fz_max * cj > P.fz_min * cj) ? 1 : 0; }
@@ -894,17 +924,23 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
     // the last iterations remove; the iteration that stops always runs on an exact one (tests/test_ipm_model_cpu.py).
     bool exact = true;
     const double exact_gap = 1e7 * P.gap_tol;
+    // `frozen`: this problem has stopped.  With one problem per warp that ends the loop; with two, the warp goes on until
+    // both have stopped, the per-contact passes of the frozen one run over zero contacts (n_act) and nothing of its
+    // state changes any more.
+    bool frozen = false;
+    int n_act = n_stance;
 #pragma unroll 1
-    for (it = 0;; it++) {
+    for (it = 0;;) {
         PH(7)
     again:
+        n_act = frozen ? 0 : n_stance;
         double p_gf = 0.0;
-        if (exact) {
+        if (HL == 32 ? exact : __any_sync(kFullMask, exact && !frozen)) {
             // (1) gradient: V <- Bm^T (M W u + h)
-            gradient_sweeps<N, NC>(sm, P, C, lane);
+            gradient_sweeps<N, NC, HL>(sm, P, C, lane);
             PH(0)
             const double *Vt = sm + L_::oV;
-            for (int i = lane; i < n_stance; i += 32) {
+            for (int i = lane; i < (exact ? n_act : 0); i += HL) {
                 const int c = stIdx[i], k = c / NC;
                 const double *vk = Vt + 6 * k, *r = rr + 3 * c, *uc = u + 3 * c;
                 const double g0 = sr * uc[0] + (vk[1] * r[2] - vk[2] * r[1]) + vk[3];
@@ -918,19 +954,20 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         //     predictor t = -Dblk^-1 grad f
         if (!lam_init) {
             // lambda_0 = mu0 / s with mu0 tied to the gradient scale at the start point
-            const double mu0 = fmax(1e-2, 0.1 * wmax(p_gf));
-            for (int i = lane; i < n_stance; i += 32) {
+            const double mu0 = fmax(1e-2, 0.1 * wmax<HL>(p_gf));
+            for (int i = lane; i < n_act; i += HL) {
                 const int c = stIdx[i];
 #pragma unroll
                 for (int j = 0; j < 6; j++) lam[6 * c + j] = mu0 / sl[6 * c + j];
             }
             lam_init = true;
         }
-        double p_gap = 0.0, p_rd = 0.0;
-        for (int i = lane; i < n_stance; i += 32) {
+        double p_gap2[2] = {0.0, 0.0}, p_rd = 0.0;
+        for (int i = lane, odd = 0; i < n_act; i += HL, odd ^= 1) {
             const int c = stIdx[i];
             const double *s6 = sl + 6 * c, *l6 = lam + 6 * c;
             const double g0 = gf[3 * c], g1 = gf[3 * c + 1], g2 = gf[3 * c + 2];
+            double p_gap = (HL == 16 && odd) ? p_gap2[1] : p_gap2[0];        // (see wsum2)
             const double r0 = g0 + l6[0] - l6[1], r1 = g1 + l6[2] - l6[3];
             const double r2 = g2 - mu * (l6[0] + l6[1] + l6[2] + l6[3]) + l6[4] - l6[5];
             p_rd = fmax(p_rd, fmax(fabs(r0), fmax(fabs(r1), fabs(r2))));
@@ -953,31 +990,46 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
             tv[3 * c] = -(Di[0] * g0 + Di[1] * g1 + Di[2] * g2);
             tv[3 * c + 1] = -(Di[1] * g0 + Di[3] * g1 + Di[4] * g2);
             tv[3 * c + 2] = -(Di[2] * g0 + Di[4] * g1 + Di[5] * g2);
+            if (HL == 16 && odd) p_gap2[1] = p_gap; else p_gap2[0] = p_gap;
         }
-        gap = wsum(p_gap) / m_ineq; rdmax = wmax(p_rd);
-        if (!(gap == gap) || !(rdmax == rdmax) || isinf(gap) || isinf(rdmax)) { status = G1MPC_NUMERICAL; break; }
-        if (!exact && (gap <= P.gap_tol || it >= P.max_iter)) { exact = true; __syncwarp(); goto again; }   // never stop on a carried gradient
-        if (gap <= P.gap_tol || n_stance == 0) { status = G1MPC_SOLVED; break; }
-        if (it >= P.max_iter) { status = G1MPC_MAX_ITER; break; }
+        {
+            const double gap_now = wsum2<HL>(p_gap2) / m_ineq, rd_now = wmax<HL>(p_rd);
+            if (!frozen) {
+                gap = gap_now; rdmax = rd_now;
+                if (!(gap == gap) || !(rdmax == rdmax) || isinf(gap) || isinf(rdmax)) { status = G1MPC_NUMERICAL; frozen = true; }
+            }
+        }
+        {
+            // never stop on a carried gradient: evaluate it and look again
+            const bool redo = !frozen && !exact && (gap <= P.gap_tol || it >= P.max_iter);
+            if (HL == 32 ? redo : __any_sync(kFullMask, redo)) { if (redo) exact = true; __syncwarp(); goto again; }
+        }
+        if (!frozen && (gap <= P.gap_tol || n_stance == 0)) { status = G1MPC_SOLVED; frozen = true; }
+        if (!frozen && it >= P.max_iter) { status = G1MPC_MAX_ITER; frozen = true; }
+        if (HL == 32 ? frozen : __all_sync(kFullMask, frozen)) break;
+        n_act = frozen ? 0 : n_stance;
         __syncwarp();
 
         PH(1)
         // (3) S_k, t_k, then the backward Riccati sweep (shared by predictor and corrector)
-        assemble_stage<N, NC, true>(sm, P, C, lane);
+        assemble_stage<N, NC, HL, true>(sm, P, C, lane);
         __syncwarp();
         PH(2)
-        if (!factor_stages<N, NC>(sm, P, C, lane PH_ARGS)) { status = G1MPC_NUMERICAL; break; }
+        if (!factor_stages<N, NC, HL>(sm, P, C, lane PH_ARGS) && !frozen) { status = G1MPC_NUMERICAL; frozen = true; }
+        if (HL == 32 ? frozen : __all_sync(kFullMask, frozen)) break;
+        n_act = frozen ? 0 : n_stance;
         PH(3)
         // (4) predictor.  With x = ds/s:  dl = -lam (1 + x), and the largest feasible step is
         //     1 / max_i max(-x_i, 1 + x_i)  -- no division per constraint.
-        solve_stages<N, NC>(sm, C, lane PH_ARGS);
+        solve_stages<N, NC, HL>(sm, C, lane PH_ARGS);
         PH(4)
         const double *zt = sm + L_::oVa;
-        double p_rmax = 0.0, p_sum = 0.0;
-        for (int i = lane; i < n_stance; i += 32) {
+        double p_rmax = 0.0, p_sum2[2] = {0.0, 0.0};
+        for (int i = lane, odd = 0; i < n_act; i += HL, odd ^= 1) {
             const int c = stIdx[i], k = c / NC;
             const double *z = zt + 6 * k, *r = rr + 3 * c, *Ds = Dst + 3 * c, *l6 = lam + 6 * c;
             double rt[3], X[18], si[6];
+            double p_sum = (HL == 16 && odd) ? p_sum2[1] : p_sum2[0];          // (see wsum2)
 #pragma unroll
             for (int j = 0; j < 6; j++) si[j] = frcp(sl[6 * c + j]);
             rt[0] = -gf[3 * c] - ((z[1] * r[2] - z[2] * r[1]) + z[3]);
@@ -993,10 +1045,11 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
                 prod[6 * c + j] = dsi * dli;
                 p_sum += dsi * dli;
             }
+            if (HL == 16 && odd) p_sum2[1] = p_sum; else p_sum2[0] = p_sum;
         }
-        const double a_aff = fmin(1.0, frcp(wmax(p_rmax)));
+        const double a_aff = fmin(1.0, frcp(wmax<HL>(p_rmax)));
         // sum (s + a ds)(lam + a dl) = (1 - a) s'lam + a^2 ds'dl for the affine direction
-        const double g_aff = ((1.0 - a_aff) * gap * m_ineq + a_aff * a_aff * wsum(p_sum)) / m_ineq;
+        const double g_aff = ((1.0 - a_aff) * gap * m_ineq + a_aff * a_aff * wsum2<HL>(p_sum2)) / m_ineq;
         double sig = g_aff * frcp(gap);
         sig = sig * sig * sig;
         const double sigma_gap = sig * gap;
@@ -1006,7 +1059,7 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         // no effect on iterations with a_aff >= 0.3 (tests/test_ipm_model_cpu.py keeps the two problems).
         const double w2 = fmin(1.0, a_aff * (1.0 / 0.3));
         // (5) corrector right-hand side: t = Dblk^-1 (-grad f + Cb'q),  q = (ds dl - sigma mu)/s
-        for (int i = lane; i < n_stance; i += 32) {
+        for (int i = lane; i < n_act; i += HL) {
             const int c = stIdx[i];
             const double *Ds = Dst + 3 * c, *l6 = lam + 6 * c;
             double q6[6], Di[6], si[6];
@@ -1023,15 +1076,15 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
             for (int j = 0; j < 6; j++) prod[6 * c + j] = q6[j];
         }
         __syncwarp();
-        assemble_stage<N, NC, false>(sm, P, C, lane);
+        assemble_stage<N, NC, HL, false>(sm, P, C, lane);
         __syncwarp();
         PH(5)
-        solve_stages<N, NC>(sm, C, lane PH_ARGS);
+        solve_stages<N, NC, HL>(sm, C, lane PH_ARGS);
         PH(4)
         // (6) combined direction, step length (the stage storage is dead now: ds | dl live there).
         //     dl = -lam (1 + x + q/lam)
         p_rmax = 0.0;
-        for (int i = lane; i < n_stance; i += 32) {
+        for (int i = lane; i < n_act; i += HL) {
             const int c = stIdx[i], k = c / NC;
             const double *z = zt + 6 * k, *r = rr + 3 * c, *Ds = Dst + 3 * c, *l6 = lam + 6 * c, *q6 = prod + 6 * c;
             double rt[3], X[18], Di[6], si[6];
@@ -1061,9 +1114,9 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         // fraction to the boundary: 0.995 while the predictor is blocked, -> 1 quadratically once it is not (a_aff -> 1),
         // so that the last iterations are not held at a factor 200 per step (one iteration fewer on every preset)
         const double eta = fmin(0.99999, fmax(0.995, 1.0 - (1.0 - a_aff) * (1.0 - a_aff)));
-        const double alpha = fmin(1.0, eta * frcp(wmax(p_rmax)));
+        const double alpha = fmin(1.0, eta * frcp(wmax<HL>(p_rmax)));
         // (7) step (same lane -> same contacts as in (6): no barrier needed)
-        for (int i = lane; i < n_stance; i += 32) {
+        for (int i = lane; i < n_act; i += HL) {
             const int c = stIdx[i];
 #pragma unroll
             for (int p = 0; p < 3; p++) {
@@ -1076,25 +1129,33 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
                 sl[6 * c + j] += alpha * dsv[6 * c + j];
             }
         }
-        exact = gap * (1.0 - alpha * (1.0 - sig)) < exact_gap;       // predicted gap of the next iterate
+        if (!frozen) {
+            exact = gap * (1.0 - alpha * (1.0 - sig)) < exact_gap;   // predicted gap of the next iterate
+            it++;
+        }
         __syncwarp();
         PH(6)
     }
 
     // ---- outputs ------------------------------------------------------------------------------------
-    if (status == G1MPC_NUMERICAL) {            // a failed factorisation leaves the scratch in solve-phase state
+    // A failed factorisation leaves the scratch in solve-phase state, and with two problems per warp the one that stopped
+    // first has had its stage storage reused by the other's later iterations: evaluate w, X, V again from the returned u.
+    if (HL == 16 || status == G1MPC_NUMERICAL) {
         __syncwarp();
-        gradient_sweeps<N, NC>(sm, P, C, lane);
+        gradient_sweeps<N, NC, HL>(sm, P, C, lane);
     }
     __syncwarp();
     // here w = W u, X = state response, gf = grad f(u) are consistent with the returned u
-    bad_bounds = __any_sync(kFullMask, bad_bounds);
+    {
+        const unsigned bw = __ballot_sync(kFullMask, bad_bounds != 0);
+        bad_bounds = (HL == 32 ? bw : ((bw >> (half * HL)) & ((1u << (HL & 31)) - 1u))) != 0u;
+    }
     if (bad_bounds && status == G1MPC_SOLVED) status = G1MPC_BAD_BOUNDS;
     // The slacks are carried by the iteration (ds = -Cb du), not recomputed from u, so after ~25 iterations u can sit
     // ~1e-9 N outside an active row (measured at N = 40, nc = 8).  Clamp the returned point back into the pyramid:
     // the change is six orders below the 1e-3 N parity tolerance and makes primal feasibility exact.
     if (status != G1MPC_NUMERICAL) {
-        for (int i = lane; i < n_stance; i += 32) {
+        for (int i = lane; i < n_stance; i += HL) {
             const int c = stIdx[i];
             const double cf = cfl[c], lo = P.fz_min * cf, hi = P.fz_max * cf;
             const double fz = fmin(fmax(u[3 * c + 2], lo), hi), lim = mu * fz;
@@ -1105,24 +1166,31 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         __syncwarp();
     }
     double *gu = io.u_opt + b * NV;
-    for (int i = lane; i < NV; i += 32) gu[i] = u[i];
-    if (io.status && lane == 0) io.status[b] = status;
-    if (io.iters && lane == 0) io.iters[b] = it;
+    for (int i = lane; i < (valid ? NV : 0); i += HL) gu[i] = u[i];
+    if (io.status && lane == 0 && valid) io.status[b] = status;
+    if (io.iters && lane == 0 && valid) io.iters[b] = it;
     const double *wv = sm + L_::oW, *Xs = sm + L_::oXs;
     if (io.resid) {
-        double obj = 0.0, pv = 0.0;
-        for (int i = lane; i < NV; i += 32) obj += 0.5 * sr * u[i] * u[i];
+        double obj2[2] = {0.0, 0.0}, pv = 0.0;      // (two accumulators: see wsum2)
+        for (int i = lane, odd = 0; i < NV; i += HL, odd ^= 1) {
+            const double t = 0.5 * sr * u[i] * u[i];
+            if (HL == 16 && odd) obj2[1] += t; else obj2[0] += t;
+        }
         // 1/2 u'Hu + g'u = 1/2 sr |u|^2 + 1/2 sum sQ (e^2 - E^2),  e = E + X
-        for (int e = lane; e < 12 * N; e += 32) obj += 0.5 * P.scale * P.q[e % 12] * Xs[e] * (2.0 * E[e] + Xs[e]);
-        for (int c = lane; c < NCN; c += 32) {
+        for (int e = lane, odd = 0; e < 12 * N; e += HL, odd ^= 1) {
+            const double t = 0.5 * P.scale * P.q[e % 12] * Xs[e] * (2.0 * E[e] + Xs[e]);
+            if (HL == 16 && odd) obj2[1] += t; else obj2[0] += t;
+        }
+        for (int c = lane; c < NCN; c += HL) {
             const double fx = u[3 * c], fy = u[3 * c + 1], fz = u[3 * c + 2];
             const double cf = cfl[c], lo = P.fz_min * cf, hi = fmax(P.fz_max * cf, lo);
             const double lim = __dmul_rn(mu, fz);                  // the rounded product the clamp above used (no FMA contraction)
             pv = fmax(pv, fmax(fabs(fx) - lim, fabs(fy) - lim));
             pv = fmax(pv, fmax(fz - hi, lo - fz));
         }
-        obj = wsum(obj); pv = wmax(pv);
-        if (lane == 0) {
+        const double obj = wsum2<HL>(obj2);
+        pv = wmax<HL>(pv);
+        if (lane == 0 && valid) {
             double *r = io.resid + b * 4;
             r[0] = gap; r[1] = rdmax; r[2] = fmax(pv, 0.0); r[3] = obj;
         }
@@ -1130,7 +1198,7 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
     if (io.y_opt) {
         // multipliers of the reference's 5 rows per contact (OSQP sign: y<0 at a lower bound)
         double *gy = io.y_opt + b * (5 * NCN);
-        for (int c = lane; c < NCN; c += 32) {
+        for (int c = lane; c < (valid ? NCN : 0); c += HL) {
             double y5[5];
             const double cf = cfl[c];
             if (P.fz_max * cf > P.fz_min * cf) {
@@ -1151,11 +1219,11 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         }
     }
     rollout_rows(io.x_opt + b * (N * NS), io.x_current ? io.x_current + b * NS : nullptr, io.one_rollout ? 1 : N - 1,
-                 sm + L_::oVa, sm + L_::oXs, P.dt, cz, sz, lane);
+                 sm + L_::oVa, sm + L_::oXs, P.dt, cz, sz, lane, HL, valid);
 #ifdef G1MPC_PHASE_CLOCKS
     __syncwarp();
     PH(14)                                          // epilogue: outputs + rollout
-    if (io.y_opt && lane == 0) { for (int i = 0; i < 16; i++) io.y_opt[b * (5 * NCN) + i] = (double)ph_t[i]; }
+    if (io.y_opt && lane == 0 && valid) { for (int i = 0; i < 16; i++) io.y_opt[b * (5 * NCN) + i] = (double)ph_t[i]; }
 #endif
 }
 
