@@ -31,8 +31,8 @@ METRIC = "batched MPC build+solve/sec (N=10, whole box, device-timed)"
 UNIT = "problems/s"
 BATCH = 1024
 # dram__bytes_read.sum + dram__bytes_write.sum of one solve launch at B=1024 from the committed `ncu --set full`
-# capture (profiles/r1_v5_ncu_full_summary.csv): inputs are read once, the 2 MB of outputs stay in L2.
-NCU_TRAFFIC_BYTES = 2830336
+# capture (profiles/r1_v6_ncu_full_summary.csv): inputs are read once, the 2 MB of outputs stay in L2.
+NCU_TRAFFIC_BYTES = 2831360
 WORKLOAD = "configs[1]: 1,024 independent G1 SRBD MPC problems per GPU (cpp_node preset, N=10, nc=4, walking gait schedule)"
 
 
@@ -298,9 +298,9 @@ def main():
                 "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "batch_per_gpu": BATCH, "preset": "cpp_node", "l2": "flushed between timed steps (256 MiB fill)",
-                           "ipm_iters_mean": iters_mean, "kernel": solver.kernel_info()},
+                           "ipm_iters_mean": iters_mean, "kernel": solver.kernel_info(BATCH)},
                 "roofline": {"bound": "fp64", "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach_tf / peak_tf if peak_tf else None,
-                             "traffic": NCU_TRAFFIC_BYTES, "kernel": "v2::srbd_mpc_solve_warp_kernel<10,4>", "flops_per_problem": fl / BATCH,
+                             "traffic": NCU_TRAFFIC_BYTES, "kernel": "v2::srbd_mpc_solve_warp_kernel<10,4,16>", "flops_per_problem": fl / BATCH,
                              "peak_source": "g1mpc_fp64_peak_tflops DFMA microbenchmark, measured in this run (MEASURED_PEAKS.json has no FP64 entry)",
                              "hbm": {"bound": "hbm", "achieved": by / (per_launch_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                                      "frac": by / (per_launch_ms * 1e-3) / 1e9 / hbm_peak, "bytes_per_problem": by / BATCH,
@@ -365,7 +365,7 @@ def extras(solver, preset, dev):
         h1.record(); torch.cuda.synchronize()
         ms_h = h0.elapsed_time(h1) / 3
         sweep["N%d_nc8_B%d" % (n_h, b_h)] = {"problems_per_s": b_h / (ms_h * 1e-3), "ms_per_launch": ms_h, "unsolved": int((info_h["status"] != 0).sum()),
-                                            "ipm_iters_mean": float(info_h["iters"].double().mean()), "kernel": sv.kernel_info()}
+                                            "ipm_iters_mean": float(info_h["iters"].double().mean()), "kernel": sv.kernel_info(b_h)}
         sv.close()
     out["config4_horizon_sweep"] = sweep
     one = [t[:1].contiguous() for t in ins]

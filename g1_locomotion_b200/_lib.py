@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("G1MPC_B200_LIB") or os.path.join(_HERE, "libg1mpc_b200.so")   # override: A/B runs of two builds
 _lib = None
 
-EXPORTS = ["g1mpc_create", "g1mpc_destroy", "g1mpc_solve_batch", "g1mpc_emit_qp_batch", "g1mpc_update_host", "g1mpc_update_host_begin", "g1mpc_update_host_end",
+EXPORTS = ["g1mpc_create", "g1mpc_destroy", "g1mpc_solve_batch", "g1mpc_emit_qp_batch", "g1mpc_update_host", "g1mpc_update_host_begin", "g1mpc_update_host_end", "g1mpc_layout_info",
            "g1mpc_walk_inputs_batch", "g1mpc_wbid_refs_batch", "g1mpc_closed_loop_batch", "g1mpc_kernel_info", "g1mpc_fp64_peak_tflops", "g1mpc_last_error", "g1mpc_abi_version"]
 
 
@@ -67,6 +67,8 @@ def load():
     lib.g1mpc_closed_loop_batch.restype = C.c_int
     lib.g1mpc_kernel_info.argtypes = [vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     lib.g1mpc_kernel_info.restype = C.c_int
+    lib.g1mpc_layout_info.argtypes = [vp, i64, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    lib.g1mpc_layout_info.restype = C.c_int
     lib.g1mpc_fp64_peak_tflops.argtypes = [C.c_int, C.POINTER(C.c_double)]
     lib.g1mpc_fp64_peak_tflops.restype = C.c_int
     lib.g1mpc_last_error.restype = C.c_char_p

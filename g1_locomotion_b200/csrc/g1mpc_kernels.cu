@@ -432,10 +432,12 @@ int g1mpc_kernel_info(const g1mpc_handle *h, int32_t *smem_bytes, int32_t *threa
     return G1MPC_OK;
 }
 
-int g1mpc_solve_batch(g1mpc_handle *h, int64_t B, const double *x0, const double *x_ref, const double *contact,
-                      const double *c_horizon, const double *p_com, const double *x_current, int one_rollout,
-                      double *u_opt, double *x_opt, int32_t *status, int32_t *iters, double *resid, double *y_opt,
-                      void *stream)
+// `load` = number of problems that will be on the device together with this launch (the host API cuts a batch into chunks
+// on several streams): it selects the lane layout, the results do not depend on it
+static int solve_batch_impl(g1mpc_handle *h, int64_t B, int64_t load, const double *x0, const double *x_ref, const double *contact,
+                            const double *c_horizon, const double *p_com, const double *x_current, int one_rollout,
+                            double *u_opt, double *x_opt, int32_t *status, int32_t *iters, double *resid, double *y_opt,
+                            void *stream)
 {
     if (!h || B < 0 || (B > 0 && (!x0 || !x_ref || !contact || !c_horizon || !p_com || !u_opt || !x_opt))) {
         g_last_error = "g1mpc_solve_batch: null argument"; return G1MPC_ERR_INVALID_ARGUMENT;
@@ -445,12 +447,37 @@ int g1mpc_solve_batch(g1mpc_handle *h, int64_t B, const double *x0, const double
     CUDA_TRY(cudaSetDevice(h->device));
     BatchPtrs io{x0, x_ref, contact, c_horizon, p_com, x_current, u_opt, x_opt, resid, y_opt, status, iters, one_rollout};
     const int wpb = h->warps_per_block;
-    const bool two = h->kernel->fn2 && (h->force_ppw == 2 || (h->force_ppw != 1 && B > h->two_above));
+    const bool two = h->kernel->fn2 && (h->force_ppw == 2 || (h->force_ppw != 1 && load > h->two_above));
     if (two)
         h->kernel->fn2<<<(unsigned)((B + 2 * wpb - 1) / (2 * wpb)), kWarpThreads * wpb, 2 * h->kernel->smem * wpb, (cudaStream_t)stream>>>(h->dev, io, (long long)B);
     else
         h->kernel->fn<<<(unsigned)((B + wpb - 1) / wpb), kWarpThreads * wpb, h->kernel->smem * wpb, (cudaStream_t)stream>>>(h->dev, io, (long long)B);
     CUDA_TRY(cudaGetLastError());
+    return G1MPC_OK;
+}
+
+int g1mpc_solve_batch(g1mpc_handle *h, int64_t B, const double *x0, const double *x_ref, const double *contact,
+                      const double *c_horizon, const double *p_com, const double *x_current, int one_rollout,
+                      double *u_opt, double *x_opt, int32_t *status, int32_t *iters, double *resid, double *y_opt,
+                      void *stream)
+{
+    return solve_batch_impl(h, B, B, x0, x_ref, contact, c_horizon, p_com, x_current, one_rollout, u_opt, x_opt, status, iters,
+                            resid, y_opt, stream);
+}
+
+int g1mpc_layout_info(const g1mpc_handle *h, int64_t B, int32_t *problems_per_warp, int32_t *smem_bytes, int32_t *ctas_per_sm)
+{
+    if (!h) return G1MPC_ERR_INVALID_ARGUMENT;
+    const bool two = h->kernel->fn2 && (h->force_ppw == 2 || (h->force_ppw != 1 && B > h->two_above));
+    const int ppw = two ? 2 : 1;
+    if (problems_per_warp) *problems_per_warp = ppw;
+    if (smem_bytes) *smem_bytes = (int32_t)(ppw * h->kernel->smem * h->warps_per_block);
+    if (ctas_per_sm) {
+        int n = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, (const void *)(two ? h->kernel->fn2 : h->kernel->fn), kWarpThreads * h->warps_per_block,
+                                                      ppw * h->kernel->smem * h->warps_per_block);
+        *ctas_per_sm = n;
+    }
     return G1MPC_OK;
 }
 
@@ -554,9 +581,9 @@ int g1mpc_update_host_begin(g1mpc_handle *h, int slot, int64_t B, const double *
             CUDA_TRY(cudaMemcpyAsync(ds, hs, D * (xopt_in ? f.u : f.xo), cudaMemcpyHostToDevice, sp));
         }
         int32_t *ds_i = (int32_t *)(ds + f.st);
-        int rc = g1mpc_solve_batch(h, (int64_t)nb, ds + f.x0, ds + f.xr, ds + f.ct, ds + f.ch, ds + f.pc,
-                                   x_current ? ds + f.xc : nullptr, one_rollout, ds + f.u, ds + f.xo, ds_i, ds_i + nb,
-                                   ds + f.res, nullptr, sp);
+        int rc = solve_batch_impl(h, (int64_t)nb, B, ds + f.x0, ds + f.xr, ds + f.ct, ds + f.ch, ds + f.pc,
+                                  x_current ? ds + f.xc : nullptr, one_rollout, ds + f.u, ds + f.xo, ds_i, ds_i + nb,
+                                  ds + f.res, nullptr, sp);
         if (rc) return rc;
         if (direct_out) {
             CUDA_TRY(cudaMemcpyAsync(x_opt + b0 * N * NS, ds + f.xo, D * nb * N * NS, cudaMemcpyDeviceToHost, sp));

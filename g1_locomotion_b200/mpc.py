@@ -68,10 +68,15 @@ class BatchedMPC:
             raise ValueError(f"{name}: expected shape {tuple(shape)}, got {tuple(t.shape)}")
         return C.c_void_p(t.data_ptr())
 
-    def kernel_info(self):
+    def kernel_info(self, B=None):
+        """Launch configuration of the solve kernel; with B, that of the lane layout a batch of B problems uses."""
         a, b, c = C.c_int32(), C.c_int32(), C.c_int32()
         _lib.check(self._lib.g1mpc_kernel_info(self._h, C.byref(a), C.byref(b), C.byref(c)), "g1mpc_kernel_info")
-        return dict(smem_bytes=a.value, threads=b.value, ctas_per_sm=c.value)
+        if B is None:
+            return dict(smem_bytes=a.value, threads=b.value, ctas_per_sm=c.value)
+        ppw = C.c_int32()
+        _lib.check(self._lib.g1mpc_layout_info(self._h, int(B), C.byref(ppw), C.byref(a), C.byref(c)), "g1mpc_layout_info")
+        return dict(smem_bytes=a.value, threads=b.value, ctas_per_sm=c.value, problems_per_warp=ppw.value)
 
     # -- device API ------------------------------------------------------------------------------
     def update_batch(self, x0, x_ref, contact, c_horizon, p_com, x_current=None, *, one_rollout=False,

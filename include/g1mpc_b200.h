@@ -167,6 +167,14 @@ int g1mpc_closed_loop_batch(g1mpc_handle *h, int64_t B, int32_t ticks, double *x
 /* Dynamic shared memory (bytes) and threads per CTA of the solve kernel for this handle's shape. */
 int g1mpc_kernel_info(const g1mpc_handle *h, int32_t *smem_bytes, int32_t *threads, int32_t *ctas_per_sm);
 
+/*
+ * Lane layout a launch of B problems uses: one problem per warp, or -- for the shapes it is compiled for and above 4
+ * problems per SM -- two (a half-warp each: the per-stage 6x6 factorisations, identical in every lane, are then issued
+ * once for two problems).  Results do not depend on the layout (bit-identical).  smem_bytes / ctas_per_sm are per CTA
+ * of that layout.
+ */
+int g1mpc_layout_info(const g1mpc_handle *h, int64_t B, int32_t *problems_per_warp, int32_t *smem_bytes, int32_t *ctas_per_sm);
+
 /* FP64 FMA throughput microbenchmark (dependent-chain-free DFMA loop on every SM), TFLOP/s. */
 int g1mpc_fp64_peak_tflops(int device, double *tflops);
 

@@ -392,3 +392,27 @@ def test_empty_and_ragged_batches():
         uh, xh, infoh = s.update_host(*[a[:B] for a in full], x_current=full[0][:B])
         assert np.array_equal(uh, u_all[:B].cpu().numpy()) and np.array_equal(xh, x_all[:B].cpu().numpy())
         assert np.array_equal(infoh["status"], info_all["status"][:B].cpu().numpy())
+
+
+def test_two_problems_per_warp_layout_gives_the_same_bits(monkeypatch):
+    """Above 4 problems per SM the solve kernel runs two problems per warp (16 lanes each); G1MPC_PPW forces one layout.
+    Per problem the arithmetic is the same operation for operation (the sums over contacts are ordered by virtual lane,
+    the two trailing A22 columns follow from L and D as the column solve produces them), so everything returned must be
+    bit-identical: forces, states, iteration counts, residuals, multipliers -- odd batch sizes included."""
+    preset = presets.get_preset("cpp_node")
+    monkeypatch.setenv("G1MPC_PPW", "1")
+    s1 = _solver(preset)
+    monkeypatch.setenv("G1MPC_PPW", "2")
+    s2 = _solver(preset)
+    monkeypatch.delenv("G1MPC_PPW")
+    full = list(inputs.random_batch(preset, 2049, seed=5, device="cuda"))
+    walk = _dev(inputs.walking_batch(preset, 256))
+    for ins in (full, walk, [t[:1].contiguous() for t in full], [t[:3].contiguous() for t in full], [t[:0].contiguous() for t in full]):
+        for one, use_xc in ((False, True), (True, False)):
+            xp = torch.full((ins[0].shape[0], 10, 13), 3.0, dtype=torch.float64, device="cuda")
+            a = s1.update_batch(*ins, x_current=ins[0] if use_xc else None, one_rollout=one, x_opt=xp.clone(), want_multipliers=True)
+            b = s2.update_batch(*ins, x_current=ins[0] if use_xc else None, one_rollout=one, x_opt=xp.clone(), want_multipliers=True)
+            assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+            for k in ("status", "iters", "resid", "y"):
+                assert torch.equal(a[2][k], b[2][k]), k
+    assert int((b[2]["status"] != 0).sum()) == 0
