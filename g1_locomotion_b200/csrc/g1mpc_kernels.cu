@@ -394,9 +394,13 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
         if (e != cudaSuccess) { g_last_error = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
     }
     {
-        int sms = 0;
+        int sms = 0, ctas2 = 0;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
         h->two_above = 4LL * sms;
+        // ... and only where it does not cost residency: two-problem CTAs must hold as many problems per SM as one-problem CTAs do
+        // (N = 15: 2 x 84 KB against 5 x 42 KB per SM -> one problem per warp stays)
+        if (ke->fn2) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas2, (const void *)ke->fn2, kWarpThreads * h->warps_per_block, 2 * ke->smem * h->warps_per_block);
+        if (2 * ctas2 < h->ctas_per_sm) h->two_above = 0x7fffffffffffLL;
         const char *f = getenv("G1MPC_PPW");
         h->force_ppw = f ? atoi(f) : 0;
     }
