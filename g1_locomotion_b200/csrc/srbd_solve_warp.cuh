@@ -1163,8 +1163,8 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
             u[3 * c + 1] = fmin(fmax(u[3 * c + 1], -lim), lim);
             u[3 * c + 2] = fz;
         }
-        __syncwarp();
     }
+    __syncwarp();                                   // (outside the branch: with two problems per warp `status` differs per half)
     double *gu = io.u_opt + b * NV;
     for (int i = lane; i < (valid ? NV : 0); i += HL) gu[i] = u[i];
     if (io.status && lane == 0 && valid) io.status[b] = status;
