@@ -114,3 +114,29 @@ def test_closed_loop_matches_cpu_composition(orc):
         assert np.abs(tx[b] - wx).max() <= 1e-6, (b, np.abs(tx[b] - wx).max())
         assert np.abs(tu[b] - wu).max() <= 2e-3, (b, np.abs(tu[b] - wu).max())
     assert np.array_equal(tx[:, 0], x0)
+
+
+def test_closed_loop_of_a_large_fleet_equals_the_small_one():
+    """1,200 walkers use the two-problems-per-warp layout, 6 walkers the one-problem layout: the trajectories of the same
+    walker must be bit-identical in both runs (the layouts return the same bits, every walker is independent)."""
+    from g1_locomotion_b200 import BatchedMPC
+    preset = presets.get_preset("cpp_node")
+    s = BatchedMPC(preset)
+    B, T, dt = 1200, 5, preset["dt"]
+    rng = np.random.default_rng(9)
+    x0 = np.zeros((B, 13))
+    # all walkers start within 0.6 m of the origin: with x_opt = 0 at the first tick the node plants the first swing foot
+    # near the world origin, and a walker far away would get an absurd lever arm (tests/golden/ipm_illconditioned_problems.npz)
+    x0[:, 3] = 0.05 + 0.0005 * np.arange(B); x0[:, 4] = 7.44339342e-05; x0[:, 5] = 5.97983255e-01; x0[:, 9] = 0.35
+    x0[:, 12] = np.float32(-9.80665)
+    x0[:, :12] += rng.normal(0, 0.003, (B, 12))
+    cur = np.zeros((B, 4, 3))
+    cur[:, :, 0] = x0[:, 3:4] + np.array([-0.0293, 0.1406, -0.0293, 0.1406])
+    cur[:, :, 1] = np.array([0.118508, 0.118508, -0.118508, -0.118508])
+    t0 = (rng.integers(0, 30, B) + 0.5) * dt
+    assert s.kernel_info(B)["problems_per_warp"] == 2 and s.kernel_info(6)["problems_per_warp"] == 1
+    big = s.closed_loop(_dev(x0), _dev(cur.reshape(B, 12)), _dev(t0), T)
+    small = s.closed_loop(_dev(x0[:6]), _dev(cur[:6].reshape(6, 12)), _dev(t0[:6]), T)
+    torch.cuda.synchronize()
+    assert int(big["status_any"].abs().sum()) == 0
+    assert torch.equal(big["traj_x"][:6], small["traj_x"]) and torch.equal(big["traj_u"][:6], small["traj_u"])
