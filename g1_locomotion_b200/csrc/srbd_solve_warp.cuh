@@ -265,6 +265,13 @@ __device__ __forceinline__ void ld22(const double *p, double (&v)[22])
 #pragma unroll
     for (int i = 0; i < 11; i++) { const double2 a = q[i]; v[2 * i] = a.x; v[2 * i + 1] = a.y; }
 }
+__device__ __forceinline__ void st21(double *p, const double (&v)[21])
+{
+    double2 *q = reinterpret_cast<double2 *>(p);
+#pragma unroll
+    for (int i = 0; i < 10; i++) q[i] = make_double2(v[2 * i], v[2 * i + 1]);
+    p[20] = v[20];
+}
 __device__ __forceinline__ double dot6(const double (&a)[6], const double (&b)[6])
 {
     const double e = fma(a[4], b[4], fma(a[2], b[2], a[0] * b[0])), o = fma(a[5], b[5], fma(a[3], b[3], a[1] * b[1]));
@@ -416,7 +423,8 @@ template <int N, int NC, int HL>
 __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, const StageC &C, int lane PH_PARAMS)
 {
     using L_ = WLay<N, NC>;
-    double *Ex = sm + L_::oEx;
+    double *Ex = sm + L_::oEx, *PiX = sm + L_::oVb;             // (vB | vC are dead between the assembly and the solve)
+    static_assert(12 * N >= 22, "Pi exchange buffer lives in vB | vC");
     // HL = 32: lanes >= 18 shadow group 2 and never store.  HL = 16 (two problems per warp): groups 0 and 1 as before,
     // lanes 12..15 are columns 0..3 of group 2, and lanes 4, 5 (group 0) take over the P22 update of columns 4, 5.
     const int grp = lane < 18 ? lane / 6 : 2, cb = lane % 6;
@@ -456,7 +464,7 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
 #pragma unroll 1
     for (int k = N - 1; k >= 0; k--) {
         double *St = sm + L_::oRic + k * L_::STG;
-        const double *Sk = sm + L_::oS + L_::SST * k;
+        double *Sk = sm + L_::oS + L_::SST * k;
         // Pi = P22^-1 in closed form (P22 is well conditioned: adjugate blocks are accurate enough), T = Pi + S_k by
         // LDL' (T spans the full range of the barrier weights: the closed form stalls the interior point there --
         // measured at N = 40, nc = 8; tests/test_ipm_model_cpu.py keeps the experiment)
@@ -492,11 +500,16 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
             bsub6(T, col);
         }
         PHF(10)
-        double wv[6];                                           // P12 S col  (groups 0 and 1)
+        // S col without the product S * (small): S Gamma = Pi (I - Gamma) =: Theta (symmetric), S A21 = Pi (P21 - A21), i.e.
+        // v = Pi (c - col) in groups 0 and 1.  (S (Gamma x) loses eps |S| |P22| relative where the barrier weights are
+        // large against P22^-1 -- cond(H) 4e11 stalls on it, tests/golden/ipm_illconditioned_problems.npz -- this form
+        // is exact to eps |Pi| there and costs the same.)
+        double wv[6], v[6];                                     // v = S col,  wv = P12 v
         {
-            double v[6], ld[22], row[6];
-            ld22(Sk, ld);
-            symmv6(ld, col, v);
+            double row[6];
+#pragma unroll
+            for (int i = 0; i < 6; i++) c[i] -= col[i];
+            symmv6(Pi, c, v);
 #pragma unroll
             for (int i = 0; i < 6; i++) { ld6(St + L_::sP12 + 6 * i, row); wv[i] = dot6(row, v); }
         }
@@ -522,6 +535,12 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
         }
         double *Sn = St - L_::STG;                              // slot of stage k-1: receives P12 | P22 of P_k
         __syncwarp();
+        // Theta_k (lower triangle, column cb from group 0) replaces S_k, which nobody reads after this point: the solves
+        // form b_k = Gamma' t - Theta p2 with it
+        if (lane < 6) {
+#pragma unroll
+            for (int i = 0; i < 6; i++) if (i >= cb) Sk[tri(i, 0) + cb] = v[i];
+        }
         PHF(12)
         if (k > 0) {
             // P22 of P_k, column cb = s Q2 + A22 + Phi' M12 + A21 Phi      (group 2)
@@ -623,19 +642,12 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
         }
     }
     PHS(9)
-    // ---- b_k = gt_k - S_k Gamma p2   (lane = stage)
+    // ---- b_k = gt_k - S_k Gamma p2 = gt_k - Theta_k p2   (lane = stage; Theta_k sits where S_k was, see factor_stages)
     for (int k = lane; k < N; k += HL) {
-        const double *St = sm + L_::oRic + k * L_::STG;
-        double p2[6], g[6], row[6], sk[22], sg[6], b[6];
+        double p2[6], sk[22], sg[6], b[6];
         ld6(vD + 6 * k, p2);
-#pragma unroll
-        for (int j = 0; j < 6; j++) {                   // Gamma p2 from the stored columns
-            ld6(St + L_::sGam + 6 * j, row);
-#pragma unroll
-            for (int i = 0; i < 6; i++) g[i] = j == 0 ? row[i] * p2[0] : fma(row[i], p2[j], g[i]);
-        }
         ld22(sm + L_::oS + L_::SST * k, sk);
-        symmv6(sk, g, sg);
+        symmv6(sk, p2, sg);
         ld6(vA + 6 * k, b);
 #pragma unroll
         for (int i = 0; i < 6; i++) b[i] -= sg[i];

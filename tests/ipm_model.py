@@ -172,7 +172,8 @@ def _contact_blocks(D, sr, mu):
 
 
 def solve_ipm(prob, gap_tol=1e-10, max_iter=40, linear="riccati"):
-    """Returns u[N,nc,3], iters, gap.  `linear`: "stage" (what the kernel runs), "riccati" (textbook stage-wise) or "dense" (6N x 6N Woodbury matrix)."""
+    """Returns u[N,nc,3], iters, gap.  `linear`: "stage" (what the kernel runs), "riccati" (textbook stage-wise),
+    "dense" (6N x 6N Woodbury matrix) or "stage_s" (the stage form with S_k Gamma formed as a product: what the kernel ran before Theta_k)."""
     N, nc, mu, sr, bv = prob.N, prob.nc, prob.mu, prob.sr, prob.bv
     M, h = prob.M_h()
     st = prob.stance
@@ -218,8 +219,8 @@ def solve_ipm(prob, gap_tol=1e-10, max_iter=40, linear="riccati"):
         if linear == "riccati":
             fac = RiccatiFactor(prob, S)
             lin_solve = fac.solve
-        elif linear == "stage":
-            fac = StageFactor(prob, S)
+        elif linear in ("stage", "stage_s"):
+            fac = StageFactor(prob, S, theta=linear == "stage")
             lin_solve = fac.solve
         else:
             Sd = np.zeros((6 * N, 6 * N))
@@ -284,31 +285,39 @@ def _ldl(Amat):
 
 
 class StageFactor:
-    def __init__(self, prob, S):
+    """factor_stages of the kernel: Pi = P22^-1, T = Pi + S_k = L D L', Gamma = T^-1 Pi, A21 = Gamma P21, A22 = T^-1;
+    S_k times a column is never formed as a product with S_k: S Gamma = Pi (I - Gamma) =: Theta_k (symmetric) and
+    S A21 = Pi (P21 - A21).  (S (Gamma x) loses eps |S| |P22| relative: cond(H) 4e11 stalls on it,
+    tests/golden/ipm_illconditioned_problems.npz; `theta=False` keeps that form for the test that documents it.)"""
+
+    def __init__(self, prob, S, theta=True):
         N = prob.N
-        self.prob, self.S = prob, S
+        self.prob, self.S, self.theta = prob, S, theta
         sq = prob.s * prob.q[:12]
         Phi = prob.Phi
         P11, P12, P22 = np.diag(sq[:6]), np.zeros((6, 6)), np.diag(sq[6:])
-        self.Gam, self.Psi, self.P12, self.P22 = [None] * N, [None] * N, [None] * N, [None] * N
+        self.Gam, self.Psi, self.P12, self.P22, self.Theta = [None] * N, [None] * N, [None] * N, [None] * N, [None] * N
         self.ok = True
         for k in range(N - 1, -1, -1):
-            L, d = _ldl(P22)
-            K = np.diag(1.0 / d) + L.T @ S[k] @ L
-            L2, d2 = _ldl(K)
-            if np.any(d <= 0) or np.any(d2 <= 0):
+            Pi = np.linalg.inv(P22)
+            Pi = 0.5 * (Pi + Pi.T)
+            L, d = _ldl(Pi + S[k])
+            if np.any(np.linalg.eigvalsh(P22) <= 0) or np.any(d <= 0):
                 self.ok = False
-
-            def gam_apply(col):                          # Gamma col = L K^-1 D^-1 L^-1 col
-                x = np.linalg.solve(L, col) / d
-                x = np.linalg.solve(L2, x) / d2
-                return L @ np.linalg.solve(L2.T, x)
-            Gam = np.column_stack([gam_apply(np.eye(6)[:, b]) for b in range(6)])
-            A21 = np.column_stack([gam_apply(P12.T[:, a]) for a in range(6)])
-            A22 = np.column_stack([gam_apply(P22[:, b]) for b in range(6)])
-            Psi = P12 @ (S[k] @ Gam)
-            A11 = P11 - P12 @ (S[k] @ A21)
-            self.Gam[k], self.Psi[k], self.P12[k], self.P22[k] = Gam, Psi, P12, P22
+            tinv = lambda col: np.linalg.solve(L.T, np.linalg.solve(L, col) / d)
+            Gam = np.column_stack([tinv(Pi[:, b]) for b in range(6)])
+            A21 = np.column_stack([tinv(Pi @ P12.T[:, a]) for a in range(6)])
+            A22 = np.column_stack([tinv(np.eye(6)[:, b]) for b in range(6)])
+            if theta:
+                Theta = np.tril(Pi @ (np.eye(6) - Gam))              # the kernel keeps the lower triangle
+                Theta = Theta + np.tril(Theta, -1).T
+                Psi = P12 @ (Pi @ (np.eye(6) - Gam))
+                A11 = P11 - P12 @ (Pi @ (P12.T - A21))
+            else:
+                Theta = None
+                Psi = P12 @ (S[k] @ Gam)
+                A11 = P11 - P12 @ (S[k] @ A21)
+            self.Gam[k], self.Psi[k], self.P12[k], self.P22[k], self.Theta[k] = Gam, Psi, P12, P22, Theta
             A12 = A21.T
             M12 = A12 + A11 @ Phi
             P22n = np.diag(sq[6:]) + A22 + Phi.T @ M12 + A21 @ Phi
@@ -326,7 +335,7 @@ class StageFactor:
         for k in range(N - 1, -1, -1):                   # backward sweep: one 12x6 mat-vec on the chain
             p2s[k] = p2
             g = self.Gam[k] @ p2
-            b[k] = gt[k] - self.S[k] @ g                 # (off the chain)
+            b[k] = gt[k] - (self.Theta[k] @ p2 if self.theta else self.S[k] @ g)        # (off the chain)
             p1 = p1 - self.Psi[k] @ p2 + c1[k]
             p2 = Phi.T @ p1 + g + c2[k]
         y1 = np.zeros(6); y2 = np.zeros(6)

@@ -125,9 +125,9 @@ def test_closed_loop_of_a_large_fleet_equals_the_small_one():
     B, T, dt = 1200, 5, preset["dt"]
     rng = np.random.default_rng(9)
     x0 = np.zeros((B, 13))
-    # all walkers start within 0.6 m of the origin: with x_opt = 0 at the first tick the node plants the first swing foot
-    # near the world origin, and a walker far away would get an absurd lever arm (tests/golden/ipm_illconditioned_problems.npz)
-    x0[:, 3] = 0.05 + 0.0005 * np.arange(B); x0[:, 4] = 7.44339342e-05; x0[:, 5] = 5.97983255e-01; x0[:, 9] = 0.35
+    # walkers up to 12 m from the origin: with x_opt = 0 at the first tick the node plants the first swing foot near the
+    # WORLD origin, so the far ones get lever arms of metres and cond(H) up to 4e11 (tests/golden/ipm_illconditioned_problems.npz)
+    x0[:, 3] = 0.05 + 0.01 * np.arange(B); x0[:, 4] = 7.44339342e-05; x0[:, 5] = 5.97983255e-01; x0[:, 9] = 0.35
     x0[:, 12] = np.float32(-9.80665)
     x0[:, :12] += rng.normal(0, 0.003, (B, 12))
     cur = np.zeros((B, 4, 3))

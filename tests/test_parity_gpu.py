@@ -333,10 +333,10 @@ def test_two_cycle_problems_of_config5_are_solved(orc):
         assert np.abs(u[b].cpu().numpy().ravel() - xs).max() <= GRF_TOL
 
 
-def test_illconditioned_problems_are_flagged_not_silently_wrong(orc):
-    """cond(H) 4e11 (a stance foot planted 11 m from the body, see tests/test_ipm_model_cpu.py): beyond what the stage
-    factorisation resolves in FP64.  The kernel must either solve them to tolerance or say so: status MAX_ITER, the gap it
-    reached in resid[0], forces still within 0.5 N of the exact minimiser and inside the friction pyramids."""
+def test_illconditioned_problems_are_solved(orc):
+    """cond(H) 4e11 (a stance foot planted 11 m from the body, see tests/test_ipm_model_cpu.py): solved like the dense
+    model solves them, in at most 25 iterations, to the exact minimiser.  (Regression: with S_k (Gamma p2) formed as a
+    product in the solves the kernel stalled at a gap of 1e-3 and returned G1MPC_MAX_ITER.)"""
     import os
     z = np.load(os.path.join(os.path.dirname(__file__), "golden", "ipm_illconditioned_problems.npz"))
     preset = presets.get_preset("cpp_node")
@@ -345,17 +345,14 @@ def test_illconditioned_problems_are_flagged_not_silently_wrong(orc):
     s = _solver(preset)
     ins = _dev(arrs)
     u, x, info = s.update_batch(*ins, x_current=ins[0])
-    st, res = info["status"].cpu().numpy(), info["resid"].cpu().numpy()
+    assert int((info["status"] != 0).sum()) == 0
+    assert int(info["iters"].max()) <= 25
+    assert float(info["resid"][:, 0].max()) <= 1e-10 and float(info["resid"][:, 2].max()) == 0.0
     for b in range(arrs[0].shape[0]):
         m = orc.build(p, *[a[b] for a in arrs])
         xs, _, cert = orc.qp_exact(p, m["H"], m["g"], arrs[2][b])
         assert cert["rc"] == 0
-        err = np.abs(u[b].cpu().numpy().ravel() - xs).max()
-        if st[b] == 0:
-            assert err <= GRF_TOL and res[b, 0] <= 1e-10
-        else:
-            assert st[b] == 1 and res[b, 0] > 1e-10 and err <= 0.5, (st[b], res[b], err)      # G1MPC_MAX_ITER, honest gap
-        assert res[b, 2] == 0.0                                                                 # never outside the bounds
+        assert np.abs(u[b].cpu().numpy().ravel() - xs).max() <= GRF_TOL
 
 
 @pytest.mark.parametrize("pin", [True, False])
