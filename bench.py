@@ -388,6 +388,25 @@ def extras(solver, preset, dev):
                               "timing": "CUDA events around one B=1 call of BatchedMPC.update_batch (host call overhead inside)",
                               "device_p50": float(np.percentile(dlat, 50)), "device_p99": float(np.percentile(dlat, 99)),
                               "device_timing": "same, launch queued behind a spin kernel: the kernel alone", "ipm_iters": int(info1["iters"][0])}
+    # config 1 (BASELINE.json configs[0]): the states of the straight-line walking demo, one B=1 call per control tick as
+    # the node makes them (mpc_to_wbid_node.cpp:494); each tick timed once behind the spin kernel (kernel alone) and once bare
+    ticks = [torch.as_tensor(a, dtype=torch.float64, device=dev) for a in inputs.walking_replay(preset, n_ticks=200)]
+    rk, rh, rit = [], [], []
+    for rep in range(3):
+        for t in range(ticks[0].shape[0]):
+            tick = [a[t:t + 1] for a in ticks]
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda._sleep(300000)
+            a.record(); _, _, info_t = solver.update_batch(*tick, x_current=tick[0], want_resid=False); b.record(); b.synchronize()
+            c, d = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            c.record(); solver.update_batch(*tick, x_current=tick[0], want_resid=False); d.record(); d.synchronize()
+            if rep > 0:
+                rk.append(a.elapsed_time(b) * 1e3); rh.append(c.elapsed_time(d) * 1e3); rit.append(int(info_t["iters"][0]))
+    out["single_solve_walking_replay_us"] = {
+        "workload": "configs[0]: 200 consecutive ticks of the straight-line walking demo, one problem per call, 2 timed passes",
+        "device_p50": float(np.percentile(rk, 50)), "device_p99": float(np.percentile(rk, 99)), "device_min": float(np.min(rk)),
+        "p50": float(np.percentile(rh, 50)), "p99": float(np.percentile(rh, 99)), "solves": len(rk),
+        "ipm_iters_p50": float(np.percentile(rit, 50)), "ipm_iters_max": int(np.max(rit)), "ipm_iters_mean": float(np.mean(rit))}
     return out
 
 

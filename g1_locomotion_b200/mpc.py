@@ -93,7 +93,10 @@ class BatchedMPC:
         if u_opt is None:
             u_opt = torch.empty(B, N, nu, device=self.device, dtype=torch.float64)
         if x_opt is None:
-            x_opt = torch.zeros(B, N, NS, device=self.device, dtype=torch.float64)   # initMatrices zero-fills x_opt_
+            # initMatrices zero-fills x_opt_; the rollout overwrites every row when x_current is given and one_rollout
+            # is off (mpc.py:379-386), so the fill kernel is only queued when a row would survive
+            alloc = torch.empty if (x_current is not None and not one_rollout) else torch.zeros
+            x_opt = alloc(B, N, NS, device=self.device, dtype=torch.float64)
         pu = self._chk(u_opt, (B, N, nu), "u_opt"); pxo = self._chk(x_opt, (B, N, NS), "x_opt")
         status = torch.empty(B, device=self.device, dtype=torch.int32)
         iters = torch.empty(B, device=self.device, dtype=torch.int32)
