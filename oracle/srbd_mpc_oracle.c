@@ -18,7 +18,10 @@
  *               quadratic programs", Math. Prog. Comp. 2020; constants as in OSQP 0.6.x) with the
  *               settings the reference call sites leave at default.  orc_qp_exact() returns the
  *               unique minimiser x* of the same QP (active-set solve + KKT certificate), which is
- *               what the "GRFs within 1e-3 N" criterion is checked against.
+ *               what the "GRFs within 1e-3 N" criterion is checked against.  x* itself is cross-checked
+ *               against an independent third-party solver, HiGHS' convex-QP code as bundled with scipy
+ *               (tests/highs_qp.py, tests/test_oracle_qp.py): same optimum to 1e-11 relative, same
+ *               active rows, x* never the worse point.
  *
  * Storage: every matrix is dense, row-major, double.
  */

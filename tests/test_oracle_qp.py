@@ -77,3 +77,29 @@ def test_update_batch_threads_agree(orc):
     u2, x2, it2 = orc.update_batch(p, *batch, x_current=batch[0], nthreads=4)
     assert np.array_equal(u1, u2) and np.array_equal(x1, x2) and np.array_equal(it1, it2)
     assert np.all(x1[:, 0] == batch[0])
+
+
+@pytest.mark.parametrize("pname,kind,over", [("cpp_node", "walk", {}), ("cpp_node", "random", {}),
+                                             ("python_default", "random", {"horizon": 10}), ("cpp_node", "random", {"num_contacts": 8})])
+def test_exact_minimiser_agrees_with_highs_qp(orc, pname, kind, over):
+    """The exact minimiser x* against an independent third-party solver: HiGHS' convex-QP solver (bundled with scipy) on
+    the reference-built H, g, Acon, l, u.  Same optimal value to 1e-11 relative, x* never the worse point, and the
+    forces agree to 2e-2 N -- the accuracy HiGHS reaches on cond(H) ~ 3e8 (its point differs from x* along the directions
+    where H is cost_scale r_weight = 2e-3, which move the objective by 1e-7 of 2e6)."""
+    import highs_qp
+    if not highs_qp.available():
+        pytest.skip("scipy without the bundled HiGHS core")
+    for preset, p, args, m in _problems(orc, pname, 4, 1000 if kind == "walk" else 7, kind, **over):
+        xs, _, info = orc.qp_exact(p, m["H"], m["g"], args[2])
+        assert info["rc"] == 0
+        xh, yh, status = highs_qp.solve(m["H"], m["g"], m["Acon"], m["l"], m["u"])
+        assert status.endswith("kOptimal"), status
+        f = lambda x: 0.5 * x @ m["H"] @ x + m["g"] @ x          # noqa: E731
+        assert f(xs) <= f(xh) + 1e-12 * abs(f(xs))
+        assert abs(f(xh) - f(xs)) <= 1e-11 * abs(f(xs))
+        assert np.abs(xh - xs).max() <= 2e-2
+        # rows HiGHS holds active (non-zero dual) are at their bound at x* as well
+        ax = m["Acon"] @ xs
+        act = np.abs(yh) > 1e-6 * (1.0 + np.abs(yh).max())
+        at_bound = np.minimum(np.abs(ax - m["l"]), np.abs(m["u"] - ax)) <= 1e-6
+        assert np.all(at_bound[act])
