@@ -157,6 +157,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the config-3 throughput and B=1 latency extras")
+    ap.add_argument("--config5", action="store_true",
+                    help="BASELINE.json configs[4] instead of the headline: 2^20 random problems cut into contiguous shards over the "
+                         "ranks (strong scaling), generated on the device, one result gather; prints its own JSON line")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -189,6 +192,12 @@ def main():
     preset = presets.get_preset("cpp_node")
     N, nc = preset["horizon"], preset["num_contacts"]
     solver = BatchedMPC(preset, device=local_rank)
+    if args.config5:
+        run_config5(args, solver, preset, dev, rank, world)
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
     host_batch = inputs.walking_batch(preset, BATCH, seed0=1000 + 100000 * rank)
     ins = [torch.as_tensor(a, dtype=torch.float64).to(dev) for a in host_batch]
     u_opt = torch.empty(BATCH, N, 3 * nc, device=dev, dtype=torch.float64)
@@ -324,6 +333,54 @@ def main():
         dist.destroy_process_group()
 
 
+def run_config5(args, solver, preset, dev, rank, world):
+    """Config 5: 2^20 problems of the config-3 distribution, contiguous shard per rank generated on the
+    device with the shard's seed (13 + rank) over sharding.shard_range, one solve launch per rank, then the 200 B/problem
+    WBID payload gathered over NCCL (sharding.gather_results).  Strong scaling: the total is fixed, value = 2^20 / max over ranks."""
+    import torch
+    import torch.distributed as dist
+    from g1_locomotion_b200 import inputs, sharding
+    total = 1 << 20
+    lo, hi = sharding.shard_range(total, rank, world)
+    ins = list(inputs.random_batch(preset, hi - lo, seed=13 + rank, device=dev))
+    N, nc = preset["horizon"], preset["num_contacts"]
+    u_opt = torch.empty(hi - lo, N, 3 * nc, device=dev, dtype=torch.float64)
+    x_opt = torch.empty(hi - lo, N, 13, device=dev, dtype=torch.float64)
+    steps, warm = min(args.steps, 5), 2
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+          for _ in range(steps)]
+    for k in range(warm + steps):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        if k >= warm:
+            ev[k - warm][0].record()
+        _, _, info = solver.update_batch(*ins, x_current=ins[0], u_opt=u_opt, x_opt=x_opt, want_resid=False)
+        if k >= warm:
+            ev[k - warm][1].record()
+        gathered = sharding.gather_results(sharding.wbid_payload(u_opt, x_opt), total) if world > 1 else sharding.wbid_payload(u_opt, x_opt)
+        if k >= warm:
+            ev[k - warm][2].record()
+    torch.cuda.synchronize()
+    assert gathered.shape[0] == total
+    solve_ms = sum(a.elapsed_time(b) for a, b, _ in ev) / steps
+    gather_ms = sum(b.elapsed_time(c) for _, b, c in ev) / steps
+    t = torch.tensor([solve_ms, gather_ms, float((info["status"] != 0).sum()), float(info["iters"].double().sum())], device=dev, dtype=torch.float64)
+    mx = t.clone()
+    if world > 1:
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    if rank == 0:
+        print(json.dumps({"metric": "config 5: 2^20-problem batch sharded across the GPUs of one box (build+solve/sec, device-timed)",
+                          "value": total / (float(mx[0]) * 1e-3), "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warm,
+                          "ms_per_step": float(mx[0]), "gather_ms": float(mx[1]), "value_with_gather": total / ((float(mx[0]) + float(mx[1])) * 1e-3),
+                          "higher_is_better": True, "scaling": "strong", "dtype": "f64", "data": "synthetic",
+                          "config": {"workload": "configs[4]: 1,048,576 random problems (config-3 distribution, seed 13 + rank per shard), "
+                                                 "contiguous shards, inputs generated on the device (far larger than L2)",
+                                     "problems_per_gpu": hi - lo, "gather_bytes": total * 200, "kernel": solver.kernel_info(hi - lo)},
+                          "unsolved": int(t[2]), "ipm_iters_mean": float(t[3]) / total}), flush=True)
+
+
 def _fp64_peak(index):
     import ctypes as C
     from g1_locomotion_b200 import _lib
@@ -392,21 +449,27 @@ def extras(solver, preset, dev):
     # config 1 (BASELINE.json configs[0]): the states of the straight-line walking demo, one B=1 call per control tick as
     # the node makes them (mpc_to_wbid_node.cpp:494); each tick timed once behind the spin kernel (kernel alone) and once bare
     ticks = [torch.as_tensor(a, dtype=torch.float64, device=dev) for a in inputs.walking_replay(preset, n_ticks=200)]
-    rk, rh, rit = [], [], []
-    for rep in range(3):
+    rk, rh, rw, rit = [], [], [], []
+    for rep in range(6):
         for t in range(ticks[0].shape[0]):
             tick = [a[t:t + 1] for a in ticks]
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             torch.cuda._sleep(300000)
             a.record(); _, _, info_t = solver.update_batch(*tick, x_current=tick[0], want_resid=False); b.record(); b.synchronize()
             c, d = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            w0 = time.perf_counter()
             c.record(); solver.update_batch(*tick, x_current=tick[0], want_resid=False); d.record(); d.synchronize()
+            w1 = time.perf_counter()
             if rep > 0:
-                rk.append(a.elapsed_time(b) * 1e3); rh.append(c.elapsed_time(d) * 1e3); rit.append(int(info_t["iters"][0]))
+                rk.append(a.elapsed_time(b) * 1e3); rh.append(c.elapsed_time(d) * 1e3); rw.append((w1 - w0) * 1e6)
+                rit.append(int(info_t["iters"][0]))
     out["single_solve_walking_replay_us"] = {
-        "workload": "configs[0]: 200 consecutive ticks of the straight-line walking demo, one problem per call, 2 timed passes",
+        "workload": "configs[0]: 200 consecutive ticks of the straight-line walking demo, one problem per call, 5 timed passes after one warm-up pass",
         "device_p50": float(np.percentile(rk, 50)), "device_p99": float(np.percentile(rk, 99)), "device_min": float(np.min(rk)),
         "p50": float(np.percentile(rh, 50)), "p99": float(np.percentile(rh, 99)), "solves": len(rk),
+        "wall_p50": float(np.percentile(rw, 50)), "wall_p99": float(np.percentile(rw, 99)),
+        "timing": "device_*: CUDA events, launch queued behind a spin kernel (kernel alone); p50/p99: CUDA events around the bare "
+                  "Python call; wall_*: host clock from the call to the end of the event synchronize (launch and sync included)",
         "ipm_iters_p50": float(np.percentile(rit, 50)), "ipm_iters_max": int(np.max(rit)), "ipm_iters_mean": float(np.mean(rit))}
     return out
 
