@@ -462,3 +462,19 @@ def test_two_problems_per_warp_layout_gives_the_same_bits(monkeypatch):
             for k in ("status", "iters", "resid", "y"):
                 assert torch.equal(a[2][k], b[2][k]), k
     assert int((b[2]["status"] != 0).sum()) == 0
+
+
+def test_bench_config5_line():
+    """`bench.py --config5` on one GPU: the full 2^20-problem batch of BASELINE.json configs[4] as a single shard; one JSON
+    line, nothing unsolved, above north_star's 1e6 problems/s."""
+    import json, os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")}
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--config5", "--steps", "1"], capture_output=True,
+                         text=True, timeout=600, env=env, cwd=root)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["scaling"] == "strong" and d["n_gpus"] == 1 and d["config"]["problems_per_gpu"] == 1 << 20
+    assert d["unsolved"] == 0 and d["value"] > 1e6
