@@ -31,9 +31,9 @@ METRIC = "batched MPC build+solve/sec (N=10, whole box, device-timed)"
 UNIT = "problems/s"
 BATCH = 1024
 # dram__bytes_read.sum + dram__bytes_write.sum of one solve launch at B=1024 from the committed `ncu --set full`
-# capture (profiles/r1_v7_ncu_full_summary.csv: 2.828544 MB read, 0 B written): inputs are read once, the 2 MB of
+# capture (profiles/r1_v8_ncu_full_summary.csv: 2.827520 MB read, 0 B written): inputs are read once, the 2 MB of
 # outputs stay in L2.
-NCU_TRAFFIC_BYTES = 2828544
+NCU_TRAFFIC_BYTES = 2827520
 WORKLOAD = "configs[1]: 1,024 independent G1 SRBD MPC problems per GPU (cpp_node preset, N=10, nc=4, walking gait schedule)"
 
 

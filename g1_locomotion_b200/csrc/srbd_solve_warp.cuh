@@ -356,8 +356,7 @@ __device__ __forceinline__ void assemble_stage(double *sm, const DevParams &P, c
             tf[0] += tv[0]; tf[1] += tv[1]; tf[2] += tv[2];
             if (WITH_S) {
                 double Di[6];
-                const double *Ds = sm + L_::oDst + 3 * c, *l6 = sm + L_::oLam + 6 * c, *s6 = sm + L_::oSl + 6 * c;
-                contact_dinv(l6[0] * frcp(s6[0]), l6[1] * frcp(s6[1]), l6[2] * frcp(s6[2]), l6[3] * frcp(s6[3]), Ds[0], Ds[1], Ds[2], P.mu, Di);
+                ld6(sm + L_::oProd + 6 * c, Di);        // Dblk^-1 of this iteration, left there by the per-contact pass (2)
                 const double D00 = Di[0], D01 = Di[1], D02 = Di[2], D11 = Di[3], D12 = Di[4], D22 = Di[5];
                 // RD = skew(r) Dinv
                 const double a00 = -r2 * D01 + r1 * D02, a01 = -r2 * D11 + r1 * D12, a02 = -r2 * D12 + r1 * D22;
@@ -999,6 +998,7 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
             Ds[0] = ia; Ds[1] = ib; Ds[2] = id2;
             double Di[6];
             contact_dinv(D[0], D[1], D[2], D[3], ia, ib, id2, mu, Di);
+            st6(prod + 6 * c, Di);                  // for the assembly of S_k (prod is dead from the step to the predictor pass)
             tv[3 * c] = -(Di[0] * g0 + Di[1] * g1 + Di[2] * g2);
             tv[3 * c + 1] = -(Di[1] * g0 + Di[3] * g1 + Di[4] * g2);
             tv[3 * c + 2] = -(Di[2] * g0 + Di[4] * g1 + Di[5] * g2);
