@@ -446,6 +446,7 @@ def extras(solver, preset, dev):
                               "timing": "CUDA events around one B=1 call of BatchedMPC.update_batch (host call overhead inside)",
                               "device_p50": float(np.percentile(dlat, 50)), "device_p99": float(np.percentile(dlat, 99)),
                               "device_timing": "same, launch queued behind a spin kernel: the kernel alone", "ipm_iters": int(info1["iters"][0])}
+    out["next_rows"] = next_rows(solver, preset, dev)
     # config 1 (BASELINE.json configs[0]): the states of the straight-line walking demo, one B=1 call per control tick as
     # the node makes them (mpc_to_wbid_node.cpp:494); each tick timed once behind the spin kernel (kernel alone) and once bare
     ticks = [torch.as_tensor(a, dtype=torch.float64, device=dev) for a in inputs.walking_replay(preset, n_ticks=200)]
@@ -471,6 +472,72 @@ def extras(solver, preset, dev):
         "timing": "device_*: CUDA events, launch queued behind a spin kernel (kernel alone); p50/p99: CUDA events around the bare "
                   "Python call; wall_*: host clock from the call to the end of the event synchronize (launch and sync included)",
         "ipm_iters_p50": float(np.percentile(rit, 50)), "ipm_iters_max": int(np.max(rit)), "ipm_iters_mean": float(np.mean(rit))}
+    return out
+
+
+def next_rows(solver, preset, dev):
+    """SURVEY 8f rows on the device, each against the HBM roofline of its own algorithmic bytes: the input generator
+    (g1mpc_walk_inputs_batch), the WBID output adaptor (g1mpc_wbid_refs_batch), and the closed loop of many walkers
+    (g1mpc_closed_loop_batch: generator -> solve -> advance per tick)."""
+    import torch
+    B, N = 65536, preset["horizon"]
+    f64 = dict(device=dev, dtype=torch.float64)
+    gen = torch.Generator(device=dev); gen.manual_seed(5)
+
+    def fleet(b, spread=512):
+        x0 = torch.zeros(b, 13, **f64)
+        x0[:, 3] = 0.05 + 0.35 * 0.05 * (torch.arange(b, device=dev) % spread)
+        x0[:, 4], x0[:, 5], x0[:, 9], x0[:, 12] = 7.44339342e-05, 5.97983255e-01, 0.35, float(np.float32(-9.80665))
+        x0[:, 0:12] += 0.003 * torch.randn(b, 12, generator=gen, **f64)
+        cur = torch.zeros(b, 4, 3, **f64)
+        cur[:, :, 0] = x0[:, 3:4] + torch.tensor([-0.0293, 0.1406, -0.0293, 0.1406], **f64)
+        cur[:, :, 1] = torch.tensor([0.118508, 0.118508, -0.118508, -0.118508], **f64)
+        t = ((torch.arange(b, device=dev) % 40).double() + 0.5) * preset["dt"]
+        xp = torch.zeros(b, N, 13, **f64)
+        xp[:, :, 3] = x0[:, 3:4] + 0.35 * preset["dt"] * torch.arange(N, device=dev)
+        xp[:, :, 4], xp[:, :, 9] = 7.44339342e-05, 0.35
+        return x0, cur.reshape(b, 12).contiguous(), t, xp
+
+    def timed(fn, reps=20):
+        for _ in range(3):
+            r = fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            r = fn()
+        b.record(); torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps, r
+
+    try:
+        peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0)
+    except Exception:
+        peak = 6650.0
+    out = {}
+    x0, cur, t, xp = fleet(B)
+    x_ref = torch.zeros(B, N, 13, **f64)
+    ms, (x_ref, contact, c_hor, p_com) = timed(lambda: solver.walk_inputs(x0, cur, t, xp, x_ref=x_ref))
+    by = 8 * (13 + 12 + 1 + 13 * N) + 8 * (7 * N + 4 * N + 12 * N + 3 * N)      # x0, contact points, time, previous x_opt in; 26 N doubles out
+    out["walk_inputs"] = {"problems": B, "ms_per_launch": ms, "problems_per_s": B / (ms * 1e-3), "bytes_per_problem": by,
+                          "hbm": {"achieved": B * by / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "frac": B * by / (ms * 1e-3) / 1e9 / peak},
+                          "note": "the call also allocates its three output tensors (torch.empty) inside the event pair"}
+    u, x, info = solver.update_batch(x0, x_ref, contact, c_hor, p_com, x_current=x0, want_resid=False)
+    feet = cur.reshape(B, 4, 3).contiguous()
+    ms, _ = timed(lambda: solver.wbid_refs(u, x, feet, 35.0))
+    by = 8 * (12 + 13 + 12) + 8 * 42          # first-step forces, x_opt[1], foot positions in; 42 doubles out
+    out["wbid_refs"] = {"problems": B, "ms_per_launch": ms, "problems_per_s": B / (ms * 1e-3), "bytes_per_problem": by,
+                        "hbm": {"achieved": B * by / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "frac": B * by / (ms * 1e-3) / 1e9 / peak},
+                        "note": "reads two rows of u_opt/x_opt per problem: 32-byte sectors touched are 2,104 B in, 336 B out"}
+    Bw, T = 4096, 20
+    # the walkers start where the demo starts (the node's first Raibert point is computed from x_opt = 0, i.e. near the world
+    # origin); x_ref and x_opt are carried from call to call like the node's members
+    x0, cur, t, _ = fleet(Bw, spread=8)
+    xr, xo = torch.zeros(Bw, N, 13, **f64), torch.zeros(Bw, N, 13, **f64)
+    ms, res = timed(lambda: solver.closed_loop(x0, cur, t, T, x_ref=xr, x_opt=xo, record=False), reps=3)
+    out["closed_loop"] = {"walkers": Bw, "ticks": T, "ms_per_call": ms, "walker_ticks_per_s": Bw * T / (ms * 1e-3),
+                          "launches_per_tick": 3, "unsolved_walkers": int((res["status_any"] != 0).sum()),
+                          "status_any_values": torch.unique(res["status_any"]).tolist(), "total_ticks_simulated": 6 * T,
+                          "note": "walk_inputs -> solve (x_current = x0) -> advance per tick, no host round trip; state advances across calls"}
     return out
 
 
