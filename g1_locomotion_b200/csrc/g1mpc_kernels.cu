@@ -30,7 +30,7 @@ constexpr int kWarpThreads = 32;   // one warp per problem
 thread_local std::string g_last_error;
 
 struct DevParams {
-    double mu, fz_min, fz_max, dt, bv, weight, sr, scale, r_weight, gap_tol;
+    double mu, fz_min, fz_max, dt, bv, weight, sr, scale, r_weight, gap_tol, dual_tol, warm_margin, warm_mu0;
     double Ib[9];
     double q[13];
     int max_iter;
@@ -41,6 +41,8 @@ struct BatchPtrs {
     double *u_opt, *x_opt, *resid, *y_opt;
     int32_t *status, *iters;
     int one_rollout;
+    const double *u_warm;       // [B,N,3nc] a previous solution to start from, or null (cold start)
+    int warm_shift;             // stages the horizon has moved since that solution (closed loop: 1)
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -268,6 +270,43 @@ __global__ void __launch_bounds__(256) srbd_mpc_emit_kernel(const DevParams P, c
     }
 }
 
+// computeRollout (mpc.cpp:427-446) of a given u_opt: one thread per problem, the recurrence as the reference runs it
+// (x_i = A x_{i-1} + B_{i-1} u_{i-1} with A = I + dt Ac, mpc.cpp:196-211, and the B_i of mpc.cpp:213-254).
+__global__ void __launch_bounds__(128) srbd_rollout_kernel(const DevParams P, const double *x_ref, const double *c_hor, const double *p_com,
+                                                            const double *u_opt, const double *x_current, int one_rollout, double *x_opt,
+                                                            long long B, int N, int NC)
+{
+    const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    Lin lin;
+    linearise(P, x_ref + b * (N * NS), N, lin);
+    double *xo = x_opt + b * (N * NS);
+    double x[NS];
+    for (int r = 0; r < NS; r++) x[r] = x_current ? x_current[b * NS + r] : xo[r];
+    if (x_current) for (int r = 0; r < NS; r++) xo[r] = x[r];                  // mpc.cpp:430-433
+    const int last = one_rollout ? 1 : N - 1;
+    for (int i = 1; i <= last; i++) {                                           // mpc.cpp:435-445
+        double tq[3] = {0.0, 0.0, 0.0}, fs[3] = {0.0, 0.0, 0.0};
+        for (int j = 0; j < NC; j++) {
+            const long long c = (b * N + (i - 1)) * NC + j;
+            double bw[9];
+            contact_Bw(P, lin, c_hor + 3 * c, p_com + 3 * (b * N + (i - 1)), bw);
+            const double *f = u_opt + 3 * c;
+#pragma unroll
+            for (int a = 0; a < 3; a++) { tq[a] += bw[3 * a] * f[0] + bw[3 * a + 1] * f[1] + bw[3 * a + 2] * f[2]; fs[a] += f[a]; }
+        }
+        double y[NS];
+        y[0] = x[0] + P.dt * (lin.c * x[6] - lin.s * x[7]);                     // Ac(0:3,6:9) = Rz(psi)  (quirk Q2)
+        y[1] = x[1] + P.dt * (lin.s * x[6] + lin.c * x[7]);
+        y[2] = x[2] + P.dt * x[8];
+        y[3] = x[3] + P.dt * x[9]; y[4] = x[4] + P.dt * x[10]; y[5] = x[5] + P.dt * x[11];
+        y[6] = x[6] + tq[0]; y[7] = x[7] + tq[1]; y[8] = x[8] + tq[2];
+        y[9] = x[9] + P.bv * fs[0]; y[10] = x[10] + P.bv * fs[1]; y[11] = x[11] + P.dt * x[12] + P.bv * fs[2];
+        y[12] = x[12];
+        for (int r = 0; r < NS; r++) { x[r] = y[r]; xo[i * NS + r] = y[r]; }
+    }
+}
+
 // FP64 FMA peak microbenchmark
 __global__ void fp64_peak_kernel(double *out, int iters)
 {
@@ -292,14 +331,40 @@ __global__ void fp64_peak_kernel(double *out, int iters)
         }                                                                                        \
     } while (0)
 
-typedef void (*solve_fn)(const DevParams, const BatchPtrs, long long);
-struct KernelEntry { int N, NC; solve_fn fn; size_t smem; solve_fn fn2; };   // smem = bytes per problem; fn2 = two problems per warp (or null)
+// One entry per compiled (horizon, num_contacts): the kernel's address (attributes, occupancy) and a launcher with a
+// shape-independent signature (the kernels take their layout object by value, so their own signatures differ).
+typedef void (*launch_fn)(unsigned grid, unsigned block, size_t smem, cudaStream_t st, const DevParams &, const BatchPtrs &, long long B,
+                          const v2::DLay &);
+template <class LAY, int HL>
+void launch_static(unsigned grid, unsigned block, size_t smem, cudaStream_t st, const DevParams &P, const BatchPtrs &io, long long B,
+                   const v2::DLay &)
+{
+    v2::srbd_mpc_solve_warp_kernel<LAY, HL><<<grid, block, smem, st>>>(P, io, B, LAY());
+}
+// any other shape: the same kernel source with the layout in registers (g1mpc_create checks that it fits shared memory)
+void launch_dynamic(unsigned grid, unsigned block, size_t smem, cudaStream_t st, const DevParams &P, const BatchPtrs &io, long long B,
+                    const v2::DLay &L)
+{
+    v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32><<<grid, block, smem, st>>>(P, io, B, L);
+}
+struct KernelEntry {
+    int N, NC;
+    const void *fn; launch_fn launch; size_t smem;      // smem = bytes per problem
+    const void *fn2; launch_fn launch2;                 // two problems per warp (or null)
+};
 // the two-problems-per-warp layout is compiled for the shapes whose stages fit the 16 lanes of a half-warp in one round
 template <int N, int NC>
-constexpr solve_fn two_per_warp()
+constexpr bool two_per_warp() { return N <= 16 && NC == 4 && 2 * v2::WLay<N, NC>::bytes <= 227 * 1024; }
+template <int N, int NC>
+KernelEntry make_entry()
 {
-    if constexpr (N <= 16 && NC == 4 && 2 * v2::WLay<N, NC>::bytes <= 227 * 1024) return v2::srbd_mpc_solve_warp_kernel<N, NC, 16>;
-    else return nullptr;
+    using LAY = v2::WLay<N, NC>;
+    KernelEntry e{N, NC, (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 32>, launch_static<LAY, 32>, LAY::bytes, nullptr, nullptr};
+    if constexpr (two_per_warp<N, NC>()) {
+        e.fn2 = (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 16>;
+        e.launch2 = launch_static<LAY, 16>;
+    }
+    return e;
 }
 
 #ifdef G1MPC_DEV_SHAPE   /* development builds: only the bench shape */
@@ -307,7 +372,7 @@ constexpr solve_fn two_per_warp()
 #else
 #define G1MPC_SHAPES(X) X(10, 4) X(15, 4) X(20, 4) X(40, 4) X(10, 8) X(12, 8) X(20, 8) X(40, 8) X(5, 4) X(8, 4)
 #endif
-#define X_ENTRY(n, c) {n, c, v2::srbd_mpc_solve_warp_kernel<n, c, 32>, v2::WLay<n, c>::bytes, two_per_warp<n, c>()},
+#define X_ENTRY(n, c) make_entry<n, c>(),
 const KernelEntry kKernels[] = {G1MPC_SHAPES(X_ENTRY)};
 #undef X_ENTRY
 
@@ -318,12 +383,15 @@ struct g1mpc_handle {
     DevParams dev;
     int device;
     const KernelEntry *kernel;
+    KernelEntry dyn_entry;                 // used when no compiled shape matches: run-time layout, one problem per warp
+    v2::DLay dlay;
     int warps_per_block = 1;
     int ctas_per_sm = 0;
     // two problems per warp pay off once a scheduler would otherwise hold two warps: above 4 problems per SM
     // (G1MPC_PPW=1|2 in the environment forces one layout -- tests compare the two bit for bit)
     long long two_above = 0;
     int force_ppw = 0;
+    int host_warm = 0, host_warm_shift = 1;     // g1mpc_set_host_warm_start
     // host-API staging: kSlots batches in flight, each cut into up to kPipe chunks with a stream of their own
     static constexpr int kPipe = 4, kSlots = G1MPC_HOST_SLOTS;
     struct Off { size_t x0, xr, ct, ch, pc, xc, xo, u, res, st; };
@@ -334,6 +402,7 @@ struct g1mpc_handle {
         Off off[kPipe];
         int nchunk = 0;
         bool pending = false, staged_out = false;
+        int64_t prev_B = -1;                    // batch size of the solution still lying in d_stage (host warm start)
         double *u_opt = nullptr, *x_opt = nullptr, *resid = nullptr;     // caller's output buffers (unpacked in _end)
         int32_t *status = nullptr, *iters = nullptr;
     } slot[kSlots];
@@ -363,34 +432,56 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
         return G1MPC_ERR_INVALID_ARGUMENT;
     }
     for (int i = 0; i < 12; i++) if (!(p->q_weights[i] > 0)) { g_last_error = "q_weights[0..11] must be positive"; return G1MPC_ERR_INVALID_ARGUMENT; }
+    if (p->q_weights[12] != 0.0) {       // the gravity state is a constant, its weight is zero in both presets (mpc.cpp:96, mpc.py:50)
+        g_last_error = "q_weights[12] (gravity state) must be 0: the state is constant and is not part of the tracked cost";
+        return G1MPC_ERR_INVALID_ARGUMENT;
+    }
+    if (p->layout < 0 || p->layout > 2) { g_last_error = "layout must be 0 (auto), 1 or 2"; return G1MPC_ERR_INVALID_ARGUMENT; }
     const KernelEntry *ke = nullptr;
     for (const auto &k : kKernels) if (k.N == p->horizon && k.NC == p->num_contacts) ke = &k;
-    if (!ke) {
-        g_last_error = "no solve kernel compiled for (horizon, num_contacts) = (" + std::to_string(p->horizon) + ", " + std::to_string(p->num_contacts) + ")";
+    const v2::DLay dl(p->horizon, p->num_contacts);
+    if (!dl.valid()) {
+        g_last_error = "unsupported shape: needs horizon >= 2 and 1 <= num_contacts <= 13 (the step vectors alias the stage storage)";
         return G1MPC_ERR_UNSUPPORTED_SHAPE;
     }
     CUDA_TRY(cudaSetDevice(device));
     int max_smem = 0;
     CUDA_TRY(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
-    if (ke->smem > (size_t)max_smem) { g_last_error = "shape exceeds shared memory"; return G1MPC_ERR_UNSUPPORTED_SHAPE; }
+    if (dl.bytes > (size_t)max_smem) {
+        g_last_error = "shape exceeds shared memory: (horizon, num_contacts) = (" + std::to_string(p->horizon) + ", " + std::to_string(p->num_contacts) +
+                       ") needs " + std::to_string(dl.bytes) + " B per problem, the device allows " + std::to_string(max_smem) +
+                       " B per CTA (roughly horizon <= 80 at 4 contacts, <= 58 at 8, <= 51 at 10)";
+        return G1MPC_ERR_UNSUPPORTED_SHAPE;
+    }
     g1mpc_handle *h = new g1mpc_handle();
-    h->params = *p; h->device = device; h->kernel = ke;
+    h->params = *p; h->device = device; h->dlay = dl;
+    if (!ke) {
+        // no compile-time instantiation for this shape: the run-time-layout instantiation of the same kernel
+        h->dyn_entry = KernelEntry{p->horizon, p->num_contacts, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32>, launch_dynamic,
+                                   dl.bytes, nullptr, nullptr};
+        ke = &h->dyn_entry;
+    }
+    h->kernel = ke;
     if (!(h->params.gap_tol > 0)) h->params.gap_tol = 1e-10;
     if (h->params.max_iter <= 0) h->params.max_iter = 40;
+    if (!(h->params.dual_tol > 0)) h->params.dual_tol = 1e-6;
+    if (!(h->params.warm_margin > 0)) h->params.warm_margin = 0.01 * p->mass * fabs(p->gravity);
+    if (!(h->params.warm_mu0 > 0)) h->params.warm_mu0 = 0.1;
     DevParams &d = h->dev;
     d.mu = p->mu; d.fz_min = p->fz_min; d.fz_max = p->fz_max; d.dt = p->dt;
     d.bv = (1.0 / p->mass) * p->dt;   // (I/m)*dt as in mpc.cpp:238,251
     d.weight = p->mass * fabs(p->gravity);
     d.scale = p->cost_scale; d.r_weight = p->r_weight; d.sr = p->cost_scale * p->r_weight;
     d.gap_tol = h->params.gap_tol; d.max_iter = h->params.max_iter;
+    d.dual_tol = h->params.dual_tol; d.warm_margin = h->params.warm_margin; d.warm_mu0 = h->params.warm_mu0;
     memcpy(d.Ib, p->inertia_body, sizeof d.Ib);
     memcpy(d.q, p->q_weights, sizeof d.q);
-    cudaError_t e = cudaFuncSetAttribute((const void *)ke->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ke->smem * h->warps_per_block));
+    cudaError_t e = cudaFuncSetAttribute(ke->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ke->smem * h->warps_per_block));
     if (e != cudaSuccess) { g_last_error = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
     cudaFuncSetAttribute((const void *)srbd_mpc_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->ctas_per_sm, (const void *)ke->fn, kWarpThreads * h->warps_per_block, ke->smem * h->warps_per_block);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->ctas_per_sm, ke->fn, kWarpThreads * h->warps_per_block, ke->smem * h->warps_per_block);
     if (ke->fn2) {
-        e = cudaFuncSetAttribute((const void *)ke->fn2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * ke->smem * h->warps_per_block));
+        e = cudaFuncSetAttribute(ke->fn2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * ke->smem * h->warps_per_block));
         if (e != cudaSuccess) { g_last_error = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
     }
     {
@@ -399,10 +490,9 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
         h->two_above = 4LL * sms;
         // ... and only where it does not cost residency: two-problem CTAs must hold as many problems per SM as one-problem CTAs do
         // (N = 15: 2 x 84 KB against 5 x 42 KB per SM -> one problem per warp stays)
-        if (ke->fn2) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas2, (const void *)ke->fn2, kWarpThreads * h->warps_per_block, 2 * ke->smem * h->warps_per_block);
+        if (ke->fn2) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas2, ke->fn2, kWarpThreads * h->warps_per_block, 2 * ke->smem * h->warps_per_block);
         if (2 * ctas2 < h->ctas_per_sm) h->two_above = 0x7fffffffffffLL;
-        const char *f = getenv("G1MPC_PPW");
-        h->force_ppw = f ? atoi(f) : 0;
+        h->force_ppw = (p->layout == 1 || p->layout == 2) ? p->layout : 0;
     }
     for (int sl = 0; sl < g1mpc_handle::kSlots; sl++)
         for (int i = 0; i < g1mpc_handle::kPipe; i++) {
@@ -441,7 +531,7 @@ int g1mpc_kernel_info(const g1mpc_handle *h, int32_t *smem_bytes, int32_t *threa
 static int solve_batch_impl(g1mpc_handle *h, int64_t B, int64_t load, const double *x0, const double *x_ref, const double *contact,
                             const double *c_horizon, const double *p_com, const double *x_current, int one_rollout,
                             double *u_opt, double *x_opt, int32_t *status, int32_t *iters, double *resid, double *y_opt,
-                            void *stream)
+                            void *stream, const double *u_warm = nullptr, int warm_shift = 0)
 {
     if (!h || B < 0 || (B > 0 && (!x0 || !x_ref || !contact || !c_horizon || !p_com || !u_opt || !x_opt))) {
         g_last_error = "g1mpc_solve_batch: null argument"; return G1MPC_ERR_INVALID_ARGUMENT;
@@ -449,13 +539,14 @@ static int solve_batch_impl(g1mpc_handle *h, int64_t B, int64_t load, const doub
     if (B == 0) return G1MPC_OK;
     if (B > 0x7fffffffLL) { g_last_error = "batch too large for one launch"; return G1MPC_ERR_INVALID_ARGUMENT; }
     CUDA_TRY(cudaSetDevice(h->device));
-    BatchPtrs io{x0, x_ref, contact, c_horizon, p_com, x_current, u_opt, x_opt, resid, y_opt, status, iters, one_rollout};
+    if (warm_shift < 0) { g_last_error = "warm_shift must be >= 0"; return G1MPC_ERR_INVALID_ARGUMENT; }
+    BatchPtrs io{x0, x_ref, contact, c_horizon, p_com, x_current, u_opt, x_opt, resid, y_opt, status, iters, one_rollout, u_warm, warm_shift};
     const int wpb = h->warps_per_block;
     const bool two = h->kernel->fn2 && (h->force_ppw == 2 || (h->force_ppw != 1 && load > h->two_above));
     if (two)
-        h->kernel->fn2<<<(unsigned)((B + 2 * wpb - 1) / (2 * wpb)), kWarpThreads * wpb, 2 * h->kernel->smem * wpb, (cudaStream_t)stream>>>(h->dev, io, (long long)B);
+        h->kernel->launch2((unsigned)((B + 2 * wpb - 1) / (2 * wpb)), kWarpThreads * wpb, 2 * h->kernel->smem * wpb, (cudaStream_t)stream, h->dev, io, (long long)B, h->dlay);
     else
-        h->kernel->fn<<<(unsigned)((B + wpb - 1) / wpb), kWarpThreads * wpb, h->kernel->smem * wpb, (cudaStream_t)stream>>>(h->dev, io, (long long)B);
+        h->kernel->launch((unsigned)((B + wpb - 1) / wpb), kWarpThreads * wpb, h->kernel->smem * wpb, (cudaStream_t)stream, h->dev, io, (long long)B, h->dlay);
     CUDA_TRY(cudaGetLastError());
     return G1MPC_OK;
 }
@@ -469,6 +560,71 @@ int g1mpc_solve_batch(g1mpc_handle *h, int64_t B, const double *x0, const double
                             resid, y_opt, stream);
 }
 
+int g1mpc_solve_batch_warm(g1mpc_handle *h, int64_t B, const double *x0, const double *x_ref, const double *contact,
+                           const double *c_horizon, const double *p_com, const double *x_current, int one_rollout,
+                           const double *u_warm, int warm_shift, double *u_opt, double *x_opt, int32_t *status, int32_t *iters,
+                           double *resid, double *y_opt, void *stream)
+{
+    return solve_batch_impl(h, B, B, x0, x_ref, contact, c_horizon, p_com, x_current, one_rollout, u_opt, x_opt, status, iters,
+                            resid, y_opt, stream, u_warm, warm_shift);
+}
+
+int g1mpc_rollout_batch(g1mpc_handle *h, int64_t B, const double *x_ref, const double *c_horizon, const double *p_com,
+                        const double *u_opt, const double *x_current, int one_rollout, double *x_opt, void *stream)
+{
+    if (!h || B < 0 || (B > 0 && (!x_ref || !c_horizon || !p_com || !u_opt || !x_opt))) {
+        g_last_error = "g1mpc_rollout_batch: null argument"; return G1MPC_ERR_INVALID_ARGUMENT;
+    }
+    if (B == 0) return G1MPC_OK;
+    CUDA_TRY(cudaSetDevice(h->device));
+    srbd_rollout_kernel<<<(unsigned)((B + 127) / 128), 128, 0, (cudaStream_t)stream>>>(h->dev, x_ref, c_horizon, p_com, u_opt, x_current,
+                                                                                       one_rollout, x_opt, (long long)B, h->params.horizon,
+                                                                                       h->params.num_contacts);
+    CUDA_TRY(cudaGetLastError());
+    return G1MPC_OK;
+}
+
+int g1mpc_rollout_host(g1mpc_handle *h, int64_t B, const double *x_ref, const double *c_horizon, const double *p_com,
+                       const double *u_opt, const double *x_current, int one_rollout, double *x_opt)
+{
+    if (!h || B < 0 || (B > 0 && (!x_ref || !c_horizon || !p_com || !u_opt || !x_opt))) {
+        g_last_error = "g1mpc_rollout_host: null argument"; return G1MPC_ERR_INVALID_ARGUMENT;
+    }
+    if (B == 0) return G1MPC_OK;
+    CUDA_TRY(cudaSetDevice(h->device));
+    const size_t N = h->params.horizon, NU = 3 * (size_t)h->params.num_contacts;
+    const size_t n_xr = B * N * NS, n_ch = B * N * NU, n_pc = B * N * 3, n_xc = (size_t)B * NS;
+    const size_t need = sizeof(double) * (2 * n_xr + 2 * n_ch + n_pc + n_xc);
+    if (need > h->loop_bytes) {                       // (shares the closed-loop workspace: neither call is re-entrant on one handle)
+        if (h->d_loop) cudaFree(h->d_loop);
+        h->d_loop = nullptr; h->loop_bytes = 0;
+        CUDA_TRY(cudaMalloc((void **)&h->d_loop, need));
+        h->loop_bytes = need;
+    }
+    double *d_xr = (double *)h->d_loop, *d_ch = d_xr + n_xr, *d_pc = d_ch + n_ch, *d_u = d_pc + n_pc, *d_xc = d_u + n_ch, *d_xo = d_xc + n_xc;
+    cudaStream_t st = h->slot[0].pipe[0];
+    CUDA_TRY(cudaMemcpyAsync(d_xr, x_ref, sizeof(double) * n_xr, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(d_ch, c_horizon, sizeof(double) * n_ch, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(d_pc, p_com, sizeof(double) * n_pc, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(d_u, u_opt, sizeof(double) * n_ch, cudaMemcpyHostToDevice, st));
+    if (x_current) CUDA_TRY(cudaMemcpyAsync(d_xc, x_current, sizeof(double) * n_xc, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(d_xo, x_opt, sizeof(double) * n_xr, cudaMemcpyHostToDevice, st));
+    int rc = g1mpc_rollout_batch(h, B, d_xr, d_ch, d_pc, d_u, x_current ? d_xc : nullptr, one_rollout, d_xo, st);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(x_opt, d_xo, sizeof(double) * n_xr, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return G1MPC_OK;
+}
+
+int g1mpc_set_host_warm_start(g1mpc_handle *h, int enable, int shift)
+{
+    if (!h || shift < 0) { g_last_error = "g1mpc_set_host_warm_start: bad argument"; return G1MPC_ERR_INVALID_ARGUMENT; }
+    h->host_warm = enable ? 1 : 0;
+    h->host_warm_shift = shift;
+    for (auto &S : h->slot) S.prev_B = -1;
+    return G1MPC_OK;
+}
+
 int g1mpc_layout_info(const g1mpc_handle *h, int64_t B, int32_t *problems_per_warp, int32_t *smem_bytes, int32_t *ctas_per_sm)
 {
     if (!h) return G1MPC_ERR_INVALID_ARGUMENT;
@@ -478,7 +634,7 @@ int g1mpc_layout_info(const g1mpc_handle *h, int64_t B, int32_t *problems_per_wa
     if (smem_bytes) *smem_bytes = (int32_t)(ppw * h->kernel->smem * h->warps_per_block);
     if (ctas_per_sm) {
         int n = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, (const void *)(two ? h->kernel->fn2 : h->kernel->fn), kWarpThreads * h->warps_per_block,
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, two ? h->kernel->fn2 : h->kernel->fn, kWarpThreads * h->warps_per_block,
                                                       ppw * h->kernel->smem * h->warps_per_block);
         *ctas_per_sm = n;
     }
@@ -543,6 +699,8 @@ int g1mpc_update_host_begin(g1mpc_handle *h, int slot, int64_t B, const double *
     const size_t d_in = NS + N * NS + N * NC + N * NU + N * 3 + NS, d_xo = N * NS, d_out = N * NU + 4;   // doubles per problem
     const size_t stride = ((sizeof(double) * (d_in + d_xo + d_out) + 2 * sizeof(int32_t)) * cap + 255) & ~(size_t)255;
     const size_t bytes = stride * nchunk;
+    const bool warm = h->host_warm && S.prev_B == B && bytes <= S.stage_bytes;
+    S.prev_B = B;
     if (bytes > S.stage_bytes) {
         if (S.h_stage) cudaFreeHost(S.h_stage);
         if (S.d_stage) cudaFree(S.d_stage);
@@ -587,7 +745,7 @@ int g1mpc_update_host_begin(g1mpc_handle *h, int slot, int64_t B, const double *
         int32_t *ds_i = (int32_t *)(ds + f.st);
         int rc = solve_batch_impl(h, (int64_t)nb, B, ds + f.x0, ds + f.xr, ds + f.ct, ds + f.ch, ds + f.pc,
                                   x_current ? ds + f.xc : nullptr, one_rollout, ds + f.u, ds + f.xo, ds_i, ds_i + nb,
-                                  ds + f.res, nullptr, sp);
+                                  ds + f.res, nullptr, sp, warm ? ds + f.u : nullptr, h->host_warm_shift);
         if (rc) return rc;
         if (direct_out) {
             CUDA_TRY(cudaMemcpyAsync(x_opt + b0 * N * NS, ds + f.xo, D * nb * N * NS, cudaMemcpyDeviceToHost, sp));
@@ -676,9 +834,9 @@ int g1mpc_wbid_refs_batch(g1mpc_handle *h, int64_t B, const double *u_opt, const
     return G1MPC_OK;
 }
 
-int g1mpc_closed_loop_batch(g1mpc_handle *h, int64_t B, int32_t ticks, double *x0, double *contacts_now, double *sim_time,
-                            double *x_ref, double *x_opt, double *u_opt, double *traj_x, double *traj_u, int32_t *status_any,
-                            void *stream)
+int g1mpc_closed_loop_batch_ex(g1mpc_handle *h, int64_t B, int32_t ticks, int warm_start, double *x0, double *contacts_now,
+                               double *sim_time, double *x_ref, double *x_opt, double *u_opt, double *traj_x, double *traj_u,
+                               int32_t *status_any, int32_t *iters_sum, void *stream)
 {
     if (!h || B < 0 || ticks < 0 || (B > 0 && (!x0 || !contacts_now || !sim_time || !x_ref || !x_opt || !u_opt))) {
         g_last_error = "g1mpc_closed_loop_batch: bad argument"; return G1MPC_ERR_INVALID_ARGUMENT;
@@ -690,8 +848,8 @@ int g1mpc_closed_loop_batch(g1mpc_handle *h, int64_t B, int32_t ticks, double *x
     if (B == 0 || ticks == 0) return G1MPC_OK;
     CUDA_TRY(cudaSetDevice(h->device));
     const size_t N = h->params.horizon;
-    // workspace: contact [B,N,4] | c_horizon [B,N,12] | p_com [B,N,3] | status [B] int32 | iters [B] int32
-    const size_t need = sizeof(double) * (size_t)B * N * 19 + sizeof(int32_t) * 2 * (size_t)B;
+    // workspace: contact [B,N,4] | c_horizon [B,N,12] | p_com [B,N,3] | x0 copy, carry [B,13] each | status [B] int32 | iters [B] int32
+    const size_t need = sizeof(double) * ((size_t)B * N * 19 + 2 * (size_t)B * NS) + sizeof(int32_t) * 2 * (size_t)B;
     if (need > h->loop_bytes) {
         CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
         if (h->d_loop) cudaFree(h->d_loop);
@@ -700,14 +858,87 @@ int g1mpc_closed_loop_batch(g1mpc_handle *h, int64_t B, int32_t ticks, double *x
         h->loop_bytes = need;
     }
     double *contact = (double *)h->d_loop, *c_hor = contact + (size_t)B * N * 4, *p_com = c_hor + (size_t)B * N * 12;
-    int32_t *status = (int32_t *)(p_com + (size_t)B * N * 3), *iters = status + B;
+    int32_t *status = (int32_t *)(p_com + (size_t)B * N * 3 + 2 * (size_t)B * NS), *iters = status + B;
     for (int t = 0; t < ticks; t++) {
         int rc = g1mpc_walk_inputs_batch(h, B, x0, contacts_now, sim_time, x_opt, x_ref, contact, c_hor, p_com, nullptr, stream);
         if (rc) return rc;
-        rc = g1mpc_solve_batch(h, B, x0, x_ref, contact, c_hor, p_com, x0, 0, u_opt, x_opt, status, iters, nullptr, nullptr, stream);
+        rc = solve_batch_impl(h, B, B, x0, x_ref, contact, c_hor, p_com, x0, 0, u_opt, x_opt, status, iters, nullptr, nullptr, stream,
+                              (warm_start && t > 0) ? u_opt : nullptr, 1);
         if (rc) return rc;
         adaptors::advance_kernel<<<(unsigned)((B + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
-            x0, contacts_now, sim_time, x_opt, u_opt, c_hor, status, traj_x, traj_u, status_any, (long long)B, (int)N, t, ticks, h->params.dt);
+            x0, contacts_now, sim_time, x_opt, u_opt, c_hor, status, iters, traj_x, traj_u, status_any, iters_sum, (long long)B, (int)N, t, ticks,
+            h->params.dt);
+        CUDA_TRY(cudaGetLastError());
+    }
+    return G1MPC_OK;
+}
+
+int g1mpc_closed_loop_batch(g1mpc_handle *h, int64_t B, int32_t ticks, double *x0, double *contacts_now, double *sim_time,
+                            double *x_ref, double *x_opt, double *u_opt, double *traj_x, double *traj_u, int32_t *status_any,
+                            void *stream)
+{
+    return g1mpc_closed_loop_batch_ex(h, B, ticks, 0, x0, contacts_now, sim_time, x_ref, x_opt, u_opt, traj_x, traj_u, status_any, nullptr, stream);
+}
+
+int g1mpc_plan_gait_batch(g1mpc_handle *h, int64_t B, const double *planner, const double *current_time, double foot_offset,
+                          double *contact, double *c_horizon, void *stream)
+{
+    if (!h || B < 0 || (B > 0 && (!planner || !current_time || !contact || !c_horizon))) {
+        g_last_error = "g1mpc_plan_gait_batch: null argument"; return G1MPC_ERR_INVALID_ARGUMENT;
+    }
+    if (h->params.num_contacts != 4) {
+        g_last_error = "g1mpc_plan_gait_batch: the planner's mapping has heel and toe of two feet (main.py:273-283): num_contacts == 4";
+        return G1MPC_ERR_UNSUPPORTED_SHAPE;
+    }
+    if (B == 0) return G1MPC_OK;
+    CUDA_TRY(cudaSetDevice(h->device));
+    const long long n = (long long)B * h->params.horizon;
+    adaptors::plan_gait_kernel<<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(planner, current_time, foot_offset, h->params.dt,
+                                                                                               contact, c_horizon, (long long)B, h->params.horizon);
+    CUDA_TRY(cudaGetLastError());
+    return G1MPC_OK;
+}
+
+int g1mpc_main_loop_batch(g1mpc_handle *h, int64_t B, int32_t ticks, const double *planner, double total_duration, double foot_offset,
+                          int warm_start, double *current_time, double *x_ref, double *x_opt, double *u_opt, double *traj_x,
+                          double *traj_u, int32_t *status_any, int32_t *iters_sum, void *stream)
+{
+    if (!h || B < 0 || ticks < 0 || (B > 0 && (!planner || !current_time || !x_ref || !x_opt || !u_opt))) {
+        g_last_error = "g1mpc_main_loop_batch: bad argument"; return G1MPC_ERR_INVALID_ARGUMENT;
+    }
+    if (h->params.num_contacts != 4 || h->params.horizon < 3) {
+        g_last_error = "g1mpc_main_loop_batch: needs num_contacts == 4 and horizon >= 3 (x_opt[2] is fed back, main.py:228)";
+        return G1MPC_ERR_UNSUPPORTED_SHAPE;
+    }
+    if (B == 0 || ticks == 0) return G1MPC_OK;
+    CUDA_TRY(cudaSetDevice(h->device));
+    const size_t N = h->params.horizon;
+    const size_t need = sizeof(double) * ((size_t)B * N * 19 + 2 * (size_t)B * NS) + sizeof(int32_t) * 2 * (size_t)B;
+    if (need > h->loop_bytes) {
+        CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+        if (h->d_loop) cudaFree(h->d_loop);
+        h->d_loop = nullptr; h->loop_bytes = 0;
+        CUDA_TRY(cudaMalloc((void **)&h->d_loop, need));
+        h->loop_bytes = need;
+    }
+    double *contact = (double *)h->d_loop, *c_hor = contact + (size_t)B * N * 4, *p_com = c_hor + (size_t)B * N * 12;
+    double *x0 = p_com + (size_t)B * N * 3, *carry = x0 + (size_t)B * NS;
+    int32_t *status = (int32_t *)(carry + (size_t)B * NS), *iters = status + B;
+    cudaStream_t st = (cudaStream_t)stream;
+    const unsigned gb = (unsigned)((B + 127) / 128), gn = (unsigned)((B * (long long)N + 127) / 128);
+    for (int t = 0; t < ticks; t++) {
+        adaptors::main_pre_kernel<<<gb, 128, 0, st>>>(x0, carry, x_ref, x_opt, (long long)B, (int)N, t);
+        if (t > 0) adaptors::double_support_ref_kernel<<<gn, 128, 0, st>>>(current_time, total_duration, h->params.dt, x_ref, (long long)B, (int)N);
+        int rc = g1mpc_plan_gait_batch(h, B, planner, current_time, foot_offset, contact, c_hor, stream);
+        if (rc) return rc;
+        // p_com_horizon = x_ref_hor[:, 3:6]  (main.py:286): strided copy
+        CUDA_TRY(cudaMemcpy2DAsync(p_com, 3 * sizeof(double), x_ref + 3, NS * sizeof(double), 3 * sizeof(double), (size_t)B * N,
+                                   cudaMemcpyDeviceToDevice, st));
+        rc = solve_batch_impl(h, B, B, x0, x_ref, contact, c_hor, p_com, carry, 0, u_opt, x_opt, status, iters, nullptr, nullptr, stream,
+                              (warm_start && t > 0) ? u_opt : nullptr, 1);
+        if (rc) return rc;
+        adaptors::main_post_kernel<<<gb, 128, 0, st>>>(current_time, x_opt, u_opt, status, iters, traj_x, traj_u, status_any, iters_sum,
+                                                        (long long)B, (int)N, t, ticks, h->params.dt);
         CUDA_TRY(cudaGetLastError());
     }
     return G1MPC_OK;

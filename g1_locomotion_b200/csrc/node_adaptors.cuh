@@ -157,8 +157,8 @@ __global__ void __launch_bounds__(128) wbid_refs_kernel(const double *u_opt, con
 // The previous x_opt stays where it is: the next walk_inputs call reads it for the Raibert rule (:238-243).
 __global__ void __launch_bounds__(128) advance_kernel(double *x0, double *contacts_now, double *sim_time, const double *x_opt,
                                                        const double *u_opt, const double *c_hor, const int32_t *status,
-                                                       double *traj_x, double *traj_u, int32_t *status_any, long long B, int N,
-                                                       int tick, int ticks, double dt)
+                                                       const int32_t *iters, double *traj_x, double *traj_u, int32_t *status_any,
+                                                       int32_t *iters_sum, long long B, int N, int tick, int ticks, double dt)
 {
     const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B) return;
@@ -170,6 +170,95 @@ __global__ void __launch_bounds__(128) advance_kernel(double *x0, double *contac
     for (int i = 0; i < 12; i++) contacts_now[b * 12 + i] = c1[i];
     sim_time[b] = __dadd_rn(sim_time[b], dt);
     if (status_any) status_any[b] = (tick == 0 ? 0 : status_any[b]) | status[b];
+    if (iters_sum) iters_sum[b] = (tick == 0 ? 0 : iters_sum[b]) + iters[b];
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// SURVEY 8f-1, Python half: GaitPlanner.plan_gait (gait_planner.py:27-62) + its mapping onto contact / c_horizon
+// (main.py:259-285).  One thread per (problem, horizon step): it walks the phase list exactly as plan_gait builds it --
+// the same floating-point additions in the same order (start times and foot positions are running sums) -- and stops at the
+// phase that contains t_i = current_time + i dt; past the end the last phase applies (main.py:270-271).
+//   phase 0: [0, ds) "both"; phase 1 + i: single support, support leg left for even i (gait_planner.py:40-51); after phase
+//   1 + i the swing foot moves ahead by step_length (i == 0) or 2 step_length (:55-62).  Left foot starts at (0, -w), right
+//   at (0, +w) (:19-20, as coded).
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) plan_gait_kernel(const double *planner, const double *current_time, double foot_offset,
+                                                         double dt, double *contact, double *c_hor, long long B, int N)
+{
+    const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= B * N) return;
+    const long long b = e / N;
+    const int i = (int)(e % N);
+    const double *pl = planner + b * 5;
+    const double ds = pl[0], ss = pl[1], sl = pl[2], sw = pl[3];
+    const int nsteps = (int)pl[4];
+    const double t = __dadd_rn(current_time[b], __dmul_rn((double)i, dt));      // main.py:263
+    double lx = 0.0, ly = -sw, rx = 0.0, ry = sw;                               // gait_planner.py:19-20
+    double start = 0.0, end = __dadd_rn(0.0, ds);                               // :31-32
+    int support = 0;                                                            // 0 both, 1 left, 2 right
+    bool found = start <= t && t < end;                                         // main.py:266
+    for (int k = 0; k < nsteps && !found; k++) {
+        start = end;                                                            // current_time after the previous phase (:37,52)
+        end = __dadd_rn(start, ss);                                             // :46
+        support = (k % 2 == 0) ? 1 : 2;                                         // :41
+        found = start <= t && t < end;
+        if (!found && k + 1 < nsteps) {                                         // the feet of the NEXT phase (:55-62); the last phase keeps its own
+            const double inc = k == 0 ? sl : __dmul_rn(2.0, sl);
+            if (support == 1) rx = __dadd_rn(rx, inc); else lx = __dadd_rn(lx, inc);
+        }
+    }
+    // (not found at all: the loop has left the last phase's support leg and feet in place, main.py:270-271)
+    const bool lc = support == 0 || support == 1, rc = support == 0 || support == 2;   // main.py:282-283
+    double *ct = contact + e * 4, *ch = c_hor + e * 12;
+    ct[0] = lc ? 1.0 : 0.0; ct[1] = ct[0]; ct[2] = rc ? 1.0 : 0.0; ct[3] = ct[2];
+    ch[0] = __dsub_rn(lx, foot_offset); ch[1] = ly; ch[2] = 0.0;                // left heel   (main.py:276)
+    ch[3] = __dadd_rn(lx, foot_offset); ch[4] = ly; ch[5] = 0.0;                // left toe    (:277)
+    ch[6] = __dsub_rn(rx, foot_offset); ch[7] = ry; ch[8] = 0.0;                // right heel  (:278)
+    ch[9] = __dadd_rn(rx, foot_offset); ch[10] = ry; ch[11] = 0.0;              // right toe   (:279)
+}
+
+// testing_double_support (main.py:177-197): the CoM reference of horizon step i by the quarter of the run t_i falls in.
+__global__ void __launch_bounds__(128) double_support_ref_kernel(const double *current_time, double total, double dt, double *x_ref,
+                                                                  long long B, int N)
+{
+    const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= B * N) return;
+    const long long b = e / N;
+    const double t = __dadd_rn(current_time[b], __dmul_rn((double)(e % N), dt));
+    double rx = 0.0, ry = 0.0, rz = 1.0;
+    if (t < __ddiv_rn(total, 4.0)) ry = 0.1;
+    else if (t < __ddiv_rn(total, 2.0)) { }
+    else if (t < __ddiv_rn(__dmul_rn(3.0, total), 4.0)) rz = 0.7;
+    else rx = 0.01;
+    double *xr = x_ref + e * NS;
+    xr[3] = rx; xr[4] = ry; xr[5] = rz;
+}
+
+// main.py:222-228,306-310: the state the NEXT solve starts from is x_opt[2] of this tick's rollout (x0 = x_ref[0] at the
+// first tick), the state the next rollout starts from is x_opt[1].  `x0` / `carry` are [B,13] work arrays.
+__global__ void __launch_bounds__(128) main_pre_kernel(double *x0, double *carry, const double *x_ref, const double *x_opt,
+                                                        long long B, int N, int tick)
+{
+    const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    for (int i = 0; i < NS; i++) {
+        const double v = tick == 0 ? x_ref[b * N * NS + i] : x_opt[(b * N + 2) * NS + i];     // main.py:226,228
+        x0[b * NS + i] = v;
+        carry[b * NS + i] = tick == 0 ? v : x_opt[(b * N + 1) * NS + i];                     // main.py:306-310
+    }
+}
+__global__ void __launch_bounds__(128) main_post_kernel(double *current_time, const double *x_opt, const double *u_opt,
+                                                         const int32_t *status, const int32_t *iters, double *traj_x, double *traj_u,
+                                                         int32_t *status_any, int32_t *iters_sum, long long B, int N, int tick,
+                                                         int ticks, double dt)
+{
+    const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    if (traj_x) for (int i = 0; i < NS; i++) traj_x[(b * ticks + tick) * NS + i] = x_opt[b * N * NS + i];       // main.py:314-321
+    if (traj_u) for (int i = 0; i < 12; i++) traj_u[(b * ticks + tick) * 12 + i] = u_opt[b * N * 12 + i];       // main.py:322
+    current_time[b] = __dadd_rn(current_time[b], dt);                                                          // main.py:326
+    if (status_any) status_any[b] = (tick == 0 ? 0 : status_any[b]) | status[b];
+    if (iters_sum) iters_sum[b] = (tick == 0 ? 0 : iters_sum[b]) + iters[b];
 }
 
 } // namespace adaptors

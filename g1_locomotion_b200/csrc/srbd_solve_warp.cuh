@@ -46,6 +46,7 @@ namespace v2 {
 #endif
 
 constexpr unsigned kFullMask = 0xffffffffu;
+constexpr int kWarmCheckIt = 5;         // iteration at which a warm-started problem must have halved its gap (else: cold restart)
 
 // Reductions over the HL (32 or 16) lanes that own one problem; lanes of the other half-warp never mix in (xor offsets < HL).
 template <int HL>
@@ -86,8 +87,9 @@ __device__ __forceinline__ int trs(int i, int j) { return i >= j ? i * (i + 1) /
 // share storage; the comments say who owns what when.
 __host__ __device__ constexpr int ev(int x) { return (x + 1) & ~1; }
 
-template <int N, int NC>
+template <int N_, int NC_>
 struct WLay {
+    static constexpr int N = N_, NC = NC_;
     static constexpr int NCN = NC * N;
     // ---- per contact, persistent over the solve ----
     static constexpr int oR = 0;                    // [NCN*3] lever arm r = c - p_com            (mpc.cpp:229-233)
@@ -130,6 +132,39 @@ struct WLay {
     static_assert(12 * NCN <= STG * N, "ds|dl alias the stage storage: needs num_contacts <= 10");
     static_assert(30 * N <= STG * N, "gradient vectors alias the stage storage");
     static constexpr size_t bytes = sizeof(double) * (size_t)oEnd;
+};
+
+// The same layout with the horizon and the number of contacts known only at run time (the reference takes both at run
+// time: HORIZON_LENGTH is a constructor argument, mpc.py:12 / mpc.hpp:22, NUM_CONTACTS an attribute, mpc.py:17): every
+// member of WLay as a plain int, computed once per launch on the host and passed to the kernel by value.  The device code
+// is written against `L.member`, so one source serves the compile-time shapes (members are constants, everything folds
+// exactly as before) and this one (members live in registers / constant bank).
+struct DLay {
+    int N, NC, NCN, oR, oCf, oU, oSl, oLam, oGf, oDst, oProd, oTvOwn, oSt, oE, oS, oRic, oW, oXs, oL1, oV, oX, oVa, oVb, oVc,
+        oVd, oPb, oEx, oTv, scratch, oEnd;
+    bool kTvInScratch;
+    static constexpr int SST = 22, sG2 = 0, sPsi = 36, sP12 = 72, sGam = 108, sP22 = 144, STG = 166;
+    size_t bytes;
+    __host__ __device__ DLay() {}
+    __host__ DLay(int n, int nc)
+    {
+        N = n; NC = nc; NCN = nc * n;
+        oR = 0; oCf = ev(oR + NCN * 3); oU = ev(oCf + NCN); oSl = ev(oU + NCN * 3); oLam = oSl + NCN * 6; oGf = oLam + NCN * 6;
+        oDst = ev(oGf + NCN * 3); oProd = ev(oDst + NCN * 3);
+        kTvInScratch = 3 * NCN <= 12 * N;
+        oTvOwn = oProd + NCN * 6;
+        oSt = ev(oTvOwn + (kTvInScratch ? 0 : NCN * 3));
+        oE = ev(oSt + (NCN + 1) / 2);
+        oS = oE + N * 12; oRic = oS + N * SST;
+        oW = oRic; oXs = oW + N * 6; oL1 = oXs + N * 12; oV = oL1 + N * 6;
+        oX = oRic + N * STG; oVa = oX; oVb = oVa + N * 6; oVc = oVb + N * 6; oVd = oVc + N * 6; oPb = oVd + N * 6; oEx = oVd;
+        oTv = kTvInScratch ? oVb : oTvOwn;
+        scratch = (N * 24 + 12 > 18 * N + 36) ? N * 24 + 12 : 18 * N + 36;
+        oEnd = ev(oX + scratch);
+        bytes = sizeof(double) * (size_t)oEnd;
+    }
+    // what the static_asserts of WLay demand
+    __host__ bool valid() const { return N >= 2 && NC >= 1 && 12 * NCN <= STG * N && 12 * N >= 22; }
 };
 
 // 1/d: MUFU.RCP64H seed (relative error 9.6e-7 measured on B200, profiles/micro/lat.cu) + one cubically convergent
@@ -339,24 +374,24 @@ struct StageC {
 };
 
 // t_k = Bm sum_c [r x tv_c ; tv_c]  (lane k), optionally also S_k = Bm (sum_c W~ Dinv W~') Bm'
-template <int N, int NC, int HL, bool WITH_S>
-__device__ __forceinline__ void assemble_stage(double *sm, const DevParams &P, const StageC &C, int lane)
+template <class LAY, int HL, bool WITH_S>
+__device__ __forceinline__ void assemble_stage(const LAY &L, double *sm, const DevParams &P, const StageC &C, int lane)
 {
-    using L_ = WLay<N, NC>;
+    const int N = L.N, NC = L.NC;
     for (int k = lane; k < N; k += HL) {
         double tt[3] = {0, 0, 0}, tf[3] = {0, 0, 0};
         double Stt[6] = {0, 0, 0, 0, 0, 0}, Sff[6] = {0, 0, 0, 0, 0, 0}, Stf[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};   // tau-tau, F-F (sym), tau-F (full)
         for (int j = 0; j < NC; j++) {
             const int c = k * NC + j;
-            const double cf = sm[L_::oCf + c];
+            const double cf = sm[L.oCf + c];
             if (!(P.fz_max * cf > P.fz_min * cf)) continue;          // swing / eliminated
-            const double *r = sm + L_::oR + 3 * c, *tv = sm + L_::oTv + 3 * c;
+            const double *r = sm + L.oR + 3 * c, *tv = sm + L.oTv + 3 * c;
             const double r0 = r[0], r1 = r[1], r2 = r[2];
             tt[0] += r1 * tv[2] - r2 * tv[1]; tt[1] += r2 * tv[0] - r0 * tv[2]; tt[2] += r0 * tv[1] - r1 * tv[0];
             tf[0] += tv[0]; tf[1] += tv[1]; tf[2] += tv[2];
             if (WITH_S) {
                 double Di[6];
-                ld6(sm + L_::oProd + 6 * c, Di);        // Dblk^-1 of this iteration, left there by the per-contact pass (2)
+                ld6(sm + L.oProd + 6 * c, Di);        // Dblk^-1 of this iteration, left there by the per-contact pass (2)
                 const double D00 = Di[0], D01 = Di[1], D02 = Di[2], D11 = Di[3], D12 = Di[4], D22 = Di[5];
                 // RD = skew(r) Dinv
                 const double a00 = -r2 * D01 + r1 * D02, a01 = -r2 * D11 + r1 * D12, a02 = -r2 * D12 + r1 * D22;
@@ -375,13 +410,13 @@ __device__ __forceinline__ void assemble_stage(double *sm, const DevParams &P, c
             }
         }
         const double *J = C.J;
-        double *t = sm + L_::oVa + 6 * k;
+        double *t = sm + L.oVa + 6 * k;
         t[0] = J[0] * tt[0] + J[1] * tt[1] + J[2] * tt[2];
         t[1] = J[3] * tt[0] + J[4] * tt[1] + J[5] * tt[2];
         t[2] = J[6] * tt[0] + J[7] * tt[1] + J[8] * tt[2];
         t[3] = C.bv * tf[0]; t[4] = C.bv * tf[1]; t[5] = C.bv * tf[2];
         if (WITH_S) {
-            double *S = sm + L_::oS + L_::SST * k;
+            double *S = sm + L.oS + L.SST * k;
             // omega-omega = J Stt J'
             double JS[9];
 #pragma unroll
@@ -418,12 +453,11 @@ __device__ __forceinline__ void assemble_stage(double *sm, const DevParams &P, c
 // column of [ I | P21 | P22 ] (18 lanes), one 6x6 mat-vec and two substitutions each; then Psi = P12 S Gamma,
 // A11 = P11 - P12 S A21.
 // P11 stays in the registers of the six A21 lanes (one column each).  Returns false if a minor was not positive.
-template <int N, int NC, int HL>
-__device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, const StageC &C, int lane PH_PARAMS)
+template <class LAY, int HL>
+__device__ __forceinline__ bool factor_stages(const LAY &L, double *sm, const DevParams &P, const StageC &C, int lane PH_PARAMS)
 {
-    using L_ = WLay<N, NC>;
-    double *Ex = sm + L_::oEx, *PiX = sm + L_::oVb;             // (vB | vC are dead between the assembly and the solve)
-    static_assert(12 * N >= 22, "Pi exchange buffer lives in vB | vC");
+    const int N = L.N;
+    double *Ex = sm + L.oEx, *PiX = sm + L.oVb;             // (vB | vC are dead between the assembly and the solve)
     // HL = 32: lanes >= 18 shadow group 2 and never store.  HL = 16 (two problems per warp): groups 0 and 1 as before,
     // lanes 12..15 are columns 0..3 of group 2, and lanes 4, 5 (group 0) take over the P22 update of columns 4, 5.
     const int grp = lane < 18 ? lane / 6 : 2, cb = lane % 6;
@@ -437,14 +471,14 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
     asm volatile("" : "+d"(sq1), "+d"(sq2));                    // keep them in registers (no re-derivation per stage)
     // P_N = s Q
     {
-        double *St = sm + L_::oRic + (N - 1) * L_::STG;
+        double *St = sm + L.oRic + (N - 1) * L.STG;
         for (int e = lane; e < 58; e += HL) {
             double v = 0.0;
             if (e >= 36) {
 #pragma unroll
                 for (int d = 0; d < 6; d++) if (e - 36 == tri(d, d)) v = P.scale * P.q[6 + d];
             }
-            St[(e < 36 ? L_::sP12 : L_::sP22 - 36) + e] = v;
+            St[(e < 36 ? L.sP12 : L.sP22 - 36) + e] = v;
         }
     }
     const double m1 = grp == 1 ? 1.0 : 0.0, e1 = 1.0 - m1;
@@ -452,9 +486,9 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
     const bool st2 = (act && grp == 2) || cf2;
     // stage-slot offsets of the two column stores shared by groups 0 and 1 (group 1 writes into the slot of stage k-1 and
     // into the exchange buffer)
-    const int offr = grp == 0 ? L_::sG2 + 6 * cb : L_::sP12 - L_::STG + 6 * cb;
-    double *pcol = grp == 0 ? sm + L_::oRic + (N - 1) * L_::STG + L_::sGam + 6 * cb : Ex + 6 * cb;
-    const int dcol = grp == 0 ? L_::STG : 0;
+    const int offr = grp == 0 ? L.sG2 + 6 * cb : L.sP12 - L.STG + 6 * cb;
+    double *pcol = grp == 0 ? sm + L.oRic + (N - 1) * L.STG + L.sGam + 6 * cb : Ex + 6 * cb;
+    const int dcol = grp == 0 ? L.STG : 0;
     double p11[6];                                              // column cb of P11 (meaningful in group 1)
 #pragma unroll
     for (int i = 0; i < 6; i++) p11[i] = i == cb ? sq1 : 0.0;
@@ -462,19 +496,19 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
     int neg = 0;
 #pragma unroll 1
     for (int k = N - 1; k >= 0; k--) {
-        double *St = sm + L_::oRic + k * L_::STG;
-        double *Sk = sm + L_::oS + L_::SST * k;
+        double *St = sm + L.oRic + k * L.STG;
+        double *Sk = sm + L.oS + L.SST * k;
         // Pi = P22^-1 in closed form (P22 is well conditioned: adjugate blocks are accurate enough), T = Pi + S_k by
         // LDL' (T spans the full range of the barrier weights: the closed form stalls the interior point there --
         // measured at N = 40, nc = 8; tests/test_ipm_model_cpu.py keeps the experiment)
         double c[6];                                            // issued first: nothing below depends on it until the mat-vec
-        ld6(St + L_::sP12 + 6 * cb, c);                         // column cb of P21 = row cb of P12 (group 1)
+        ld6(St + L.sP12 + 6 * cb, c);                         // column cb of P21 = row cb of P12 (group 1)
 #pragma unroll
         for (int i = 0; i < 6; i++) c[i] = fma(m1, c[i], i == cb ? e1 : 0.0);      // groups 0, 2: unit vector (no branch)
         double Pi[21], T[21], dT[6];
         {
             double ld[22];
-            ld22(St + L_::sP22, ld);
+            ld22(St + L.sP22, ld);
 #pragma unroll
             for (int e = 0; e < 21; e++) T[e] = ld[e];
             inv6(T, Pi, neg);
@@ -510,7 +544,7 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
             for (int i = 0; i < 6; i++) c[i] -= col[i];
             symmv6(Pi, c, v);
 #pragma unroll
-            for (int i = 0; i < 6; i++) { ld6(St + L_::sP12 + 6 * i, row); wv[i] = dot6(row, v); }
+            for (int i = 0; i < 6; i++) { ld6(St + L.sP12 + 6 * i, row); wv[i] = dot6(row, v); }
         }
         PHF(11)
         // One code path for groups 0 and 1 (no divergence), x = [group 1] P11[:,cb] - wv:
@@ -530,9 +564,9 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
             const bool st01 = lane < 12 && (grp == 0 || k > 0);
             if (st01) { st6(St + offr, px); st6(pcol, col); }
             pcol -= dcol;
-            if (grp == 0) st6(St + L_::sPsi + 6 * cb, wv);
+            if (grp == 0) st6(St + L.sPsi + 6 * cb, wv);
         }
-        double *Sn = St - L_::STG;                              // slot of stage k-1: receives P12 | P22 of P_k
+        double *Sn = St - L.STG;                              // slot of stage k-1: receives P12 | P22 of P_k
         __syncwarp();
         // Theta_k (lower triangle, column cb from group 0) replaces S_k, which nobody reads after this point: the solves
         // form b_k = Gamma' t - Theta p2 with it
@@ -554,10 +588,10 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
                 col[5] = cf2 ? (cb == 4 ? x5 : dT[5]) : col[5];
             }
 #pragma unroll
-            for (int i = 0; i < 6; i++) m12[i] = Sn[L_::sP12 + 6 * i + cb];
+            for (int i = 0; i < 6; i++) m12[i] = Sn[L.sP12 + 6 * i + cb];
             ld6(Ex + 6 * ja, ca); ld6(Ex + 6 * jb, cbv);
             phiT6(C.F, m12, pm);
-            double *dst = Sn + L_::sP22 + cb;                   // lower triangle: entry (i, cb), i >= cb, at tri(i,0) + cb
+            double *dst = Sn + L.sP22 + cb;                   // lower triangle: entry (i, cb), i >= cb, at tri(i,0) + cb
 #pragma unroll
             for (int i = 0; i < 6; i++) {
                 const double val = fma(ga, ca[i], fma(gb, cbv[i], col[i] + pm[i])) + (i == cb ? sq2 : 0.0);
@@ -575,22 +609,22 @@ __device__ __forceinline__ bool factor_stages(double *sm, const DevParams &P, co
 // per-contact step needs: W_c^T y = zeta~_tau x r + zeta~_F).  The two sequential sweeps run on 12 lanes (one state
 // component each) and exchange the 12-vector through shared memory once per stage (42 cycles measured for
 // STS + sync + LDS against 27 for one dependent shuffle, but 8 instructions instead of 16-28 SHFL).
-template <int N, int NC, int HL>
-__device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int lane PH_PARAMS)
+template <class LAY, int HL>
+__device__ __forceinline__ void solve_stages(const LAY &L, double *sm, const StageC &C, int lane PH_PARAMS)
 {
-    using L_ = WLay<N, NC>;
-    double *vA = sm + L_::oVa, *vB = sm + L_::oVb, *vC = sm + L_::oVc, *vD = sm + L_::oVd, *pbuf = sm + L_::oPb;
+    const int N = L.N;
+    double *vA = sm + L.oVa, *vB = sm + L.oVb, *vC = sm + L.oVc, *vD = sm + L.oVd, *pbuf = sm + L.oPb;
     const PhiC F = C.F;
     // ---- pre (lane = stage): gt = Gamma^T t, c1 = P12 gt, c2 = Phi^T c1 + P22 gt
     for (int k = lane; k < N; k += HL) {
-        const double *St = sm + L_::oRic + k * L_::STG;
+        const double *St = sm + L.oRic + k * L.STG;
         double t[6], gt[6], c1[6], c2[6], pc1[6], row[6], p22[22];
         ld6(vA + 6 * k, t);
 #pragma unroll
-        for (int j = 0; j < 6; j++) { ld6(St + L_::sGam + 6 * j, row); gt[j] = dot6(row, t); }      // (columns of Gamma are stored)
+        for (int j = 0; j < 6; j++) { ld6(St + L.sGam + 6 * j, row); gt[j] = dot6(row, t); }      // (columns of Gamma are stored)
 #pragma unroll
-        for (int i = 0; i < 6; i++) { ld6(St + L_::sP12 + 6 * i, row); c1[i] = dot6(row, gt); }
-        ld22(St + L_::sP22, p22);
+        for (int i = 0; i < 6; i++) { ld6(St + L.sP12 + 6 * i, row); c1[i] = dot6(row, gt); }
+        ld22(St + L.sP22, p22);
         symmv6(p22, gt, c2);
         phiT6(F, c1, pc1);
 #pragma unroll
@@ -611,13 +645,13 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
     //      constant term) are issued one step ahead, before the barrier.
     const bool lo6 = lane < 6;
     {
-        const double *rowp = sm + L_::oRic + (lo6 ? L_::sPsi : L_::sG2) + r6;          // row r6 of column storage: + k STG + 6 j
+        const double *rowp = sm + L.oRic + (lo6 ? L.sPsi : L.sG2) + r6;          // row r6 of column storage: + k STG + 6 j
         const double *cp = (lo6 ? vB : vC) + r6;                                        // + 6 k
         double *dstp = lo6 ? pbuf + r6 : vD + r6 - 6;                                   // p1 -> pbuf[6 (k&1)], p2 -> vD[6 (k-1)]
         const bool wr = lane < 12;
         double pown = 0.0, row[6], cadd;
 #pragma unroll
-        for (int j = 0; j < 6; j++) row[j] = rowp[(N - 1) * L_::STG + 6 * j];
+        for (int j = 0; j < 6; j++) row[j] = rowp[(N - 1) * L.STG + 6 * j];
         cadd = cp[6 * (N - 1)];
 #pragma unroll 2
         for (int k = N - 1; k >= 0; k--) {
@@ -634,7 +668,7 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
             if (wr && (lo6 || k > 0)) dstp[lo6 ? 6 * (k & 1) : 6 * k] = pown;
             if (k > 0) {
 #pragma unroll
-                for (int j = 0; j < 6; j++) row[j] = rowp[(k - 1) * L_::STG + 6 * j];
+                for (int j = 0; j < 6; j++) row[j] = rowp[(k - 1) * L.STG + 6 * j];
                 cadd = cp[6 * (k - 1)];
             }
             __syncwarp();
@@ -645,7 +679,7 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
     for (int k = lane; k < N; k += HL) {
         double p2[6], sk[22], sg[6], b[6];
         ld6(vD + 6 * k, p2);
-        ld22(sm + L_::oS + L_::SST * k, sk);
+        ld22(sm + L.oS + L.SST * k, sk);
         symmv6(sk, p2, sg);
         ld6(vA + 6 * k, b);
 #pragma unroll
@@ -657,12 +691,12 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
     PHS(10)
     // ---- forward sweep:  y1 <- y1 + Phi y2 ;  y2 <- b + G2^T y2 - Psi^T y1   (old values on the right)
     {
-        const double *g2p = sm + L_::oRic + L_::sG2 + 6 * r6, *psp = sm + L_::oRic + L_::sPsi + 6 * r6;   // column r6: + k STG
+        const double *g2p = sm + L.oRic + L.sG2 + 6 * r6, *psp = sm + L.oRic + L.sPsi + 6 * r6;   // column r6: + k STG
         double *dstp = (lo6 ? vB : vA) + r6;                                                      // + 6 k
         const bool wr = lane < 12;
         double yown = lo6 ? 0.0 : vA[r6];
         double g2c[6], psc[6], bk;
-        ld6(g2p + L_::STG, g2c); ld6(psp + L_::STG, psc);
+        ld6(g2p + L.STG, g2c); ld6(psp + L.STG, psc);
         bk = vA[6 + r6];
 #pragma unroll 2
         for (int k = 1; k < N; k++) {
@@ -678,23 +712,23 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
             asm volatile("" : "+d"(v_lo), "+d"(v_hi));          // both forms in every lane: no divergent split (see above)
             yown = lo6 ? v_lo : v_hi;
             if (wr) dstp[6 * k] = yown;
-            if (k + 1 < N) { ld6(g2p + (k + 1) * L_::STG, g2c); ld6(psp + (k + 1) * L_::STG, psc); bk = vA[6 * (k + 1) + r6]; }
+            if (k + 1 < N) { ld6(g2p + (k + 1) * L.STG, g2c); ld6(psp + (k + 1) * L.STG, psc); bk = vA[6 * (k + 1) + r6]; }
             __syncwarp();
         }
     }
     PHS(11)
     // ---- output (lane = stage): y_k = P12^T y1 + P22 y2 + p2 ; zeta~ = Bm^T y_k
     for (int k = lane; k < N; k += HL) {
-        const double *St = sm + L_::oRic + k * L_::STG;
+        const double *St = sm + L.oRic + k * L.STG;
         double y1[6], y2[6], z[6], row[6], p22[22], q[6];
         ld6(vB + 6 * k, y1); ld6(vA + 6 * k, y2); ld6(vD + 6 * k, z);
-        ld22(St + L_::sP22, p22);
+        ld22(St + L.sP22, p22);
         symmv6(p22, y2, q);
 #pragma unroll
         for (int i = 0; i < 6; i++) z[i] += q[i];
 #pragma unroll
         for (int j = 0; j < 6; j++) {
-            ld6(St + L_::sP12 + 6 * j, row);
+            ld6(St + L.sP12 + 6 * j, row);
 #pragma unroll
             for (int i = 0; i < 6; i++) z[i] = fma(row[i], y1[j], z[i]);
         }
@@ -713,19 +747,19 @@ __device__ __forceinline__ void solve_stages(double *sm, const StageC &C, int la
 
 // grad f(u) = s r u + W^T (M W u + h): per-stage wrench, state rollout, adjoint sweep (all O(N)), then the
 // per-stage co-state wrench in physical units (Bm^T v) is left in V for the per-contact pass.
-template <int N, int NC, int HL>
-__device__ __forceinline__ void gradient_sweeps(double *sm, const DevParams &P, const StageC &C, int lane)
+template <class LAY, int HL>
+__device__ __forceinline__ void gradient_sweeps(const LAY &L, double *sm, const DevParams &P, const StageC &C, int lane)
 {
-    using L_ = WLay<N, NC>;
-    double *w = sm + L_::oW, *X = sm + L_::oXs, *L1 = sm + L_::oL1, *V = sm + L_::oV;
-    const double *E = sm + L_::oE;
+    const int N = L.N, NC = L.NC;
+    double *w = sm + L.oW, *X = sm + L.oXs, *L1 = sm + L.oL1, *V = sm + L.oV;
+    const double *E = sm + L.oE;
     const PhiC F = C.F;
     // w_k = Bm sum_c [r x f ; f]    (lane = stage)                                   (mpc.cpp:213-254)
     for (int k = lane; k < N; k += HL) {
         double tt[3] = {0, 0, 0}, tf[3] = {0, 0, 0};
         for (int j = 0; j < NC; j++) {
             const int c = k * NC + j;
-            const double *r = sm + L_::oR + 3 * c, *f = sm + L_::oU + 3 * c;
+            const double *r = sm + L.oR + 3 * c, *f = sm + L.oU + 3 * c;
             tt[0] += r[1] * f[2] - r[2] * f[1]; tt[1] += r[2] * f[0] - r[0] * f[2]; tt[2] += r[0] * f[1] - r[1] * f[0];
             tf[0] += f[0]; tf[1] += f[1]; tf[2] += f[2];
         }
@@ -817,6 +851,54 @@ __device__ __noinline__ void rollout_rows(double *gx, const double *x_current, i
     }
 }
 
+// Start point of the interior point.  Cold (gw == nullptr): the weight shared by the stance contacts of each step,
+// clamped into the interior.  Warm (gw = a previous solution u[N,NC,3] of a neighbouring problem, `shift` = how many
+// stages the horizon has moved since; the reference asks its solver for a warm start -- setWarmStart(true),
+// mpc.cpp:386 / warm_start=True, mpc.py:342 -- but builds a fresh solver per call, so it never gets one): stage k takes
+// the force of stage min(k + shift, N-1), pulled `warm_margin` newtons inside every row of the friction pyramid and of the
+// fz box, so that the slacks s = b - C u are consistent with u AND bounded away from zero; a contact that was in swing in
+// the shifted solution gets the cold value.  lambda = mu0 / s is set at the first pass (2).  tests/ipm_model.py:warm_point
+// is the numpy twin.  `active` = this half-warp's problem takes part (control flow stays warp-uniform).
+template <class LAY, int HL>
+__device__ __forceinline__ void start_point(const LAY &L, double *sm, const DevParams &P, int lane, bool active, const double *gw, int shift)
+{
+    const int N = L.N, NC = L.NC, NCN = L.NCN;
+    double *cfl = sm + L.oCf, *u = sm + L.oU, *sl = sm + L.oSl, *lam = sm + L.oLam;
+    const double mu = P.mu;
+    for (int c = lane; c < (active ? NCN : 0); c += HL) {
+        const int k = c / NC;
+        int ns = 0;
+        for (int j = 0; j < NC; j++) { const double cj = cfl[k * NC + j]; ns += (P.fz_max * cj > P.fz_min * cj) ? 1 : 0; }
+        const double cf = cfl[c], lo = P.fz_min * cf, hi = P.fz_max * cf;
+        const bool st = hi > lo;
+        double f0 = 0.0, f1 = 0.0, fz = 0.0;
+        double *s6 = sl + 6 * c, *l6 = lam + 6 * c;
+        if (st) {
+            const double span = hi - lo;
+            fz = P.weight / (double)ns;
+            fz = fmin(fmax(fz, lo + 0.1 * span), hi - 0.1 * span);
+            if (gw) {
+                const int kp = k + shift < N ? k + shift : N - 1;
+                const double *f = gw + (size_t)(kp * NC + (c - k * NC)) * 3;
+                const double w0 = f[0], w1 = f[1], w2 = f[2];
+                if (w2 > 0.0) {                                 // (false for NaN and for a contact that was in swing)
+                    const double m = fmin(P.warm_margin, 0.1 * span);
+                    fz = fmin(fmax(w2, lo + m), hi - m);
+                    const double lim = fmax(mu * fz - m, 0.0);
+                    f0 = fmin(fmax(w0, -lim), lim); f1 = fmin(fmax(w1, -lim), lim);
+                }
+            }
+            s6[0] = mu * fz - f0; s6[1] = mu * fz + f0; s6[2] = mu * fz - f1; s6[3] = mu * fz + f1; s6[4] = hi - fz; s6[5] = fz - lo;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 6; i++) s6[i] = 1.0;
+        }
+        u[3 * c] = f0; u[3 * c + 1] = f1; u[3 * c + 2] = fz;
+#pragma unroll
+        for (int i = 0; i < 6; i++) l6[i] = 0.0;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // fused solve kernel: blockDim.x = 32 * warps_per_block.  HL = 32: warp -> problem.  HL = 16: two problems per warp, one
 // per half-warp (the 6x6 inverse and LDL' of a stage, identical in every lane, are then issued once for two problems, and
@@ -824,25 +906,25 @@ __device__ __noinline__ void rollout_rows(double *gx, const double *x_current, i
 // control flow stays warp-uniform (a half that has finished keeps executing with its state frozen), so every
 // __syncwarp / shuffle is reached by all 32 lanes.  Both layouts give the same bits per problem.
 // ------------------------------------------------------------------------------------------------
-template <int N, int NC, int HL>
-__global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParams P, const BatchPtrs io, long long B)
+template <class LAY, int HL>
+__global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParams P, const BatchPtrs io, long long B, const LAY L)
 {
-    using L_ = WLay<N, NC>;
-    constexpr int NU = 3 * NC, NV = NU * N, NCN = NC * N, PPW = 32 / HL;
+    const int N = L.N, NC = L.NC, NU = 3 * NC, NV = NU * N, NCN = NC * N;
+    constexpr int PPW = 32 / HL;
     extern __shared__ __align__(16) double sm_all[];
 #ifdef G1MPC_PHASE_CLOCKS
     const long long ph_k0 = clock64();
 #endif
     const int lane = threadIdx.x & (HL - 1), half = (threadIdx.x & 31) / HL, warp = threadIdx.x >> 5;
-    double *sm = sm_all + (size_t)(warp * PPW + half) * L_::oEnd;
+    double *sm = sm_all + (size_t)(warp * PPW + half) * L.oEnd;
     long long b = ((long long)blockIdx.x * (blockDim.x >> 5) + warp) * PPW + half;
     if (b - half >= B) return;                     // whole warp out of range
     const bool valid = b < B;                      // odd batch: the last half-warp repeats the last problem and writes nothing
     if (!valid) b = B - 1;
-    double *rr = sm + L_::oR, *cfl = sm + L_::oCf, *u = sm + L_::oU, *sl = sm + L_::oSl, *lam = sm + L_::oLam;
-    double *gf = sm + L_::oGf, *Dst = sm + L_::oDst, *prod = sm + L_::oProd, *tv = sm + L_::oTv, *E = sm + L_::oE;
-    double *dsv = sm + L_::oRic, *dlv = sm + L_::oRic + 6 * NCN;     // alias: valid only after the corrector solve
-    int *stIdx = reinterpret_cast<int *>(sm + L_::oSt);
+    double *rr = sm + L.oR, *cfl = sm + L.oCf, *u = sm + L.oU, *sl = sm + L.oSl, *lam = sm + L.oLam;
+    double *gf = sm + L.oGf, *Dst = sm + L.oDst, *prod = sm + L.oProd, *tv = sm + L.oTv, *E = sm + L.oE;
+    double *dsv = sm + L.oRic, *dlv = sm + L.oRic + 6 * NCN;     // alias: valid only after the corrector solve
+    int *stIdx = reinterpret_cast<int *>(sm + L.oSt);
     const double *gx0 = io.x0 + b * NS, *gxr = io.x_ref + b * (N * NS), *gct = io.contact + b * NCN;
     const double *gch = io.c_hor + b * (NCN * 3), *gpc = io.p_com + b * (N * 3);
     const double sr = P.sr, mu = P.mu;
@@ -896,28 +978,9 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         }
     }
     __syncwarp();
-    // start point: weight shared by the stance contacts of each step, clamped into the interior
-    for (int c = lane; c < NCN; c += HL) {
-        const int k = c / NC;
-        int ns = 0;
-        for (int j = 0; j < NC; j++) { const double cj = cfl[k * NC + j]; ns += (P.fz_max * cj > P.fz_min * cj) ? 1 : 0; }
-        const double cf = cfl[c], lo = P.fz_min * cf, hi = P.fz_max * cf;
-        const bool st = hi > lo;
-        double fz = 0.0;
-        double *s6 = sl + 6 * c, *l6 = lam + 6 * c;
-        if (st) {
-            const double span = hi - lo;
-            fz = P.weight / (double)ns;
-            fz = fmin(fmax(fz, lo + 0.1 * span), hi - 0.1 * span);
-            s6[0] = mu * fz; s6[1] = mu * fz; s6[2] = mu * fz; s6[3] = mu * fz; s6[4] = hi - fz; s6[5] = fz - lo;
-        } else {
-#pragma unroll
-            for (int i = 0; i < 6; i++) s6[i] = 1.0;
-        }
-        u[3 * c] = 0.0; u[3 * c + 1] = 0.0; u[3 * c + 2] = fz;
-#pragma unroll
-        for (int i = 0; i < 6; i++) l6[i] = 0.0;
-    }
+    // start point (cold, or from a previous solution)
+    bool warm = io.u_warm != nullptr;
+    start_point<LAY, HL>(L, sm, P, lane, true, warm ? io.u_warm + b * NV : nullptr, io.warm_shift);
     const double m_ineq = 6.0 * (double)(n_stance > 0 ? n_stance : 1);
     __syncwarp();
 
@@ -926,7 +989,7 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
     ph_t[13] = ph_last - ph_k0;                     // prologue: linearise, stage the inputs, start point
 #endif
     int status = G1MPC_MAX_ITER, it = 0;
-    double gap = 0.0, rdmax = 0.0;
+    double gap = 0.0, rdmax = 0.0, gscale = 1.0, gap_start = 0.0;
     bool lam_init = false;
 
     // grad f is recomputed from u (two O(N) sweeps) only near the end; while the gap is large it is carried along with
@@ -948,9 +1011,9 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         double p_gf = 0.0;
         if (HL == 32 ? exact : __any_sync(kFullMask, exact && !frozen)) {
             // (1) gradient: V <- Bm^T (M W u + h)
-            gradient_sweeps<N, NC, HL>(sm, P, C, lane);
+            gradient_sweeps<LAY, HL>(L, sm, P, C, lane);
             PH(0)
-            const double *Vt = sm + L_::oV;
+            const double *Vt = sm + L.oV;
             for (int i = lane; i < (exact ? n_act : 0); i += HL) {
                 const int c = stIdx[i], k = c / NC;
                 const double *vk = Vt + 6 * k, *r = rr + 3 * c, *uc = u + 3 * c;
@@ -963,15 +1026,20 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         }
         // (2) per stance contact: dual residual, gap, reciprocals and D-state of the 3x3 block,
         //     predictor t = -Dblk^-1 grad f
-        if (!lam_init) {
-            // lambda_0 = mu0 / s with mu0 tied to the gradient scale at the start point
-            const double mu0 = fmax(1e-2, 0.1 * wmax<HL>(p_gf));
-            for (int i = lane; i < n_act; i += HL) {
-                const int c = stIdx[i];
+        {
+            // lambda_0 = mu0 / s with mu0 tied to the gradient scale at the start point (cold) or the fixed warm value
+            const double gmax = wmax<HL>(p_gf);                 // (outside the branch: the halves of a warp may differ)
+            if (!lam_init) {
+                const double mu0 = warm ? P.warm_mu0 : fmax(1e-2, 0.1 * gmax);
+                gscale = 1.0 + gmax;
+                gap_start = mu0;
+                for (int i = lane; i < n_act; i += HL) {
+                    const int c = stIdx[i];
 #pragma unroll
-                for (int j = 0; j < 6; j++) lam[6 * c + j] = mu0 / sl[6 * c + j];
+                    for (int j = 0; j < 6; j++) lam[6 * c + j] = mu0 / sl[6 * c + j];
+                }
+                lam_init = true;
             }
-            lam_init = true;
         }
         double p_gap2[2] = {0.0, 0.0}, p_rd = 0.0;
         for (int i = lane, odd = 0; i < n_act; i += HL, odd ^= 1) {
@@ -1012,11 +1080,31 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
             }
         }
         {
+            // Safeguard of the warm start: a start point whose multipliers are far off stalls close to the boundary (steps of
+            // a few per cent for tens of iterations -- seen on walkers that are falling over, tests/ipm_model.py).  If the gap
+            // has not halved after kWarmCheckIt iterations the problem restarts from the cold point; the iterations spent count.
+            const bool fall = warm && !frozen && it == kWarmCheckIt && gap > 0.5 * gap_start;
+            if (HL == 32 ? fall : __any_sync(kFullMask, fall)) {
+                __syncwarp();
+                start_point<LAY, HL>(L, sm, P, lane, fall, nullptr, 0);
+                if (fall) { warm = false; lam_init = false; exact = true; }
+                __syncwarp();
+                goto again;
+            }
+        }
+        {
             // never stop on a carried gradient: evaluate it and look again
             const bool redo = !frozen && !exact && (gap <= P.gap_tol || it >= P.max_iter);
             if (HL == 32 ? redo : __any_sync(kFullMask, redo)) { if (redo) exact = true; __syncwarp(); goto again; }
         }
-        if (!frozen && (gap <= P.gap_tol || n_stance == 0)) { status = G1MPC_SOLVED; frozen = true; }
+        // solved = complementarity gap AND dual residual |grad f + C' lambda|inf <= dual_tol (1 + |grad f(u_start)|inf); the
+        // primal residual is zero by construction (slacks start consistent and move with ds = -Cb du; the returned point is
+        // clamped).  A gap that converged on a dual residual that did not (long horizons sit on the accuracy floor of the
+        // stage-wise solves) is reported, not hidden.
+        if (!frozen && (gap <= P.gap_tol || n_stance == 0)) {
+            status = (rdmax <= P.dual_tol * gscale || n_stance == 0) ? G1MPC_SOLVED : G1MPC_DUAL_RESIDUAL;
+            frozen = true;
+        }
         if (!frozen && it >= P.max_iter) { status = G1MPC_MAX_ITER; frozen = true; }
         if (HL == 32 ? frozen : __all_sync(kFullMask, frozen)) break;
         n_act = frozen ? 0 : n_stance;
@@ -1024,18 +1112,18 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
 
         PH(1)
         // (3) S_k, t_k, then the backward Riccati sweep (shared by predictor and corrector)
-        assemble_stage<N, NC, HL, true>(sm, P, C, lane);
+        assemble_stage<LAY, HL, true>(L, sm, P, C, lane);
         __syncwarp();
         PH(2)
-        if (!factor_stages<N, NC, HL>(sm, P, C, lane PH_ARGS) && !frozen) { status = G1MPC_NUMERICAL; frozen = true; }
+        if (!factor_stages<LAY, HL>(L, sm, P, C, lane PH_ARGS) && !frozen) { status = G1MPC_NUMERICAL; frozen = true; }
         if (HL == 32 ? frozen : __all_sync(kFullMask, frozen)) break;
         n_act = frozen ? 0 : n_stance;
         PH(3)
         // (4) predictor.  With x = ds/s:  dl = -lam (1 + x), and the largest feasible step is
         //     1 / max_i max(-x_i, 1 + x_i)  -- no division per constraint.
-        solve_stages<N, NC, HL>(sm, C, lane PH_ARGS);
+        solve_stages<LAY, HL>(L, sm, C, lane PH_ARGS);
         PH(4)
-        const double *zt = sm + L_::oVa;
+        const double *zt = sm + L.oVa;
         double p_rmax = 0.0, p_sum2[2] = {0.0, 0.0};
         for (int i = lane, odd = 0; i < n_act; i += HL, odd ^= 1) {
             const int c = stIdx[i], k = c / NC;
@@ -1088,10 +1176,10 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
             for (int j = 0; j < 6; j++) prod[6 * c + j] = q6[j];
         }
         __syncwarp();
-        assemble_stage<N, NC, HL, false>(sm, P, C, lane);
+        assemble_stage<LAY, HL, false>(L, sm, P, C, lane);
         __syncwarp();
         PH(5)
-        solve_stages<N, NC, HL>(sm, C, lane PH_ARGS);
+        solve_stages<LAY, HL>(L, sm, C, lane PH_ARGS);
         PH(4)
         // (6) combined direction, step length (the stage storage is dead now: ds | dl live there).
         //     dl = -lam (1 + x + q/lam)
@@ -1154,7 +1242,7 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
     // first has had its stage storage reused by the other's later iterations: evaluate w, X, V again from the returned u.
     if (HL == 16 || status == G1MPC_NUMERICAL) {
         __syncwarp();
-        gradient_sweeps<N, NC, HL>(sm, P, C, lane);
+        gradient_sweeps<LAY, HL>(L, sm, P, C, lane);
     }
     __syncwarp();
     // here w = W u, X = state response, gf = grad f(u) are consistent with the returned u
@@ -1181,7 +1269,7 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
     for (int i = lane; i < (valid ? NV : 0); i += HL) gu[i] = u[i];
     if (io.status && lane == 0 && valid) io.status[b] = status;
     if (io.iters && lane == 0 && valid) io.iters[b] = it;
-    const double *wv = sm + L_::oW, *Xs = sm + L_::oXs;
+    const double *wv = sm + L.oW, *Xs = sm + L.oXs;
     if (io.resid) {
         double obj2[2] = {0.0, 0.0}, pv = 0.0;      // (two accumulators: see wsum2)
         for (int i = lane, odd = 0; i < NV; i += HL, odd ^= 1) {
@@ -1218,7 +1306,7 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
                 y5[0] = -l6[1]; y5[1] = l6[0]; y5[2] = -l6[3]; y5[3] = l6[2]; y5[4] = l6[4] - l6[5];
             } else {
                 // swing contact: any sign-feasible multiplier set that balances the gradient
-                const double *vk = sm + L_::oV + 6 * (c / NC), *r = rr + 3 * c;      // u = 0 here: grad f = W_c^T v
+                const double *vk = sm + L.oV + 6 * (c / NC), *r = rr + 3 * c;      // u = 0 here: grad f = W_c^T v
                 const double g0 = (vk[1] * r[2] - vk[2] * r[1]) + vk[3], g1 = (vk[2] * r[0] - vk[0] * r[2]) + vk[4];
                 const double g2 = (vk[0] * r[1] - vk[1] * r[0]) + vk[5];
                 y5[0] = y5[1] = y5[2] = y5[3] = 0.0;
@@ -1231,7 +1319,7 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
         }
     }
     rollout_rows(io.x_opt + b * (N * NS), io.x_current ? io.x_current + b * NS : nullptr, io.one_rollout ? 1 : N - 1,
-                 sm + L_::oVa, sm + L_::oXs, P.dt, cz, sz, lane, HL, valid);
+                 sm + L.oVa, sm + L.oXs, P.dt, cz, sz, lane, HL, valid);
 #ifdef G1MPC_PHASE_CLOCKS
     __syncwarp();
     PH(14)                                          // epilogue: outputs + rollout

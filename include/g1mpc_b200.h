@@ -31,22 +31,24 @@ extern "C" {
 #endif
 
 #define G1MPC_NUM_STATES 13
-#define G1MPC_ABI_VERSION 4
+#define G1MPC_ABI_VERSION 5
 
 typedef enum g1mpc_error {
     G1MPC_OK = 0,
     G1MPC_ERR_INVALID_ARGUMENT = -1,
-    G1MPC_ERR_UNSUPPORTED_SHAPE = -2, /* (horizon, num_contacts) has no compiled kernel / exceeds shared memory */
+    G1MPC_ERR_UNSUPPORTED_SHAPE = -2, /* (horizon, num_contacts) exceeds shared memory, or an adaptor's fixed shape   */
     G1MPC_ERR_CUDA = -3,              /* see g1mpc_last_error() */
     G1MPC_ERR_NO_DEVICE = -4
 } g1mpc_error;
 
 /* per-problem status written by g1mpc_solve_batch */
 typedef enum g1mpc_status {
-    G1MPC_SOLVED = 0,          /* complementarity gap <= gap_tol                                        */
+    G1MPC_SOLVED = 0,          /* complementarity gap <= gap_tol AND dual residual <= dual_tol (1 + |grad f(u_start)|inf) */
     G1MPC_MAX_ITER = 1,        /* iteration limit hit; best iterate returned                            */
     G1MPC_BAD_BOUNDS = 2,      /* some contact had fz_max*c < fz_min*c (negative flag); treated as swing */
-    G1MPC_NUMERICAL = 3        /* NaN/Inf in the inputs or a breakdown of the factorisation             */
+    G1MPC_NUMERICAL = 3,       /* NaN/Inf in the inputs or a breakdown of the factorisation             */
+    G1MPC_DUAL_RESIDUAL = 4    /* gap converged, dual residual |H u + g + A'y|inf above dual_tol: result returned,
+                                  accurate to what resid[1] says (long horizons: accuracy floor of the stage-wise solves) */
 } g1mpc_status;
 
 /* Constants the reference hard-codes in its constructors (mpc.hpp:22,136; mpc.cpp:25-27,90-98;
@@ -63,7 +65,12 @@ typedef struct g1mpc_params {
     double cost_scale;        /* 2: H=2(B'QB+R) (mpc.cpp:361,375); 1: Python (mpc.py:301,317) */
     double gap_tol;           /* stop when mean complementarity s'lambda/m <= gap_tol  (<=0: default 1e-10) */
     int32_t max_iter;         /* interior-point iteration limit               (<=0: default 40)     */
-    int32_t reserved;
+    int32_t layout;           /* lane layout of the solve kernel: 0 = chosen per launch (g1mpc_layout_info), 1 = one problem
+                                 per warp, 2 = two (where compiled).  Results do not depend on it (bit-identical).       */
+    double dual_tol;          /* see G1MPC_SOLVED                             (<=0: default 1e-6)   */
+    double warm_margin;       /* warm start: newtons a previous solution is pulled inside every constraint row
+                                                                              (<=0: default 0.01 mass |g|) */
+    double warm_mu0;          /* warm start: initial complementarity s*lambda (<=0: default 0.1)    */
 } g1mpc_params;
 
 typedef struct g1mpc_handle g1mpc_handle;
@@ -87,6 +94,35 @@ int g1mpc_solve_batch(g1mpc_handle *h, int64_t B, const double *x0, const double
                       int32_t *status, int32_t *iters, double *resid, double *y_opt, void *stream);
 
 /*
+ * g1mpc_solve_batch started from a previous solution -- the warm start the reference asks its solver for
+ * (setWarmStart(true), mpc.cpp:386; warm_start=True, mpc.py:342) but never gets, because it constructs a fresh solver on
+ * every call (mpc.cpp:380).  u_warm [B,N,3nc] (device) is the u_opt of a neighbouring problem, warm_shift the
+ * number of stages the horizon has moved since (1 for consecutive control ticks, 0 for a re-solve); u_warm may alias
+ * u_opt.  The minimiser is unique, so the result is the cold-start result to solver accuracy (not bit for bit); a start
+ * that stalls is detected after 5 iterations and the problem restarts cold.  u_warm == NULL: identical to g1mpc_solve_batch.
+ */
+int g1mpc_solve_batch_warm(g1mpc_handle *h, int64_t B, const double *x0, const double *x_ref,
+                           const double *contact, const double *c_horizon, const double *p_com,
+                           const double *x_current, int one_rollout, const double *u_warm, int warm_shift,
+                           double *u_opt, double *x_opt, int32_t *status, int32_t *iters, double *resid,
+                           double *y_opt, void *stream);
+
+/*
+ * MPC::computeRollout (mpc.cpp:427-446 / mpc.py:379-391) of a GIVEN u_opt, device pointers: x_opt[0] = x_current if given,
+ * x_opt[i] = A x_opt[i-1] + B_{i-1} u_opt[i-1] for i = 1..N-1 (only i = 1 with one_rollout); A, B_i from x_ref (mean yaw),
+ * c_horizon and p_com as in the build (mpc.cpp:153-254).  x_opt [B,N,13] is in/out like the member x_opt_.
+ */
+int g1mpc_rollout_batch(g1mpc_handle *h, int64_t B, const double *x_ref, const double *c_horizon,
+                        const double *p_com, const double *u_opt, const double *x_current, int one_rollout,
+                        double *x_opt, void *stream);
+
+/* The same with HOST pointers (copies in, rolls out, copies x_opt back, synchronises): what a host-side computeRollout()
+ * wrapper calls (include/g1mpc_mpc.hpp, g1_locomotion_b200/mpc.py). */
+int g1mpc_rollout_host(g1mpc_handle *h, int64_t B, const double *x_ref, const double *c_horizon,
+                       const double *p_com, const double *u_opt, const double *x_current, int one_rollout,
+                       double *x_opt);
+
+/*
  * Materialises the reference's intermediate matrices for a batch (device pointers, any may be NULL):
  *   A [B,13,13] (mpc.cpp:208-211)        Bd  [B,13N,3nc] (mpc.cpp:246-254)   Aqp [B,13N,13]  (mpc.cpp:256-270)
  *   Bqp [B,13N,3ncN] (mpc.cpp:272-291)   H   [B,3ncN,3ncN] (mpc.cpp:359-364) g [B,3ncN]      (mpc.cpp:366-376)
@@ -108,6 +144,13 @@ int g1mpc_update_host(g1mpc_handle *h, int64_t B, const double *x0, const double
                       const double *contact, const double *c_horizon, const double *p_com,
                       const double *x_current, int one_rollout, double *u_opt, double *x_opt,
                       int32_t *status, int32_t *iters, double *resid);
+
+/*
+ * Host-API warm start (off by default = the reference's behaviour, a cold solve per call): when enabled, every
+ * g1mpc_update_host / _begin call on a slot starts from the solution the previous call on that slot left on the device,
+ * shifted by `shift` stages, provided the batch size is unchanged (otherwise that call is a cold start).
+ */
+int g1mpc_set_host_warm_start(g1mpc_handle *h, int enable, int shift);
 
 /*
  * The same call in two halves, for a host that feeds one batch after the other (a fleet of simulated walkers, or
@@ -163,6 +206,42 @@ int g1mpc_wbid_refs_batch(g1mpc_handle *h, int64_t B, const double *u_opt, const
 int g1mpc_closed_loop_batch(g1mpc_handle *h, int64_t B, int32_t ticks, double *x0, double *contacts_now,
                             double *sim_time, double *x_ref, double *x_opt, double *u_opt, double *traj_x,
                             double *traj_u, int32_t *status_any, void *stream);
+
+/*
+ * SURVEY 8f-1, Python half -- GaitPlanner.plan_gait (g1_mpc/scripts/gait_planner.py:27-62) and its mapping onto the MPC
+ * inputs in the SRBD-only loop (g1_mpc/scripts/main.py:259-285), for a batch of planners (device pointers):
+ *   planner [B,5] = double_support_time, single_support_time, step_length, step_width, num_steps (a whole number);
+ *   current_time [B]  ->  contact [B,N,4], c_horizon [B,N,12] (left heel, left toe, right heel, right toe; z = 0),
+ *   horizon step i looks the phase up at t_i = current_time + i dt, the last phase if none contains it; heel / toe sit
+ *   foot_offset (0.08 in main.py:261) behind / ahead of the foot centre.  Needs num_contacts == 4.  Bit-exact against the
+ *   reference class (same additions in the same order).
+ */
+int g1mpc_plan_gait_batch(g1mpc_handle *h, int64_t B, const double *planner, const double *current_time,
+                          double foot_offset, double *contact, double *c_horizon, void *stream);
+
+/*
+ * SURVEY 8f-3 as main.py runs it (g1_mpc/scripts/main.py:200-326), B walkers, `ticks` control periods on the device, four
+ * launches per tick: reference schedule of testing_double_support (main.py:177-197; tick > 0) -> g1mpc_plan_gait_batch ->
+ * solve -> advance.  State feedback as coded: the solve of tick t > 0 uses x0 = x_opt[2] of the previous rollout
+ * (main.py:228) while the rollout restarts from x_opt[1] (main.py:306-310).  warm_start != 0: every tick after the first
+ * starts from the previous tick's u_opt shifted by one stage (g1mpc_solve_batch_warm).
+ * In/out: x_ref [B,N,13] (main.py:207-209 initialises it: zeros, column 12 = g, column 5 = 1), x_opt [B,N,13], u_opt
+ * [B,N,12], current_time [B].  Optional outputs: traj_x [B,ticks,13] (x_opt[0] after each tick's rollout, what main.py
+ * records), traj_u [B,ticks,12], status_any [B], iters_sum [B] (interior-point iterations summed over the ticks).
+ */
+int g1mpc_main_loop_batch(g1mpc_handle *h, int64_t B, int32_t ticks, const double *planner, double total_duration,
+                          double foot_offset, int warm_start, double *current_time, double *x_ref, double *x_opt,
+                          double *u_opt, double *traj_x, double *traj_u, int32_t *status_any, int32_t *iters_sum,
+                          void *stream);
+
+/*
+ * g1mpc_closed_loop_batch with the options SURVEY 8f-3 names: warm_start != 0 starts every tick after the first from
+ * the previous tick's u_opt shifted by one stage; iters_sum [B] (optional) receives the interior-point iterations summed
+ * over the ticks, so that cold and warm runs can be compared.
+ */
+int g1mpc_closed_loop_batch_ex(g1mpc_handle *h, int64_t B, int32_t ticks, int warm_start, double *x0,
+                               double *contacts_now, double *sim_time, double *x_ref, double *x_opt, double *u_opt,
+                               double *traj_x, double *traj_u, int32_t *status_any, int32_t *iters_sum, void *stream);
 
 /* Dynamic shared memory (bytes) and threads per CTA of the solve kernel for this handle's shape. */
 int g1mpc_kernel_info(const g1mpc_handle *h, int32_t *smem_bytes, int32_t *threads, int32_t *ctas_per_sm);

@@ -28,6 +28,14 @@ CASES = [
 ]
 
 
+# cost_scale 1: the Python class has no x2 (mpc.py:301,317); the cpp_node constants are applied to it as in ref_loader
+UPDATE_CASES = [
+    ("py_default_n15", "python_default", {}, "random", 23),
+    ("cpp_consts_walk", "cpp_node", {"cost_scale": 1.0}, "walk", 14),
+    ("cpp_consts_walk_b", "cpp_node", {"cost_scale": 1.0}, "walk", 27),
+]
+
+
 def make_inputs(kind, preset, seed):
     if kind == "walk":
         return inputs.walking_problem(seed, np.random.default_rng(seed), preset)
@@ -55,6 +63,23 @@ def main():
                             contact=ct, c_horizon=ch, p_com=pc, u_rollout=u, x_opt_full=x_full, x_opt_one=x_one,
                             **out)
         print(name, {k: v.shape for k, v in out.items() if hasattr(v, "shape")})
+    # The reference's MPC.update() run END TO END (mpc.py:360-377; solve_qp through oracle/osqp_shim.py, i.e. the OSQP
+    # restatement with default settings): pins the reference's own control flow -- the hand-over of P, q, A, l, u, the
+    # row-major reshape of result.x (mpc.py:352) and compute_rollout after a solve (mpc.py:379-386) -- for the three
+    # call patterns its callers use: update(x_current, one_rollout=False) (run_simulation.py:106), one_rollout=True
+    # (mpc_to_wbid.py:158) and x_current=None.
+    for name, pname, over, kind, seed in UPDATE_CASES:
+        preset = presets.get_preset(pname, **over)
+        x0, xr, ct, ch, pc = make_inputs(kind, preset, seed)
+        ref = ref_loader.make_reference_mpc(preset)
+        res = {}
+        for tag, xc, one in (("full", x0, False), ("one", x0, True), ("nocur", None, False)):
+            ref.x_opt = np.zeros((preset["horizon"], 13))
+            u, x = ref_loader.reference_update(ref, x0, xr, ct, ch, pc, x_current=xc, one_rollout=one)
+            res["u_opt_" + tag], res["x_opt_" + tag] = u, x
+        np.savez_compressed(os.path.join(OUT, f"ref_update_{name}.npz"), preset=json.dumps(preset), x0=x0, x_ref=xr,
+                            contact=ct, c_horizon=ch, p_com=pc, H=ref.Hessian.copy(), g=ref.gradient.ravel().copy(), **res)
+        print("update", name, res["u_opt_full"].shape)
 
 
 if __name__ == "__main__":

@@ -2,8 +2,10 @@
 
 Only usable in the build container (the GPU box has no /root/reference); used by oracle/gen_golden.py to
 produce tests/golden/*.npz and by tests that are skipped when the reference tree is absent.
-`import osqp` at mpc.py:1 is satisfied by an empty stand-in module: no reference test or build step
-other than solve_qp() (mpc.py:323-358) touches it.
+`import osqp` at mpc.py:1 is satisfied by oracle/osqp_shim.py (OSQP().setup/.solve over the C restatement of the
+OSQP algorithm), so that solve_qp() (mpc.py:323-358) and with it the whole MPC.update() (mpc.py:360-377) run
+unmodified; the build steps never touch it.  `import matplotlib.pyplot` at gait_planner.py:2 is satisfied by an
+empty stand-in (only plot_gait() uses it).
 """
 import importlib.util
 import os
@@ -18,13 +20,40 @@ def available():
     return os.path.exists(REF_MPC_PY)
 
 
+REF_GAIT_PY = "/root/reference/g1_mpc/scripts/gait_planner.py"
+
+
 def load_module():
     if "osqp" not in sys.modules:
-        sys.modules["osqp"] = types.ModuleType("osqp")
+        from . import osqp_shim
+        sys.modules["osqp"] = osqp_shim
     spec = importlib.util.spec_from_file_location("g1_ref_mpc", REF_MPC_PY)
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     return mod
+
+
+def load_gait_planner():
+    """The reference's GaitPlanner class (gait_planner.py:4-62), imported unmodified."""
+    if "matplotlib" not in sys.modules:
+        mpl = types.ModuleType("matplotlib")
+        mpl.pyplot = types.ModuleType("matplotlib.pyplot")
+        sys.modules["matplotlib"], sys.modules["matplotlib.pyplot"] = mpl, mpl.pyplot
+    spec = importlib.util.spec_from_file_location("g1_ref_gait_planner", REF_GAIT_PY)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.GaitPlanner
+
+
+def reference_update(o, x0, xref, contact, c_hor, p_com, x_current=None, one_rollout=False):
+    """The reference's MPC.update() (mpc.py:360-377) end to end: build, solve_qp through the osqp shim, rollout."""
+    import contextlib, io
+    o.x0 = np.array(x0, float).copy()
+    o.x_ref_hor = np.array(xref, float).copy()
+    with contextlib.redirect_stdout(io.StringIO()):      # compute_rollout prints (mpc.py:389-391)
+        u, x = o.update(np.array(contact, float), np.array(c_hor, float), np.array(p_com, float),
+                        None if x_current is None else np.array(x_current, float), one_rollout)
+    return np.array(u, float).copy(), np.array(x, float).copy()
 
 
 def make_reference_mpc(preset):

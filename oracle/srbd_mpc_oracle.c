@@ -84,34 +84,50 @@ static void inv3(const double *M, double *R)
     R[6] = (d * h - e * g) * id; R[7] = (b * g - a * h) * id; R[8] = (a * e - b * d) * id;
 }
 
-/* in-place lower Cholesky of SPD n x n (row-major, full storage); returns 0 on success */
+/* dot product with four independent partial sums (fixed order: reproducible, and the compiler can keep four
+ * FMA chains in flight / use one AVX2 register -- a single running sum is latency bound at 4 cycles per term) */
+static inline double dot4(const double *a, const double *b, int n)
+{
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    int k = 0;
+    for (; k + 4 <= n; k += 4) { s0 += a[k] * b[k]; s1 += a[k + 1] * b[k + 1]; s2 += a[k + 2] * b[k + 2]; s3 += a[k + 3] * b[k + 3]; }
+    for (; k < n; k++) s0 += a[k] * b[k];
+    return (s0 + s1) + (s2 + s3);
+}
+
+/* in-place lower Cholesky of SPD n x n (row-major, full storage; the strict upper triangle receives L^T so that both
+ * triangular solves below stream contiguous rows); returns 0 on success */
 static int chol(double *A, int n)
 {
     for (int j = 0; j < n; j++) {
-        double d = A[(size_t)j * n + j];
-        for (int k = 0; k < j; k++) d -= A[(size_t)j * n + k] * A[(size_t)j * n + k];
+        double d = A[(size_t)j * n + j] - dot4(A + (size_t)j * n, A + (size_t)j * n, j);
         if (!(d > 0.0)) return -1;
         d = sqrt(d);
         A[(size_t)j * n + j] = d;
+        const double id = 1.0 / d;
         for (int i = j + 1; i < n; i++) {
-            double s = A[(size_t)i * n + j];
-            for (int k = 0; k < j; k++) s -= A[(size_t)i * n + k] * A[(size_t)j * n + k];
-            A[(size_t)i * n + j] = s / d;
+            const double v = (A[(size_t)i * n + j] - dot4(A + (size_t)i * n, A + (size_t)j * n, j)) * id;
+            A[(size_t)i * n + j] = v;
         }
     }
+    for (int j = 0; j < n; j++) for (int i = j + 1; i < n; i++) A[(size_t)j * n + i] = A[(size_t)i * n + j];
     return 0;
 }
 static void chol_solve(const double *L, int n, double *b)
 {
-    for (int i = 0; i < n; i++) {
-        double s = b[i];
-        for (int k = 0; k < i; k++) s -= L[(size_t)i * n + k] * b[k];
-        b[i] = s / L[(size_t)i * n + i];
+    /* forward: L y = b, column sweep over the rows of L^T (stored in the upper triangle) */
+    for (int k = 0; k < n; k++) {
+        const double yk = b[k] / L[(size_t)k * n + k];
+        b[k] = yk;
+        const double *lt = L + (size_t)k * n;
+        for (int i = k + 1; i < n; i++) b[i] -= lt[i] * yk;
     }
+    /* backward: L^T x = y, column sweep over the rows of L */
     for (int i = n - 1; i >= 0; i--) {
-        double s = b[i];
-        for (int k = i + 1; k < n; k++) s -= L[(size_t)k * n + i] * b[k];
-        b[i] = s / L[(size_t)i * n + i];
+        const double xi = b[i] / L[(size_t)i * n + i];
+        b[i] = xi;
+        const double *lr = L + (size_t)i * n;
+        for (int k = 0; k < i; k++) b[k] -= lr[k] * xi;
     }
 }
 
@@ -283,7 +299,9 @@ static double vinf(const double *v, int n) { double m = 0; for (int i = 0; i < n
 
 typedef struct {
     int n, m;
-    double *P, *A, *q, *l, *u;     /* scaled copies */
+    double *P, *q, *l, *u;         /* scaled copies */
+    int *Ap, *Aj; double *Ax;      /* A in CSR (row pointers, column indices, scaled values): OSQP keeps A sparse; only the
+                                      stored entries are touched, in column order, so sums equal the dense ones */
     double *D, *E, c;              /* scaling */
     double *rho_vec, *K;           /* K = chol(P + sigma I + A^T rho A) */
 } osqp_work;
@@ -299,12 +317,10 @@ static int osqp_factor(osqp_work *w, double rho, double sigma)
     memcpy(w->K, w->P, sizeof(double) * (size_t)n * n);
     for (int i = 0; i < n; i++) w->K[(size_t)i * n + i] += sigma;
     for (int r = 0; r < m; r++) {
-        const double *a = w->A + (size_t)r * n;
         const double rr = w->rho_vec[r];
-        for (int i = 0; i < n; i++) {
-            if (a[i] == 0.0) continue;
-            const double ai = rr * a[i];
-            for (int j = 0; j < n; j++) if (a[j] != 0.0) w->K[(size_t)i * n + j] += ai * a[j];
+        for (int ii = w->Ap[r]; ii < w->Ap[r + 1]; ii++) {
+            const double ai = rr * w->Ax[ii];
+            for (int jj = w->Ap[r]; jj < w->Ap[r + 1]; jj++) w->K[(size_t)w->Aj[ii] * n + w->Aj[jj]] += ai * w->Ax[jj];
         }
     }
     return chol(w->K, n);
@@ -317,7 +333,17 @@ int orc_osqp_solve(int n, int m, const double *P_in, const double *q_in, const d
 {
     osqp_work w; w.n = n; w.m = m;
     w.P = (double *)malloc(sizeof(double) * (size_t)n * n); memcpy(w.P, P_in, sizeof(double) * (size_t)n * n);
-    w.A = (double *)malloc(sizeof(double) * (size_t)m * n); memcpy(w.A, A_in, sizeof(double) * (size_t)m * n);
+    {   /* CSR of the non-zero entries of A (Ac is block diagonal with 5x3 blocks, mpc.cpp:296-322: 9 non-zeros per block) */
+        int nnz = 0;
+        for (size_t i = 0; i < (size_t)m * n; i++) nnz += A_in[i] != 0.0;
+        w.Ap = (int *)malloc(sizeof(int) * (m + 1)); w.Aj = (int *)malloc(sizeof(int) * (nnz + 1)); w.Ax = (double *)malloc(sizeof(double) * (nnz + 1));
+        int k = 0;
+        for (int i = 0; i < m; i++) {
+            w.Ap[i] = k;
+            for (int j = 0; j < n; j++) if (A_in[(size_t)i * n + j] != 0.0) { w.Aj[k] = j; w.Ax[k] = A_in[(size_t)i * n + j]; k++; }
+        }
+        w.Ap[m] = k;
+    }
     w.q = (double *)malloc(sizeof(double) * n); memcpy(w.q, q_in, sizeof(double) * n);
     w.l = (double *)malloc(sizeof(double) * m); w.u = (double *)malloc(sizeof(double) * m);
     for (int i = 0; i < m; i++) { /* bounds are clipped to +-OSQP_INFTY at setup */
@@ -337,13 +363,13 @@ int orc_osqp_solve(int n, int m, const double *P_in, const double *q_in, const d
         for (int i = 0; i < n; i++) for (int j = 0; j < n; j++) { double a = fabs(w.P[(size_t)i * n + j]); if (a > Dt[j]) Dt[j] = a; }
         for (int i = 0; i < m; i++) {
             double e = 0.0;
-            for (int j = 0; j < n; j++) { double a = fabs(w.A[(size_t)i * n + j]); if (a > Dt[j]) Dt[j] = a; if (a > e) e = a; }
+            for (int k = w.Ap[i]; k < w.Ap[i + 1]; k++) { double a = fabs(w.Ax[k]); if (a > Dt[w.Aj[k]]) Dt[w.Aj[k]] = a; if (a > e) e = a; }
             Et[i] = e;
         }
         for (int j = 0; j < n; j++) Dt[j] = 1.0 / sqrt(limit_scaling(Dt[j]));
         for (int i = 0; i < m; i++) Et[i] = 1.0 / sqrt(limit_scaling(Et[i]));
         for (int i = 0; i < n; i++) for (int j = 0; j < n; j++) w.P[(size_t)i * n + j] *= Dt[i] * Dt[j];
-        for (int i = 0; i < m; i++) for (int j = 0; j < n; j++) w.A[(size_t)i * n + j] *= Et[i] * Dt[j];
+        for (int i = 0; i < m; i++) for (int k = w.Ap[i]; k < w.Ap[i + 1]; k++) w.Ax[k] *= Et[i] * Dt[w.Aj[k]];
         for (int j = 0; j < n; j++) { w.q[j] *= Dt[j]; w.D[j] *= Dt[j]; }
         for (int i = 0; i < m; i++) w.E[i] *= Et[i];
         /* cost normalisation */
@@ -375,11 +401,10 @@ int orc_osqp_solve(int n, int m, const double *P_in, const double *q_in, const d
         for (int i = 0; i < m; i++) {
             const double t = w.rho_vec[i] * z[i] - y[i];
             if (t == 0.0) continue;
-            const double *a = w.A + (size_t)i * n;
-            for (int j = 0; j < n; j++) xt[j] += a[j] * t;
+            for (int k = w.Ap[i]; k < w.Ap[i + 1]; k++) xt[w.Aj[k]] += w.Ax[k] * t;
         }
         chol_solve(w.K, n, xt);
-        for (int i = 0; i < m; i++) { double s = 0; const double *a = w.A + (size_t)i * n; for (int j = 0; j < n; j++) s += a[j] * xt[j]; zt[i] = s; }
+        for (int i = 0; i < m; i++) { double s = 0; for (int k = w.Ap[i]; k < w.Ap[i + 1]; k++) s += w.Ax[k] * xt[w.Aj[k]]; zt[i] = s; }
         for (int j = 0; j < n; j++) x[j] = st->alpha * xt[j] + (1.0 - st->alpha) * x[j];
         for (int i = 0; i < m; i++) {
             const double zh = st->alpha * zt[i] + (1.0 - st->alpha) * z[i];
@@ -392,10 +417,10 @@ int orc_osqp_solve(int n, int m, const double *P_in, const double *q_in, const d
         const int adapt = (st->adaptive_rho && st->adaptive_rho_interval && iter % st->adaptive_rho_interval == 0);
         if (!check && !adapt && iter != st->max_iter) continue;
         /* residuals */
-        for (int i = 0; i < m; i++) { double s = 0; const double *a = w.A + (size_t)i * n; for (int j = 0; j < n; j++) s += a[j] * x[j]; Ax[i] = s; }
+        for (int i = 0; i < m; i++) { double s = 0; for (int k = w.Ap[i]; k < w.Ap[i + 1]; k++) s += w.Ax[k] * x[w.Aj[k]]; Ax[i] = s; }
         for (int i = 0; i < n; i++) { double s = 0; const double *pr = w.P + (size_t)i * n; for (int j = 0; j < n; j++) s += pr[j] * x[j]; Px[i] = s; }
         for (int j = 0; j < n; j++) Aty[j] = 0.0;
-        for (int i = 0; i < m; i++) { if (y[i] == 0.0) continue; const double *a = w.A + (size_t)i * n; for (int j = 0; j < n; j++) Aty[j] += a[j] * y[i]; }
+        for (int i = 0; i < m; i++) { if (y[i] == 0.0) continue; for (int k = w.Ap[i]; k < w.Ap[i + 1]; k++) Aty[w.Aj[k]] += w.Ax[k] * y[i]; }
         if (check || iter == st->max_iter) { /* unscaled termination (scaled_termination = 0) */
             double pr = 0, nAx = 0, nz = 0, dr = 0, nq = 0, nAty = 0, nPx = 0;
             for (int i = 0; i < m; i++) {
@@ -437,7 +462,7 @@ int orc_osqp_solve(int n, int m, const double *P_in, const double *q_in, const d
     for (int j = 0; j < n; j++) x_out[j] = w.D[j] * x[j];
     if (y_out) for (int i = 0; i < m; i++) y_out[i] = w.E[i] * y[i] / w.c;
     if (info) { info->iters = iter; info->status = rc ? -1 : status; info->rho_updates = rho_updates; info->prim_res = prim_res; info->dual_res = dual_res; info->rho_final = rho; }
-    free(w.P); free(w.A); free(w.q); free(w.l); free(w.u); free(w.D); free(w.E); free(w.rho_vec); free(w.K);
+    free(w.P); free(w.Ap); free(w.Aj); free(w.Ax); free(w.q); free(w.l); free(w.u); free(w.D); free(w.E); free(w.rho_vec); free(w.K);
     free(x); free(z); free(y); free(xt); free(zt); free(Ax); free(Px); free(Aty);
     return rc;
 }

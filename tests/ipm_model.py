@@ -171,9 +171,37 @@ def _contact_blocks(D, sr, mu):
     return Dinv, X
 
 
-def solve_ipm(prob, gap_tol=1e-10, max_iter=40, linear="riccati"):
+def warm_point(prob, u_prev, margin, shift=1):
+    """Start point from a previous solution (the kernel's warm start): u_prev shifted by `shift` stages (the last
+    stage repeated), pulled `margin` newtons inside every row of the friction pyramid / fz box so that the slacks
+    s = b - C u are consistent with u AND at least `margin`; contacts that were in swing in the shifted solution (or
+    whose box is narrower than 2 margin) get the cold start value."""
+    N, nc, mu = prob.N, prob.nc, prob.mu
+    u = np.zeros((N, nc, 3)); s = np.ones((N, nc, 6))
+    for k in range(N):
+        ns = int(prob.stance[k].sum())
+        kp = min(k + shift, N - 1)
+        for j in range(nc):
+            if not prob.stance[k, j]:
+                continue
+            lo, hi = prob.lo[k, j], prob.hi[k, j]
+            f = np.array(u_prev[kp, j], float)
+            m = min(margin, 0.1 * (hi - lo))
+            if f[2] <= 0.0:                                   # was a swing contact: cold value
+                span = hi - lo
+                f = np.array([0.0, 0.0, min(max(prob.weight / ns, lo + 0.1 * span), hi - 0.1 * span)])
+            f[2] = min(max(f[2], lo + m), hi - m)
+            lim = max(mu * f[2] - m, 0.0)
+            f[0] = min(max(f[0], -lim), lim); f[1] = min(max(f[1], -lim), lim)
+            u[k, j] = f
+            s[k, j] = [mu * f[2] - f[0], mu * f[2] + f[0], mu * f[2] - f[1], mu * f[2] + f[1], hi - f[2], f[2] - lo]
+    return u, s
+
+
+def solve_ipm(prob, gap_tol=1e-10, max_iter=40, linear="riccati", warm=None, trace=None):
     """Returns u[N,nc,3], iters, gap.  `linear`: "stage" (what the kernel runs), "riccati" (textbook stage-wise),
-    "dense" (6N x 6N Woodbury matrix) or "stage_s" (the stage form with S_k Gamma formed as a product: what the kernel ran before Theta_k)."""
+    "dense" (6N x 6N Woodbury matrix) or "stage_s" (the stage form with S_k Gamma formed as a product: what the kernel ran before Theta_k).
+    `warm` = dict(u=previous solution [N,nc,3], margin=, mu0=, shift=): start from warm_point() with lambda = mu0 / s."""
     N, nc, mu, sr, bv = prob.N, prob.nc, prob.mu, prob.sr, prob.bv
     M, h = prob.M_h()
     st = prob.stance
@@ -195,15 +223,28 @@ def solve_ipm(prob, gap_tol=1e-10, max_iter=40, linear="riccati"):
         v = (M @ w.ravel() + h).reshape(N, 6)
         return np.array([sr * u[k].ravel() + Wk[k].T @ v[k] for k in range(N)]).reshape(N, nc, 3)
 
+    if warm is not None:
+        u, s = warm_point(prob, warm["u"], warm["margin"], warm.get("shift", 1))
     gf = grad(u)
     mu0 = max(1e-2, 0.1 * np.abs(gf[st]).max()) if st.any() else 0.0
+    if warm is not None:
+        mu0 = warm["mu0"]
     lam[st] = mu0 / s[st]
+    gap_start = mu0
     it = 0
     exact = True            # the kernel carries grad f along with the step while the gap is large (srbd_solve_warp.cuh)
     while True:
         if exact:
             gf = grad(u)
         gap = float((s[st] * lam[st]).sum() / m_ineq) if st.any() else 0.0
+        if trace is not None:
+            trace.append((it, gap))
+        if warm is not None and it == warm.get("fallback_it", 4) and gap > warm.get("fallback_ratio", 0.5) * gap_start:
+            # Safeguard of the warm start (mirrors the kernel): a start point whose multipliers are far off stalls close to
+            # the boundary (steps of a few per cent for tens of iterations).  If the gap has not halved after 4 iterations
+            # the problem is restarted from the cold point; the iterations spent are counted.
+            u2, it2, gap2 = solve_ipm(prob, gap_tol, max_iter - it, linear, None, trace)
+            return u2, it + it2, gap2
         if gap <= gap_tol or not st.any() or it >= max_iter:
             if not exact:
                 exact = True

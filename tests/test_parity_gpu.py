@@ -6,7 +6,7 @@ import pytest
 import torch
 
 from conftest import golden_cases, load_golden, rel_err
-from g1_locomotion_b200 import presets, inputs
+from g1_locomotion_b200 import presets, inputs, BatchedMPC
 
 pytestmark = pytest.mark.gpu
 
@@ -440,17 +440,15 @@ def test_empty_and_ragged_batches():
         assert np.array_equal(infoh["status"], info_all["status"][:B].cpu().numpy())
 
 
-def test_two_problems_per_warp_layout_gives_the_same_bits(monkeypatch):
-    """Above 4 problems per SM the solve kernel runs two problems per warp (16 lanes each); G1MPC_PPW forces one layout.
+def test_two_problems_per_warp_layout_gives_the_same_bits():
+    """Above 4 problems per SM the solve kernel runs two problems per warp (16 lanes each); g1mpc_params.layout forces one.
     Per problem the arithmetic is the same operation for operation (the sums over contacts are ordered by virtual lane,
     the two trailing A22 columns follow from L and D as the column solve produces them), so everything returned must be
     bit-identical: forces, states, iteration counts, residuals, multipliers -- odd batch sizes included."""
     preset = presets.get_preset("cpp_node")
-    monkeypatch.setenv("G1MPC_PPW", "1")
-    s1 = _solver(preset)
-    monkeypatch.setenv("G1MPC_PPW", "2")
-    s2 = _solver(preset)
-    monkeypatch.delenv("G1MPC_PPW")
+    s1 = BatchedMPC(preset, device=0, layout=1)
+    s2 = BatchedMPC(preset, device=0, layout=2)
+    assert s1.kernel_info(2049)["problems_per_warp"] == 1 and s2.kernel_info(3)["problems_per_warp"] == 2
     full = list(inputs.random_batch(preset, 2049, seed=5, device="cuda"))
     walk = _dev(inputs.walking_batch(preset, 256))
     for ins in (full, walk, [t[:1].contiguous() for t in full], [t[:3].contiguous() for t in full], [t[:0].contiguous() for t in full]):
