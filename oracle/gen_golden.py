@@ -82,5 +82,34 @@ def main():
         print("update", name, res["u_opt_full"].shape)
 
 
+def gait_golden():
+    """GaitPlanner.plan_gait of the REFERENCE class (gait_planner.py, imported unmodified) mapped onto (contact, c_horizon)
+    by main.py:259-285 (restated in oracle/node_oracle.map_gait_phases -- the mapping lives inside main() and cannot be called),
+    for a few planners and query times, N = 10 and 15."""
+    from oracle import node_oracle
+    GP = ref_loader.load_gait_planner()
+    planners = [(1000., 0.25, 0.1, 0.2, 100), (0.2, 0.8, 0.3, 0.2, 10), (0.5, 0.8, 0.3, 0.2, 10), (0.13, 0.07, 0.033, 0.11, 37),
+                (0.0, 0.3, 0.25, 0.15, 5), (0.4, 0.1, 0.05, 0.1, 0)]
+    rows = []
+    for pl in planners:
+        phases = GP(pl[0], pl[1], pl[2], pl[3], int(pl[4])).plan_gait()
+        ours = node_oracle.plan_gait(*pl)
+        assert len(ours) == len(phases)
+        for a, b in zip(ours, phases):      # the restated planner is the reference planner, bit for bit
+            assert a["start_time"] == b["start_time"] and a["end_time"] == b["end_time"] and a["support_leg"] == b["support_leg"]
+            assert np.array_equal(a["left_foot"], b["left_foot"]) and np.array_equal(a["right_foot"], b["right_foot"])
+        span = phases[-1]["end_time"]
+        for t in list(np.linspace(0.0, min(span, 12.0) * 1.1, 23)) + [phases[1]["start_time"] if len(phases) > 1 else 0.0, -0.5]:
+            for N, dt in ((10, 0.05), (15, 0.04)):
+                ct, ch = node_oracle.map_gait_phases(phases, float(t), N, dt, 0.08)
+                rows.append(dict(planner=np.array(pl, float), t=float(t), N=N, dt=dt, contact=ct, c_horizon=ch))
+    np.savez_compressed(os.path.join(OUT, "gait_plan.npz"), planner=np.stack([r["planner"] for r in rows]), t=np.array([r["t"] for r in rows]),
+                        N=np.array([r["N"] for r in rows]), dt=np.array([r["dt"] for r in rows]),
+                        contact=np.stack([np.pad(r["contact"], ((0, 15 - r["N"]), (0, 0))) for r in rows]),
+                        c_horizon=np.stack([np.pad(r["c_horizon"], ((0, 15 - r["N"]), (0, 0))) for r in rows]))
+    print("gait_plan", len(rows), "cases")
+
+
 if __name__ == "__main__":
     main()
+    gait_golden()

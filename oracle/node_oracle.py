@@ -70,6 +70,93 @@ def node_update_inputs(x0, contacts_now, sim_time, x_opt_prev, x_ref_prev, dt, N
     return x_ref, contact.astype(float), c_hor, p_com, np.array(land_pub)
 
 
+def map_gait_phases(phases, current_time, N, dt, foot_offset=0.08):
+    """main.py:259-285 -- the lookup of the planner's phase list per horizon step and its mapping onto
+    (contact_horizon [N,4], c_horizon [N,12]); `phases` is what GaitPlanner.plan_gait returns (gait_planner.py:27-62)."""
+    c_horizon, contact_horizon = [], []
+    for i in range(N):
+        t_i = current_time + i * dt                              # :263
+        phase = None
+        for ph in phases:                                        # :265-268
+            if ph["start_time"] <= t_i < ph["end_time"]:
+                phase = ph
+                break
+        if phase is None:                                        # :270-271
+            phase = phases[-1]
+        left = np.hstack((np.array(phase["left_foot"]), 0))      # :273-274
+        right = np.hstack((np.array(phase["right_foot"]), 0))
+        off = np.array([foot_offset, 0, 0])
+        c_horizon.append(np.concatenate((left - off, left + off, right - off, right + off)))     # :276-281
+        lc = 1 if phase["support_leg"] in ["both", "left"] else 0                                # :282-283
+        rc = 1 if phase["support_leg"] in ["both", "right"] else 0
+        contact_horizon.append([lc, lc, rc, rc])
+    return np.array(contact_horizon, float), np.array(c_horizon, float)
+
+
+def plan_gait(double_support_time, single_support_time, step_length, step_width, num_steps):
+    """GaitPlanner.__init__ + plan_gait restated (gait_planner.py:5-62): the phase list, with the same running sums."""
+    left, right = np.array([0.0, -step_width]), np.array([0.0, step_width])                      # :19-20
+    t = 0.0
+    phases = [dict(start_time=t, end_time=t + double_support_time, left_foot=left.copy(), right_foot=right.copy(), support_leg="both")]
+    t += double_support_time
+    for i in range(int(num_steps)):
+        leg = "left" if i % 2 == 0 else "right"
+        phases.append(dict(start_time=t, end_time=t + single_support_time, left_foot=left.copy(), right_foot=right.copy(), support_leg=leg))
+        t += single_support_time
+        inc = step_length if i == 0 else 2 * step_length
+        if leg == "left":
+            right = right + np.array([inc, 0.0])
+        else:
+            left = left + np.array([inc, 0.0])
+    return phases
+
+
+def double_support_reference(x_ref, current_time, total_duration, dt):
+    """testing_double_support, main.py:177-197 (in place on x_ref[N,13])."""
+    for i in range(x_ref.shape[0]):
+        t_ref = current_time + i * dt
+        if t_ref < total_duration / 4:
+            ref = (0.0, 0.1, 1.0)
+        elif t_ref < total_duration / 2:
+            ref = (0.0, 0.0, 1.0)
+        elif t_ref < 3 * total_duration / 4:
+            ref = (0.0, 0.0, 0.7)
+        else:
+            ref = (0.01, 0.0, 1.0)
+        x_ref[i, 3:6] = ref
+    return x_ref
+
+
+def main_loop(orc, preset, planner, ticks, total_duration=4.0, foot_offset=0.08):
+    """The SRBD-only loop of g1_mpc/scripts/main.py:200-326 for ONE walker on the CPU: planner phases -> mapping ->
+    reference build (oracle.build) -> exact QP minimiser -> x_opt[0] carry and rollout without x_current (main.py:306-311);
+    the next solve starts from x_opt[2] (main.py:228).  Returns traj_x[ticks,13] (x_opt[0] after each rollout), traj_u[ticks,12]."""
+    N, dt, g = preset["horizon"], preset["dt"], preset.get("gravity", -9.80665)
+    p = orc.params_from_dict(preset)
+    phases = plan_gait(*planner)
+    x_ref = np.zeros((N, 13)); x_ref[:, 12] = g; x_ref[:, 5] = 1.0         # main.py:207-209
+    x_opt = np.zeros((N, 13))
+    t = 0.0
+    tx, tu = np.zeros((ticks, 13)), np.zeros((ticks, 12))
+    for k in range(ticks):
+        if k == 0:
+            x0 = x_ref[0].copy()                                          # main.py:226
+        else:
+            x0 = x_opt[2].copy()                                          # main.py:228
+            double_support_reference(x_ref, t, total_duration, dt)        # main.py:230
+        contact, c_hor = map_gait_phases(phases, t, N, dt, foot_offset)
+        p_com = x_ref[:, 3:6].copy()                                      # main.py:286
+        m = orc.build(p, x0, x_ref, contact, c_hor, p_com)
+        xs, _, cert = orc.qp_exact(p, m["H"], m["g"], contact)
+        assert cert["rc"] == 0, cert
+        u = xs.reshape(N, 12)
+        x_opt[0] = x0 if k == 0 else x_opt[1].copy()                      # main.py:306-310
+        x_opt = orc.rollout(p, m["A"], m["Bd"], u, None, False, x_opt=x_opt)
+        tx[k], tu[k] = x_opt[0], u[0]
+        t += dt                                                           # main.py:326
+    return tx, tu
+
+
 def _euler_matrix_sxyz(ai, aj, ak):
     """tf.transformations.euler_matrix(ai, aj, ak, 'sxyz')[0:3,0:3] (static x-y-z: i=0, j=1, k=2, no repetition, parity even)."""
     si, sj, sk = math.sin(ai), math.sin(aj), math.sin(ak)

@@ -31,7 +31,7 @@ def test_library_exports_every_declared_symbol():
 def test_params_struct_matches_header_layout():
     # 2 int32 + 6 double + 9 + 13 + 2 double + 1 double + 2 int32 + 3 double
     assert C.sizeof(_lib.G1mpcParams) == 8 + 8 * 6 + 8 * 9 + 8 * 13 + 8 * 2 + 8 + 8 + 8 * 3
-    assert _lib.G1mpcParams.layout.offset == 268 and _lib.G1mpcParams.dual_tol.offset == 272
+    assert _lib.G1mpcParams.layout.offset == 260 and _lib.G1mpcParams.dual_tol.offset == 264
     assert _lib.G1mpcParams.mu.offset == 8 and _lib.G1mpcParams.inertia_body.offset == 56
 
 
