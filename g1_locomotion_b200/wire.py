@@ -48,8 +48,13 @@ def _state_row(s):
 
 
 def _stamp(t):
+    """ros::Time(double) / fromSec: seconds floored, nanoseconds rounded, and a fraction that rounds up to a full second
+    carried into `secs` (ros/time.h normalizeSecNSec) -- not wrapped to zero, which would put the stamp one second early."""
     secs = int(np.floor(t))
-    return {"secs": secs, "nsecs": int(round((t - secs) * 1e9)) % 1000000000}
+    nsecs = int(round((t - secs) * 1e9))
+    if nsecs >= 1000000000:
+        secs, nsecs = secs + 1, nsecs - 1000000000
+    return {"secs": secs, "nsecs": nsecs}
 
 
 # ---- simulator -> node: /srbd_current ------------------------------------------------------------------------

@@ -71,3 +71,18 @@ def test_batch_helpers_feed_the_batched_path_shapes():
     assert np.array_equal(x0[:, :12], batch[0][:, :12]) and np.array_equal(now, batch[3][:, 0])
     out = wire.pack_mpc_solution_batch(batch[1], np.zeros((B, N, 12)), batch[3], batch[2], np.zeros((B, 2)), t)
     assert len(out) == B and all(len(m["states_horizon"]) == N for m in out)
+
+
+def test_stamp_carries_a_fraction_that_rounds_up_to_a_full_second():
+    """sim_time accumulated by += dt lands a hair below whole seconds (2.9999999999999973 after 60 ticks of 0.05): the
+    nanosecond field then rounds to 1e9 and must carry into the seconds (ros::Time::fromSec), not wrap to zero."""
+    assert wire._stamp(2.9999999999999973) == {"secs": 3, "nsecs": 0}
+    t, worst = 0.0, 0.0
+    for k in range(4000):
+        st = wire._stamp(t)
+        assert 0 <= st["nsecs"] < 1000000000
+        worst = max(worst, abs(st["secs"] + 1e-9 * st["nsecs"] - t))
+        # the time that round-trips through the message gives the node the same gait phase (mpc_to_wbid_node.cpp:105)
+        assert int(np.floor((st["secs"] + 1e-9 * st["nsecs"] + 1e-9) / 0.05)) == int(np.floor((t + 1e-9) / 0.05)), (k, t, st)
+        t += 0.05
+    assert worst < 1e-9
