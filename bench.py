@@ -10,9 +10,11 @@ data-path collective; one NCCL all_gather of the first-step results after the ti
 separately (`gather_ms`).  Prints ONE JSON line on rank 0.
 
 `--impl reference` times the CPU restatement of the reference path (oracle/srbd_mpc_oracle.c: build as
-coded + OSQP-style ADMM with the reference's default settings) on all host threads; the reference's own
-C++ (needs Eigen/OSQP/OsqpEigen) cannot be built on this image and /root/reference does not exist on
-the GPU box, so kind = "port".
+coded + OSQP-style ADMM with the reference's default settings, constraint matrix in CSR, vectorisable
+Cholesky) on all host threads over the SAME 1,024 problems per step; the reference's own C++ (needs
+Eigen/OSQP/OsqpEigen) cannot be built on this image and /root/reference does not exist on the GPU box,
+so kind = "port".  The reference's own Python class (mpc.py + the osqp shim) was timed in the build
+container by oracle/time_reference_py.py; its committed result is quoted as `cpu_baseline.reference_py`.
 """
 import argparse
 import json
@@ -30,11 +32,49 @@ if ROOT not in sys.path:
 METRIC = "batched MPC build+solve/sec (N=10, whole box, device-timed)"
 UNIT = "problems/s"
 BATCH = 1024
-# dram__bytes_read.sum + dram__bytes_write.sum of one solve launch at B=1024 from the committed `ncu --set full`
-# capture (profiles/r1_v8_ncu_full_summary.csv: 2.827520 MB read, 0 B written): inputs are read once, the 2 MB of
-# outputs stay in L2.
-NCU_TRAFFIC_BYTES = 2827520
+# roofline.traffic = dram__bytes_read.sum + dram__bytes_write.sum of one solve launch at B = 1,024, READ at run time from the
+# newest committed `ncu --set full` summary of that launch (profiles/r*_ncu_full_summary.csv, written by
+# profiles/ncu_summary.py); null when no summary is found or its kernel / grid does not match the launch being timed.
 WORKLOAD = "configs[1]: 1,024 independent G1 SRBD MPC problems per GPU (cpp_node preset, N=10, nc=4, walking gait schedule)"
+
+
+def bench_config():
+    """`config` of the JSON line -- the same dict on both arms, so that the driver sees one configuration."""
+    return {"workload": WORKLOAD, "batch_per_gpu": BATCH, "preset": "cpp_node", "horizon": 10, "num_contacts": 4,
+            "problems_per_step": "1,024 per GPU (weak scaling)"}
+
+
+def ncu_traffic(kernel_substr, grid):
+    """(bytes, source file) from the newest committed ncu summary whose kernel name and grid match, else (None, reason)."""
+    import csv
+    import glob
+    import re
+    best = None
+    for f in glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_summary*.csv")):
+        m = re.match(r"r(\d+)_v?(\d+)", os.path.basename(f))
+        key = (int(m.group(1)), int(m.group(2))) if m else (0, 0)
+        try:
+            rows = {r[0]: r for r in csv.reader(open(f)) if len(r) >= 3}
+        except Exception:
+            continue
+        if kernel_substr not in rows.get("Kernel Name", ["", "", ""])[2] or rows.get("Grid Size", ["", "", ""])[2].replace(" ", "") != grid:
+            continue
+        unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        try:
+            tot = sum(float(rows[k][2]) * unit[rows[k][1]] for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
+        except Exception:
+            continue
+        if best is None or key > best[0]:
+            best = (key, tot, os.path.relpath(f, ROOT))
+    return (best[1], best[2]) if best else (None, "no committed ncu summary matches this kernel and grid")
+
+
+def iters_stats(iters):
+    """p50 / p99 / max and the histogram of the interior-point iteration counts of one batch (SURVEY section 5 'Metrics')."""
+    it = np.asarray(iters.cpu().numpy() if hasattr(iters, "cpu") else iters).astype(np.int64)
+    h = np.bincount(it)
+    return {"mean": float(it.mean()), "p50": float(np.percentile(it, 50)), "p99": float(np.percentile(it, 99)), "max": int(it.max()),
+            "histogram": {str(k): int(v) for k, v in enumerate(h) if v}}
 
 
 def algorithmic_flops(N, nc, iters_mean, stance_mean):
@@ -123,6 +163,16 @@ def cpu_reference_pass(preset, batch, nthreads):
     return time.perf_counter() - t0
 
 
+def reference_py_record():
+    """The reference's own Python class timed in the build container (oracle/time_reference_py.py) -- it cannot run on the GPU box."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "r2_reference_py_cpu.json")))
+        d["note"] = "measured in the build container, NOT on this box (/root/reference does not travel); quoted for scale only"
+        return d
+    except Exception:
+        return None
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
@@ -130,23 +180,30 @@ def run_reference(args, rank, world):
     from oracle import oracle
     oracle.build_lib()
     preset = presets.get_preset("cpp_node")
-    sample_B = 256
-    batch = [a[:sample_B] for a in inputs.walking_batch(preset, sample_B)]
+    batch = list(inputs.walking_batch(preset, BATCH))                       # the same 1,024 problems the GPU arm's rank 0 solves
     cores = host_threads()         # torchrun exports OMP_NUM_THREADS=1: the reference arm uses every host thread anyway
-    for _ in range(max(args.warmup, 1)):
+    for _ in range(max(min(args.warmup, 2), 1)):
         cpu_reference_pass(preset, batch, cores)
     times = [cpu_reference_pass(preset, batch, cores) for _ in range(args.steps)]
     total = float(np.sum(times))
-    value = sample_B * args.steps / total
-    sample = f"{sample_B} of the 1,024 walking problems per step, {args.steps} steps, OpenMP over {cores} threads"
+    value = BATCH * args.steps / total
+    t1 = cpu_reference_pass(preset, [a[:64] for a in batch], 1) / 64
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "cpu_impl": "oracle/srbd_mpc_oracle.c (mpc.cpp restatement + OSQP-style ADMM, defaults eps 1e-3)"},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": bench_config(),
+            "cpu_baseline": cpu_baseline_record(value, cores, f"all {BATCH} walking problems per step, {args.steps} steps, OpenMP over {cores} threads", t1),
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
+
+
+def cpu_baseline_record(value, cores, sample, t1):
+    return {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+            "impl": "oracle/srbd_mpc_oracle.c: mpc.cpp build as coded + OSQP restatement (defaults: eps 1e-3, adaptive rho every 100 "
+                    "iterations, cold start), CSR constraint matrix, one Cholesky per rho update",
+            "single_core_ms_per_solve": 1e3 * t1,
+            "accuracy_note": "stops at OSQP's eps 1e-3 (forces O(100 N) from the minimiser); the GPU arm solves to a gap of 1e-10",
+            "reference_py": reference_py_record()}
 
 
 def main():
@@ -156,10 +213,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-extras", action="store_true", help="skip the config-3 throughput and B=1 latency extras")
+    ap.add_argument("--no-extras", action="store_true", help="skip configs 3/4/5, the latency legs and the next-row adaptors")
     ap.add_argument("--config5", action="store_true",
-                    help="BASELINE.json configs[4] instead of the headline: 2^20 random problems cut into contiguous shards over the "
-                         "ranks (strong scaling), generated on the device, one result gather; prints its own JSON line")
+                    help="BASELINE.json configs[4] alone: 2^20 random problems cut into contiguous shards over the ranks (strong "
+                         "scaling), generated on the device, one result gather; prints its own JSON line")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -193,7 +250,9 @@ def main():
     N, nc = preset["horizon"], preset["num_contacts"]
     solver = BatchedMPC(preset, device=local_rank)
     if args.config5:
-        run_config5(args, solver, preset, dev, rank, world)
+        line = run_config5(args, solver, preset, dev, rank, world)
+        if rank == 0:
+            print(json.dumps(line), flush=True)
         if world > 1:
             dist.barrier()
             dist.destroy_process_group()
@@ -211,11 +270,26 @@ def main():
         if world > 1:
             dist.barrier()
 
+    def allmax(vals):
+        t = torch.tensor(vals, device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return [float(v) for v in t.tolist()]
+
+    def allgather(val):
+        t = torch.tensor([val], device=dev, dtype=torch.float64)
+        if world == 1:
+            return [float(val)]
+        out = torch.empty(world, device=dev, dtype=torch.float64)
+        dist.all_gather_into_tensor(out, t)
+        return [float(v) for v in out.tolist()]
+
     for _ in range(max(args.warmup, 3)):
         _, _, info = step()
     torch.cuda.synchronize()
     assert int((info["status"] != 0).sum()) == 0, "unsolved problems in the bench batch"
     iters_mean = float(info["iters"].double().mean())
+    it_stats = iters_stats(info["iters"])
 
     starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
@@ -271,6 +345,26 @@ def main():
     e2e_s = time.perf_counter() - t0
     barrier()
     assert int((inf_p["status"] != 0).sum()) == 0 and np.array_equal(u_p, uh), "pipelined host API differs from the synchronous call"
+    # (c) where a step's time goes on THIS rank: the copies alone (page-locked buffers, CUDA events on the copy stream), the kernel
+    #     alone (above), and what is left of a blocking step = host work (ctypes, staging memcpy, stream synchronise)
+    cp = torch.cuda.Stream(device=dev)
+    d_in = [torch.empty_like(t) for t in ins]
+    h_in = [torch.as_tensor(a) for a in hin]
+    h_out = [torch.as_tensor(outs[0]["u_opt"]), torch.as_tensor(outs[0]["x_opt"])]
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    h2d_ms = d2h_ms = 0.0
+    with torch.cuda.stream(cp):
+        for rep in range(12):
+            ev[0].record(cp)
+            for d, h in zip(d_in, h_in):
+                d.copy_(h, non_blocking=True)
+            ev[1].record(cp)
+            h_out[0].copy_(u_opt, non_blocking=True); h_out[1].copy_(x_opt, non_blocking=True)
+            ev[2].record(cp)
+            cp.synchronize()
+            if rep >= 2:
+                h2d_ms += ev[0].elapsed_time(ev[1]) / 10; d2h_ms += ev[1].elapsed_time(ev[2]) / 10
+    barrier()
 
     # result collection over NCCL (first-step GRFs + x_opt[1], what the WBID layer consumes)
     gather_ms = None
@@ -284,13 +378,19 @@ def main():
         assert gathered.shape[0] == world * BATCH
         gather_ms = float(g0.elapsed_time(g1))
 
-    tot = torch.tensor([dev_ms, e2e_s, gather_ms or 0.0, e2e_sync_s], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(tot, op=dist.ReduceOp.MAX)
-    dev_ms_max, e2e_s_max, gather_ms_max, e2e_sync_s_max = [float(v) for v in tot.tolist()]
+    dev_ms_max, e2e_s_max, gather_ms_max, e2e_sync_s_max = allmax([dev_ms, e2e_s, gather_ms or 0.0, e2e_sync_s])
+    per_rank = {"kernel_ms_per_step": allgather(per_launch_ms), "e2e_pipelined_ms_per_step": allgather(1e3 * e2e_s / e2e_pipe_steps),
+                "e2e_blocking_ms_per_step": allgather(1e3 * e2e_sync_s / e2e_steps), "h2d_ms_per_step": allgather(h2d_ms),
+                "d2h_ms_per_step": allgather(d2h_ms), "ipm_iters_max": allgather(it_stats["max"])}
     value = world * BATCH * args.steps / (dev_ms_max * 1e-3)
     e2e_value = world * BATCH * e2e_pipe_steps / e2e_s_max
     e2e_sync_value = world * BATCH * e2e_steps / e2e_sync_s_max
+
+    # legs every rank takes part in: the 65,536-per-rank weak-scaling figure and BASELINE.json configs[4] (2^20 problems, strong scaling)
+    collective = None
+    if not args.no_extras:
+        collective = {"weak_65536_per_gpu": run_weak_65536(solver, preset, dev, rank, world),
+                      "config5": run_config5(args, solver, preset, dev, rank, world)}
 
     if rank == 0:
         stance_mean = float((ins[2] > 0).double().sum() / BATCH)
@@ -304,13 +404,17 @@ def main():
             pass
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         by = algorithmic_bytes(N, nc) * BATCH
+        kinfo = solver.kernel_info(BATCH)
+        ppw = kinfo["problems_per_warp"]
+        kname = "srbd_mpc_solve_warp_kernel<v2::WLay<10, 4>, %d>" % (32 // ppw)
+        traffic, traffic_src = ncu_traffic("srbd_mpc_solve_warp_kernel", "(%d,1,1)" % ((BATCH + ppw - 1) // ppw))
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
                 "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "f64", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "batch_per_gpu": BATCH, "preset": "cpp_node", "l2": "flushed between timed steps (256 MiB fill)",
-                           "ipm_iters_mean": iters_mean, "kernel": solver.kernel_info(BATCH)},
+                "dtype": "f64", "data": "synthetic", "config": bench_config(),
+                "timing": {"l2": "flushed between timed steps (256 MiB fill, outside the event pair)", "clock": "CUDA events on the launching stream, max over ranks"},
+                "solver": {"ipm_iters": it_stats, "kernel": kinfo, "gap_tol": 1e-10, "dual_tol": 1e-6},
                 "roofline": {"bound": "fp64", "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach_tf / peak_tf if peak_tf else None,
-                             "traffic": NCU_TRAFFIC_BYTES, "kernel": "v2::srbd_mpc_solve_warp_kernel<10,4,16>", "flops_per_problem": fl / BATCH,
+                             "traffic": traffic, "traffic_source": traffic_src, "kernel": kname, "flops_per_problem": fl / BATCH,
                              "peak_source": "g1mpc_fp64_peak_tflops DFMA microbenchmark, measured in this run (MEASURED_PEAKS.json has no FP64 entry)",
                              "hbm": {"bound": "hbm", "achieved": by / (per_launch_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                                      "frac": by / (per_launch_ms * 1e-3) / 1e9 / hbm_peak, "bytes_per_problem": by / BATCH,
@@ -320,17 +424,53 @@ def main():
                         "api": "BatchedMPC.update_host_begin/_end -> g1mpc_update_host_begin/_end: %d batches in flight, caller "
                                "buffers page-locked (inputs copied host->device and results device->host every step)" % depth,
                         "sync": {"value": e2e_sync_value, "steps": e2e_steps,
-                                 "api": "BatchedMPC.update_host -> g1mpc_update_host, one blocking call per step, pageable numpy buffers"}},
+                                 "api": "BatchedMPC.update_host -> g1mpc_update_host, one blocking call per step, pageable numpy buffers"},
+                        "per_rank": per_rank,
+                        "breakdown_note": "per rank and step: copies alone (page-locked, CUDA events on a copy stream), kernel alone, one blocking "
+                                          "step, one pipelined step; blocking - (h2d + kernel + d2h) = host work of the call (ctypes, staging "
+                                          "memcpy of 5 MB, synchronise), which is what the ranks of one box compete for"},
                 "gpu_launches": args.steps, "clocks": clk.summary(), "wall_s_timed_region": t_wall,
                 "gather_ms": gather_ms_max if world > 1 else None}
         if not args.no_extras:
             line["extras"] = extras(solver, preset, dev)
+            line["extras"].update(collective)
+            if world == 1:
+                line["extras"]["config3_65536_random"] = collective["weak_65536_per_gpu"]      # configs[2]: the same launch
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline(preset, host_batch)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def run_weak_65536(solver, preset, dev, rank, world):
+    """65,536 random problems PER RANK (config-3 distribution, seed 7 + rank), one launch, max over ranks: the weak-scaling
+    figure of the throughput regime beside the one-wave 1,024-problem headline."""
+    import torch
+    import torch.distributed as dist
+    from g1_locomotion_b200 import inputs
+    B = 65536
+    ins = list(inputs.random_batch(preset, B, seed=7 + rank, device=dev))
+    for _ in range(2):
+        _, _, info = solver.update_batch(*ins, x_current=ins[0], want_resid=False)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(3):
+        solver.update_batch(*ins, x_current=ins[0], want_resid=False)
+    e1.record(); torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / 3, float((info["status"] != 0).sum())], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    out = {"problems_per_s": world * B / (float(t[0]) * 1e-3), "ms_per_launch": float(t[0]), "n_gpus": world, "unsolved_max_per_rank": int(t[1]),
+           "note": "inputs (315 MB per rank) exceed the 126 MB L2"}
+    if rank == 0:
+        out["ipm_iters"] = iters_stats(info["iters"])
+        out["kernel"] = solver.kernel_info(B)
+    return out
 
 
 def run_config5(args, solver, preset, dev, rank, world):
@@ -346,7 +486,7 @@ def run_config5(args, solver, preset, dev, rank, world):
     N, nc = preset["horizon"], preset["num_contacts"]
     u_opt = torch.empty(hi - lo, N, 3 * nc, device=dev, dtype=torch.float64)
     x_opt = torch.empty(hi - lo, N, 13, device=dev, dtype=torch.float64)
-    steps, warm = min(args.steps, 5), 2
+    steps, warm = 3, 1
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
           for _ in range(steps)]
     for k in range(warm + steps):
@@ -370,15 +510,16 @@ def run_config5(args, solver, preset, dev, rank, world):
     if world > 1:
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
-    if rank == 0:
-        print(json.dumps({"metric": "config 5: 2^20-problem batch sharded across the GPUs of one box (build+solve/sec, device-timed)",
-                          "value": total / (float(mx[0]) * 1e-3), "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warm,
-                          "ms_per_step": float(mx[0]), "gather_ms": float(mx[1]), "value_with_gather": total / ((float(mx[0]) + float(mx[1])) * 1e-3),
-                          "higher_is_better": True, "scaling": "strong", "dtype": "f64", "data": "synthetic",
-                          "config": {"workload": "configs[4]: 1,048,576 random problems (config-3 distribution, seed 13 + rank per shard), "
-                                                 "contiguous shards, inputs generated on the device (far larger than L2)",
-                                     "problems_per_gpu": hi - lo, "gather_bytes": total * 200, "kernel": solver.kernel_info(hi - lo)},
-                          "unsolved": int(t[2]), "ipm_iters_mean": float(t[3]) / total}), flush=True)
+    del ins, u_opt, x_opt, gathered
+    torch.cuda.empty_cache()
+    return {"metric": "config 5: 2^20-problem batch sharded across the GPUs of one box (build+solve/sec, device-timed)",
+            "value": total / (float(mx[0]) * 1e-3), "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warm,
+            "ms_per_step": float(mx[0]), "gather_ms": float(mx[1]), "value_with_gather": total / ((float(mx[0]) + float(mx[1])) * 1e-3),
+            "higher_is_better": True, "scaling": "strong", "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "configs[4]: 1,048,576 random problems (config-3 distribution, seed 13 + rank per shard), "
+                                   "contiguous shards, inputs generated on the device (far larger than L2)",
+                       "problems_per_gpu": hi - lo, "gather_bytes": total * 200, "kernel": solver.kernel_info(hi - lo)},
+            "unsolved": int(t[2]), "ipm_iters_mean": float(t[3]) / total}
 
 
 def _fp64_peak(index):
@@ -390,88 +531,114 @@ def _fp64_peak(index):
 
 
 def extras(solver, preset, dev):
-    """Config-3 throughput regime (65,536 random problems) and single-problem latency (p50 over 500 B=1 launches)."""
+    """Rank 0 only: config 4 (horizon sweep, nc = 8), single-problem latency (one random problem; the configs[0] replay cold and
+    warm; the drop-in MPC.update() with host arrays), and the next-row adaptors."""
     import torch
-    from g1_locomotion_b200 import inputs
+    from g1_locomotion_b200 import inputs, BatchedMPC, MPC, presets as _presets
     out = {}
-    ins = list(inputs.random_batch(preset, 65536, seed=7, device=dev))
-    for _ in range(2):
-        _, _, info = solver.update_batch(*ins, x_current=ins[0], want_resid=False)
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(3):
-        solver.update_batch(*ins, x_current=ins[0], want_resid=False)
-    e1.record(); torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / 3
-    out["config3_65536_random"] = {"problems_per_s": 65536 / (ms * 1e-3), "ms_per_launch": ms, "unsolved": int((info["status"] != 0).sum()),
-                                   "ipm_iters_mean": float(info["iters"].double().mean())}
-    # config 4: horizon sweep with four corner contacts per foot (SURVEY 8d: B = 4,096 / 1,024 / 256, seed 11)
-    from g1_locomotion_b200 import BatchedMPC, presets as _presets
+    # config 4: horizon sweep with four corner contacts per foot -- SURVEY 8d's batch (B = 4,096 / 1,024 / 256, seed 11) and a
+    # machine-filling one (8 problems per SM-resident slot would not fit memory at N = 40: 16,384 / 8,192 / 4,096)
     sweep = {}
-    for n_h, b_h in ((10, 4096), (20, 1024), (40, 256)):
+    for n_h, b_h, b_fill in ((10, 4096, 16384), (20, 1024, 8192), (40, 256, 4096)):
         pr = _presets.get_preset("cpp_node", horizon=n_h, num_contacts=8)
         sv = BatchedMPC(pr, device=dev.index)
-        ins_h = list(inputs.random_batch(pr, b_h, seed=11, device=dev))
-        for _ in range(2):
-            _, _, info_h = sv.update_batch(*ins_h, x_current=ins_h[0], want_resid=False)
-        torch.cuda.synchronize()
-        h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        h0.record()
-        for _ in range(3):
-            sv.update_batch(*ins_h, x_current=ins_h[0], want_resid=False)
-        h1.record(); torch.cuda.synchronize()
-        ms_h = h0.elapsed_time(h1) / 3
-        sweep["N%d_nc8_B%d" % (n_h, b_h)] = {"problems_per_s": b_h / (ms_h * 1e-3), "ms_per_launch": ms_h, "unsolved": int((info_h["status"] != 0).sum()),
-                                            "ipm_iters_mean": float(info_h["iters"].double().mean()), "kernel": sv.kernel_info(b_h)}
+        for tag, bb in (("B%d" % b_h, b_h), ("fill_B%d" % b_fill, b_fill)):
+            ins_h = list(inputs.random_batch(pr, bb, seed=11, device=dev))
+            for _ in range(2):
+                _, _, info_h = sv.update_batch(*ins_h, x_current=ins_h[0], want_resid=False)
+            torch.cuda.synchronize()
+            h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            h0.record()
+            for _ in range(3):
+                sv.update_batch(*ins_h, x_current=ins_h[0], want_resid=False)
+            h1.record(); torch.cuda.synchronize()
+            ms_h = h0.elapsed_time(h1) / 3
+            st = torch.bincount(info_h["status"], minlength=5).tolist()
+            sweep["N%d_nc8_%s" % (n_h, tag)] = {"problems_per_s": bb / (ms_h * 1e-3), "ms_per_launch": ms_h, "status_counts": st,
+                                                "ipm_iters_mean": float(info_h["iters"].double().mean()), "kernel": sv.kernel_info(bb)}
+            del ins_h
         sv.close()
     out["config4_horizon_sweep"] = sweep
+
+    def timed_call(fn, spin):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if spin:
+            torch.cuda._sleep(300000)       # host ahead of the device: the event pair brackets the kernel alone
+        w0 = time.perf_counter()
+        a.record(); r = fn(); b.record(); b.synchronize()
+        return a.elapsed_time(b) * 1e3, (time.perf_counter() - w0) * 1e6, r
+
+    pct = lambda v, q: float(np.percentile(v, q))
+    # one fixed random problem (as in round 1)
+    ins = list(inputs.random_batch(preset, 8, seed=7, device=dev))
     one = [t[:1].contiguous() for t in ins]
-    lat = []
-    for i in range(520):
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record(); solver.update_batch(*one, x_current=one[0], want_resid=False); b.record(); b.synchronize()
+    lat, dlat = [], []
+    for i in range(320):
+        d, _, _ = timed_call(lambda: solver.solve_one(*one, x_current=one[0]), True)
+        e, _, r = timed_call(lambda: solver.solve_one(*one, x_current=one[0]), False)
         if i >= 20:
-            lat.append(a.elapsed_time(b) * 1e3)
-    # the same launch with the host kept ahead of the device (a 150 us spin kernel is queued first), so that the event pair
-    # brackets the kernel alone and not the ~25 us of Python/ctypes between the first event and the launch
-    dlat = []
-    for i in range(220):
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda._sleep(300000)
-        a.record(); _, _, info1 = solver.update_batch(*one, x_current=one[0], want_resid=False); b.record(); b.synchronize()
-        if i >= 20:
-            dlat.append(a.elapsed_time(b) * 1e3)
-    out["single_solve_us"] = {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)), "launches": len(lat),
-                              "timing": "CUDA events around one B=1 call of BatchedMPC.update_batch (host call overhead inside)",
-                              "device_p50": float(np.percentile(dlat, 50)), "device_p99": float(np.percentile(dlat, 99)),
-                              "device_timing": "same, launch queued behind a spin kernel: the kernel alone", "ipm_iters": int(info1["iters"][0])}
+            dlat.append(d); lat.append(e)
+    out["single_solve_us"] = {"p50": pct(lat, 50), "p99": pct(lat, 99), "device_p50": pct(dlat, 50), "device_p99": pct(dlat, 99), "launches": len(lat),
+                              "ipm_iters": int(r[2]["it"][0]),
+                              "timing": "device_*: CUDA events, launch queued behind a spin kernel (the kernel alone); p50/p99: events around the bare "
+                                        "BatchedMPC.solve_one call (Python + launch overhead inside)"}
+    # configs[0]: the closed-loop replay of SURVEY 8d (tests/golden/config1_replay.npz, written by oracle/gen_config1_replay.py):
+    # 200 consecutive ticks, one B = 1 call per tick as the node makes them (mpc_to_wbid_node.cpp:494)
+    z = np.load(os.path.join(ROOT, "tests", "golden", "config1_replay.npz"))
+    ticks = [torch.as_tensor(z[k], dtype=torch.float64, device=dev) for k in ("x0", "x_ref", "contact", "c_horizon", "p_com")]
+    T = ticks[0].shape[0]
+    ustar = torch.as_tensor(z["u_star"], dtype=torch.float64, device=dev)
+    for mode in ("cold", "warm"):
+        rk, rh, rw, rit, err = [], [], [], [], 0.0
+        prev = torch.zeros(1, preset["horizon"], 12, dtype=torch.float64, device=dev)
+        for rep in range(4):
+            for t in range(T):
+                tick = [a[t:t + 1] for a in ticks]
+                uw = prev if (mode == "warm" and t > 0) else None
+                call = lambda: solver.solve_one(*tick, x_current=tick[0], u_warm=uw, warm_shift=1)
+                keep = prev.clone()
+                d, _, r = timed_call(call, True)
+                if rep == 3:
+                    err = max(err, float((r[0][0] - ustar[t]).abs().max()))
+                prev.copy_(keep)            # the second, bare call starts from the same previous solution
+                e, w, r = timed_call(call, False)
+                prev.copy_(r[0])
+                if rep > 0:
+                    rk.append(d); rh.append(e); rw.append(w); rit.append(int(r[2]["it"][0]))
+        out["single_solve_walking_replay_us" + ("" if mode == "cold" else "_warm")] = {
+            "workload": "configs[0]: 200 consecutive ticks of the straight-line walking demo closed on the oracle's solution (SURVEY 8d generator, "
+                        "seed 20251104), one problem per call, 3 timed passes after one warm-up pass" +
+                        ("" if mode == "cold" else "; every tick after the first starts from the previous tick's solution shifted by one stage "
+                                                   "(g1mpc_solve_batch_warm) -- the warm start the reference asks its solver for and never gets"),
+            "device_p50": pct(rk, 50), "device_p99": pct(rk, 99), "device_min": float(np.min(rk)), "p50": pct(rh, 50), "p99": pct(rh, 99),
+            "wall_p50": pct(rw, 50), "wall_p99": pct(rw, 99), "solves": len(rk), "max_force_error_vs_exact_minimiser_N": err,
+            "ipm_iters": iters_stats(np.array(rit)),
+            "timing": "device_*: CUDA events, launch queued behind a spin kernel (kernel alone); p50/p99: CUDA events around the bare "
+                      "BatchedMPC.solve_one call; wall_*: host clock from the call to the end of the event synchronize (launch and sync included)"}
+    # the kept API itself: MPC.update() of the drop-in class, numpy arrays in, numpy arrays out (H2D, kernel, D2H inside)
+    m = MPC.cpp_node(device=dev.index)
+    m.init_matrices()
+    hz = {k: z[k] for k in ("x0", "x_ref", "contact", "c_horizon", "p_com")}
+    upd = {}
+    for mode in ("cold", "warm"):
+        m.warm_start = mode == "warm"
+        w = []
+        for rep in range(3):
+            for t in range(T):
+                m.x0 = hz["x0"][t].reshape(13, 1)
+                m.x_ref_hor = hz["x_ref"][t]
+                w0 = time.perf_counter()
+                m.update(hz["contact"][t], hz["c_horizon"][t], hz["p_com"][t], x_current=hz["x0"][t], one_rollout=False)
+                w1 = time.perf_counter()
+                if rep > 0:
+                    w.append((w1 - w0) * 1e6)
+        upd[mode] = {"p50": pct(w, 50), "p99": pct(w, 99), "calls": len(w)}
+    m.warm_start = False
+    out["mpc_update_host_us"] = {"api": "g1_locomotion_b200.MPC.update(contact, c_horizon, p_com_horizon, x_current) -- the reference's Python "
+                                        "signature (mpc.py:360), host arrays in and out, wall clock around the call, configs[0] replay",
+                                 "p50": upd["cold"]["p50"], "p99": upd["cold"]["p99"], "calls": upd["cold"]["calls"],
+                                 "warm_start_attribute": upd["warm"]}
     out["next_rows"] = next_rows(solver, preset, dev)
-    # config 1 (BASELINE.json configs[0]): the states of the straight-line walking demo, one B=1 call per control tick as
-    # the node makes them (mpc_to_wbid_node.cpp:494); each tick timed once behind the spin kernel (kernel alone) and once bare
-    ticks = [torch.as_tensor(a, dtype=torch.float64, device=dev) for a in inputs.walking_replay(preset, n_ticks=200)]
-    rk, rh, rw, rit = [], [], [], []
-    for rep in range(6):
-        for t in range(ticks[0].shape[0]):
-            tick = [a[t:t + 1] for a in ticks]
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            torch.cuda._sleep(300000)
-            a.record(); _, _, info_t = solver.update_batch(*tick, x_current=tick[0], want_resid=False); b.record(); b.synchronize()
-            c, d = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            w0 = time.perf_counter()
-            c.record(); solver.update_batch(*tick, x_current=tick[0], want_resid=False); d.record(); d.synchronize()
-            w1 = time.perf_counter()
-            if rep > 0:
-                rk.append(a.elapsed_time(b) * 1e3); rh.append(c.elapsed_time(d) * 1e3); rw.append((w1 - w0) * 1e6)
-                rit.append(int(info_t["iters"][0]))
-    out["single_solve_walking_replay_us"] = {
-        "workload": "configs[0]: 200 consecutive ticks of the straight-line walking demo, one problem per call, 5 timed passes after one warm-up pass",
-        "device_p50": float(np.percentile(rk, 50)), "device_p99": float(np.percentile(rk, 99)), "device_min": float(np.min(rk)),
-        "p50": float(np.percentile(rh, 50)), "p99": float(np.percentile(rh, 99)), "solves": len(rk),
-        "wall_p50": float(np.percentile(rw, 50)), "wall_p99": float(np.percentile(rw, 99)),
-        "timing": "device_*: CUDA events, launch queued behind a spin kernel (kernel alone); p50/p99: CUDA events around the bare "
-                  "Python call; wall_*: host clock from the call to the end of the event synchronize (launch and sync included)",
-        "ipm_iters_p50": float(np.percentile(rit, 50)), "ipm_iters_max": int(np.max(rit)), "ipm_iters_mean": float(np.mean(rit))}
     return out
 
 
@@ -537,25 +704,49 @@ def next_rows(solver, preset, dev):
     out["closed_loop"] = {"walkers": Bw, "ticks": T, "ms_per_call": ms, "walker_ticks_per_s": Bw * T / (ms * 1e-3),
                           "launches_per_tick": 3, "unsolved_walkers": int((res["status_any"] != 0).sum()),
                           "status_any_values": torch.unique(res["status_any"]).tolist(), "total_ticks_simulated": 6 * T,
+                          "ipm_iters_mean_per_tick": float(res["iters_sum"].double().mean()) / T,
                           "note": "walk_inputs -> solve (x_current = x0) -> advance per tick, no host round trip; state advances across calls"}
+    # the same fleet with warm start across ticks (every tick after the first starts from the previous solution shifted by one stage)
+    x0, cur, t, _ = fleet(Bw, spread=8)
+    xr, xo = torch.zeros(Bw, N, 13, **f64), torch.zeros(Bw, N, 13, **f64)
+    ms, res = timed(lambda: solver.closed_loop(x0, cur, t, T, x_ref=xr, x_opt=xo, record=False, warm_start=True), reps=3)
+    out["closed_loop_warm"] = {"walkers": Bw, "ticks": T, "ms_per_call": ms, "walker_ticks_per_s": Bw * T / (ms * 1e-3),
+                               "unsolved_walkers": int((res["status_any"] != 0).sum()),
+                               "ipm_iters_mean_per_tick": float(res["iters_sum"].double().mean()) / T}
+    # main.py's SRBD-only loop (planner -> mapping -> solve -> x0 <- x_opt[2]) on the device, cold and warm
+    pl = torch.tensor([[1000.0, 0.25, 0.1, 0.2, 100.0]], **f64).repeat(Bw, 1).contiguous()
+    pl[:, 1] += 0.05 * (torch.arange(Bw, device=dev) % 5)
+    pl[:, 0] = 0.2 * (torch.arange(Bw, device=dev) % 3)
+    for tag, warm in (("main_loop", False), ("main_loop_warm", True)):
+        ms, res = timed(lambda: solver.main_loop(pl, T, total_duration=T * preset["dt"], warm_start=warm, record=False), reps=2)
+        out[tag] = {"walkers": Bw, "ticks": T, "ms_per_call": ms, "walker_ticks_per_s": Bw * T / (ms * 1e-3), "launches_per_tick": 5,
+                    "status_any_values": torch.unique(res["status_any"]).tolist(),
+                    "ipm_iters_mean_per_tick": float(res["iters_sum"].double().mean()) / T}
+    out["main_loop"]["note"] = ("g1mpc_main_loop_batch: main.py:200-326 as coded (x0 <- x_opt[2], rollout from x_opt[1], reference schedule of "
+                                "testing_double_support); consecutive solutions differ by 100-250 N there, so the warm start falls back to cold")
+    B2 = 65536
+    plB = pl[:1].repeat(B2, 1).contiguous()
+    tB = torch.rand(B2, generator=gen, **f64) * 20.0
+    ms, _ = timed(lambda: solver.plan_gait(plB, tB))
+    by = 8 * 6 + 8 * 16 * N
+    out["plan_gait"] = {"problems": B2, "ms_per_launch": ms, "problems_per_s": B2 / (ms * 1e-3), "bytes_per_problem": by,
+                        "hbm": {"achieved": B2 * by / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "frac": B2 * by / (ms * 1e-3) / 1e9 / peak}}
     return out
 
 
 def cpu_baseline(preset, host_batch):
+    """The port on this box's host cores over the SAME 1,024 problems (bounded: passes until 3 s have been spent)."""
     from oracle import oracle
     oracle.build_lib()
     cores = host_threads()
-    sample = [a[:256] for a in host_batch]
-    cpu_reference_pass(preset, [a[:32] for a in host_batch], cores)
-    t1 = cpu_reference_pass(preset, [a[:32] for a in host_batch], 1) / 32
+    small = [a[:64] for a in host_batch]
+    cpu_reference_pass(preset, small, cores)
+    t1 = cpu_reference_pass(preset, small, 1) / 64
     reps, t_all = 0, 0.0
-    while t_all < 2.0 and reps < 50:
-        t_all += cpu_reference_pass(preset, sample, cores)
+    while t_all < 3.0 and reps < 50:
+        t_all += cpu_reference_pass(preset, list(host_batch), cores)
         reps += 1
-    return {"value": 256 * reps / t_all, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"first 256 of the 1,024 walking problems x {reps} passes, OpenMP over {cores} host threads "
-                      f"(oracle/srbd_mpc_oracle.c: mpc.cpp build as coded + OSQP-style ADMM, eps 1e-3, cold start)",
-            "single_core_ms_per_solve": 1e3 * t1}
+    return cpu_baseline_record(BATCH * reps / t_all, cores, f"all {BATCH} walking problems x {reps} passes, OpenMP over {cores} host threads", t1)
 
 
 if __name__ == "__main__":
