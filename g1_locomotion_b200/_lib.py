@@ -14,7 +14,7 @@ EXPORTS = ["g1mpc_create", "g1mpc_destroy", "g1mpc_solve_batch", "g1mpc_solve_ba
            "g1mpc_update_host", "g1mpc_update_host_begin", "g1mpc_update_host_end", "g1mpc_set_host_warm_start", "g1mpc_layout_info",
            "g1mpc_walk_inputs_batch", "g1mpc_wbid_refs_batch", "g1mpc_closed_loop_batch", "g1mpc_closed_loop_batch_ex", "g1mpc_plan_gait_batch",
            "g1mpc_main_loop_batch", "g1mpc_kernel_info", "g1mpc_fp64_peak_tflops", "g1mpc_last_error", "g1mpc_abi_version"]
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 
 class G1mpcParams(C.Structure):
@@ -23,7 +23,8 @@ class G1mpcParams(C.Structure):
                 ("fz_max", C.c_double), ("dt", C.c_double), ("mass", C.c_double), ("gravity", C.c_double),
                 ("inertia_body", C.c_double * 9), ("q_weights", C.c_double * 13), ("r_weight", C.c_double),
                 ("cost_scale", C.c_double), ("gap_tol", C.c_double), ("max_iter", C.c_int32), ("layout", C.c_int32),
-                ("dual_tol", C.c_double), ("warm_margin", C.c_double), ("warm_mu0", C.c_double)]
+                ("dual_tol", C.c_double), ("warm_margin", C.c_double), ("warm_mu0", C.c_double),
+                ("workspace", C.c_int32), ("reserved", C.c_int32)]
 
 
 def build(force=False, extra=""):

@@ -43,6 +43,7 @@ struct BatchPtrs {
     int one_rollout;
     const double *u_warm;       // [B,N,3nc] a previous solution to start from, or null (cold start)
     int warm_shift;             // stages the horizon has moved since that solution (closed loop: 1)
+    double *workspace;          // global-workspace variant of the kernel: one slot of WLay::oEnd doubles per resident warp
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -335,34 +336,44 @@ __global__ void fp64_peak_kernel(double *out, int iters)
 // shape-independent signature (the kernels take their layout object by value, so their own signatures differ).
 typedef void (*launch_fn)(unsigned grid, unsigned block, size_t smem, cudaStream_t st, const DevParams &, const BatchPtrs &, long long B,
                           const v2::DLay &);
-template <class LAY, int HL>
+template <class LAY, int HL, bool WSG>
 void launch_static(unsigned grid, unsigned block, size_t smem, cudaStream_t st, const DevParams &P, const BatchPtrs &io, long long B,
                    const v2::DLay &)
 {
-    v2::srbd_mpc_solve_warp_kernel<LAY, HL><<<grid, block, smem, st>>>(P, io, B, LAY());
+    v2::srbd_mpc_solve_warp_kernel<LAY, HL, WSG><<<grid, block, smem, st>>>(P, io, B, LAY());
 }
-// any other shape: the same kernel source with the layout in registers (g1mpc_create checks that it fits shared memory)
+// any other shape: the same kernel source with the layout in registers
+template <bool WSG>
 void launch_dynamic(unsigned grid, unsigned block, size_t smem, cudaStream_t st, const DevParams &P, const BatchPtrs &io, long long B,
                     const v2::DLay &L)
 {
-    v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32><<<grid, block, smem, st>>>(P, io, B, L);
+    v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, WSG><<<grid, block, smem, st>>>(P, io, B, L);
 }
 struct KernelEntry {
     int N, NC;
-    const void *fn; launch_fn launch; size_t smem;      // smem = bytes per problem
-    const void *fn2; launch_fn launch2;                 // two problems per warp (or null)
+    const void *fn; launch_fn launch; size_t smem;      // workspace in shared memory; smem = bytes per problem
+    const void *fn2; launch_fn launch2;                 // ... two problems per warp (or null)
+    const void *fng; launch_fn launchg;                 // workspace in global memory, persistent grid (or null)
 };
 // the two-problems-per-warp layout is compiled for the shapes whose stages fit the 16 lanes of a half-warp in one round
 template <int N, int NC>
 constexpr bool two_per_warp() { return N <= 16 && NC == 4 && 2 * v2::WLay<N, NC>::bytes <= 227 * 1024; }
+// the global-workspace variant is compiled for the shapes of which fewer than four fit the shared memory of an SM
+template <int N, int NC>
+constexpr bool global_ws() { return 4 * v2::WLay<N, NC>::bytes > 227 * 1024; }
 template <int N, int NC>
 KernelEntry make_entry()
 {
     using LAY = v2::WLay<N, NC>;
-    KernelEntry e{N, NC, (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 32>, launch_static<LAY, 32>, LAY::bytes, nullptr, nullptr};
+    KernelEntry e{N, NC, (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 32, false>, launch_static<LAY, 32, false>, LAY::bytes,
+                  nullptr, nullptr, nullptr, nullptr};
     if constexpr (two_per_warp<N, NC>()) {
-        e.fn2 = (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 16>;
-        e.launch2 = launch_static<LAY, 16>;
+        e.fn2 = (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 16, false>;
+        e.launch2 = launch_static<LAY, 16, false>;
+    }
+    if constexpr (global_ws<N, NC>()) {
+        e.fng = (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 32, true>;
+        e.launchg = launch_static<LAY, 32, true>;
     }
     return e;
 }
@@ -385,6 +396,11 @@ struct g1mpc_handle {
     const KernelEntry *kernel;
     KernelEntry dyn_entry;                 // used when no compiled shape matches: run-time layout, one problem per warp
     v2::DLay dlay;
+    // global-workspace variant (long horizons): workspace of ws_warps slots, launches serialised on it by ws_event
+    bool use_global = false;
+    double *d_ws = nullptr;
+    int ws_warps = 0, ws_ctas_per_sm = 0;
+    cudaEvent_t ws_event = nullptr;
     int warps_per_block = 1;
     int ctas_per_sm = 0;
     // two problems per warp pay off once a scheduler would otherwise hold two warps: above 4 problems per SM
@@ -447,20 +463,25 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
     CUDA_TRY(cudaSetDevice(device));
     int max_smem = 0;
     CUDA_TRY(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
-    if (dl.bytes > (size_t)max_smem) {
+    if (p->workspace < 0 || p->workspace > 2) { g_last_error = "workspace must be 0 (auto), 1 (shared) or 2 (global)"; return G1MPC_ERR_INVALID_ARGUMENT; }
+    const bool fits_smem = dl.bytes <= (size_t)max_smem;
+    if (!fits_smem && p->workspace == 1) {
         g_last_error = "shape exceeds shared memory: (horizon, num_contacts) = (" + std::to_string(p->horizon) + ", " + std::to_string(p->num_contacts) +
                        ") needs " + std::to_string(dl.bytes) + " B per problem, the device allows " + std::to_string(max_smem) +
-                       " B per CTA (roughly horizon <= 80 at 4 contacts, <= 58 at 8, <= 51 at 10)";
+                       " B per CTA; use workspace = 0 or 2 (global-memory workspace)";
         return G1MPC_ERR_UNSUPPORTED_SHAPE;
     }
     g1mpc_handle *h = new g1mpc_handle();
     h->params = *p; h->device = device; h->dlay = dl;
     if (!ke) {
         // no compile-time instantiation for this shape: the run-time-layout instantiation of the same kernel
-        h->dyn_entry = KernelEntry{p->horizon, p->num_contacts, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32>, launch_dynamic,
-                                   dl.bytes, nullptr, nullptr};
+        h->dyn_entry = KernelEntry{p->horizon, p->num_contacts, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, false>, launch_dynamic<false>,
+                                   dl.bytes, nullptr, nullptr, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, true>, launch_dynamic<true>};
         ke = &h->dyn_entry;
     }
+    // workspace in global memory: forced, needed (does not fit shared memory), or -- auto -- where fewer than four problems fit an SM
+    h->use_global = ke->fng && (p->workspace == 2 || !fits_smem || (p->workspace == 0 && 4 * dl.bytes > (size_t)max_smem));
+    if (p->workspace == 2 && !ke->fng) { g_last_error = "no global-workspace kernel compiled for this shape"; delete h; return G1MPC_ERR_UNSUPPORTED_SHAPE; }
     h->kernel = ke;
     if (!(h->params.gap_tol > 0)) h->params.gap_tol = 1e-10;
     if (h->params.max_iter <= 0) h->params.max_iter = 40;
@@ -476,10 +497,24 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
     d.dual_tol = h->params.dual_tol; d.warm_margin = h->params.warm_margin; d.warm_mu0 = h->params.warm_mu0;
     memcpy(d.Ib, p->inertia_body, sizeof d.Ib);
     memcpy(d.q, p->q_weights, sizeof d.q);
-    cudaError_t e = cudaFuncSetAttribute(ke->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ke->smem * h->warps_per_block));
-    if (e != cudaSuccess) { g_last_error = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
+    cudaError_t e = cudaSuccess;
+    if (fits_smem) {
+        e = cudaFuncSetAttribute(ke->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ke->smem * h->warps_per_block));
+        if (e != cudaSuccess) { g_last_error = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
+    }
+    if (h->use_global) {
+        int sms = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        cudaFuncSetAttribute(ke->fng, cudaFuncAttributePreferredSharedMemoryCarveout, 0);       // all of the on-chip SRAM as L1
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->ws_ctas_per_sm, ke->fng, kWarpThreads, 0);
+        if (h->ws_ctas_per_sm < 1) h->ws_ctas_per_sm = 1;
+        h->ws_warps = sms * h->ws_ctas_per_sm;
+        e = cudaMalloc((void **)&h->d_ws, (size_t)h->ws_warps * dl.bytes);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ws_event, cudaEventDisableTiming);
+        if (e != cudaSuccess) { g_last_error = std::string("global workspace: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
+    }
     cudaFuncSetAttribute((const void *)srbd_mpc_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->ctas_per_sm, ke->fn, kWarpThreads * h->warps_per_block, ke->smem * h->warps_per_block);
+    if (fits_smem) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->ctas_per_sm, ke->fn, kWarpThreads * h->warps_per_block, ke->smem * h->warps_per_block);
     if (ke->fn2) {
         e = cudaFuncSetAttribute(ke->fn2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * ke->smem * h->warps_per_block));
         if (e != cudaSuccess) { g_last_error = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
@@ -514,15 +549,17 @@ void g1mpc_destroy(g1mpc_handle *h)
         if (S.d_stage) cudaFree(S.d_stage);
     }
     if (h->d_loop) cudaFree(h->d_loop);
+    if (h->d_ws) cudaFree(h->d_ws);
+    if (h->ws_event) cudaEventDestroy(h->ws_event);
     delete h;
 }
 
 int g1mpc_kernel_info(const g1mpc_handle *h, int32_t *smem_bytes, int32_t *threads, int32_t *ctas_per_sm)
 {
     if (!h) return G1MPC_ERR_INVALID_ARGUMENT;
-    if (smem_bytes) *smem_bytes = (int32_t)(h->kernel->smem * h->warps_per_block);
+    if (smem_bytes) *smem_bytes = h->use_global ? 0 : (int32_t)(h->kernel->smem * h->warps_per_block);
     if (threads) *threads = kWarpThreads * h->warps_per_block;
-    if (ctas_per_sm) *ctas_per_sm = h->ctas_per_sm;
+    if (ctas_per_sm) *ctas_per_sm = h->use_global ? h->ws_ctas_per_sm : h->ctas_per_sm;
     return G1MPC_OK;
 }
 
@@ -540,7 +577,17 @@ static int solve_batch_impl(g1mpc_handle *h, int64_t B, int64_t load, const doub
     if (B > 0x7fffffffLL) { g_last_error = "batch too large for one launch"; return G1MPC_ERR_INVALID_ARGUMENT; }
     CUDA_TRY(cudaSetDevice(h->device));
     if (warm_shift < 0) { g_last_error = "warm_shift must be >= 0"; return G1MPC_ERR_INVALID_ARGUMENT; }
-    BatchPtrs io{x0, x_ref, contact, c_horizon, p_com, x_current, u_opt, x_opt, resid, y_opt, status, iters, one_rollout, u_warm, warm_shift};
+    BatchPtrs io{x0, x_ref, contact, c_horizon, p_com, x_current, u_opt, x_opt, resid, y_opt, status, iters, one_rollout, u_warm, warm_shift, h->d_ws};
+    if (h->use_global) {
+        // persistent grid over the handle's workspace; launches on different streams take turns on it
+        cudaStream_t st = (cudaStream_t)stream;
+        CUDA_TRY(cudaStreamWaitEvent(st, h->ws_event, 0));
+        const long long want = B < h->ws_warps ? B : h->ws_warps;
+        h->kernel->launchg((unsigned)want, kWarpThreads, 0, st, h->dev, io, (long long)B, h->dlay);
+        CUDA_TRY(cudaGetLastError());
+        CUDA_TRY(cudaEventRecord(h->ws_event, st));
+        return G1MPC_OK;
+    }
     const int wpb = h->warps_per_block;
     const bool two = h->kernel->fn2 && (h->force_ppw == 2 || (h->force_ppw != 1 && load > h->two_above));
     if (two)
@@ -628,6 +675,12 @@ int g1mpc_set_host_warm_start(g1mpc_handle *h, int enable, int shift)
 int g1mpc_layout_info(const g1mpc_handle *h, int64_t B, int32_t *problems_per_warp, int32_t *smem_bytes, int32_t *ctas_per_sm)
 {
     if (!h) return G1MPC_ERR_INVALID_ARGUMENT;
+    if (h->use_global) {        // workspace in global memory: persistent grid, one problem per warp, no dynamic shared memory
+        if (problems_per_warp) *problems_per_warp = 1;
+        if (smem_bytes) *smem_bytes = 0;
+        if (ctas_per_sm) *ctas_per_sm = h->ws_ctas_per_sm;
+        return G1MPC_OK;
+    }
     const bool two = h->kernel->fn2 && (h->force_ppw == 2 || (h->force_ppw != 1 && B > h->two_above));
     const int ppw = two ? 2 : 1;
     if (problems_per_warp) *problems_per_warp = ppw;

@@ -906,18 +906,16 @@ __device__ __forceinline__ void start_point(const LAY &L, double *sm, const DevP
 // control flow stays warp-uniform (a half that has finished keeps executing with its state frozen), so every
 // __syncwarp / shuffle is reached by all 32 lanes.  Both layouts give the same bits per problem.
 // ------------------------------------------------------------------------------------------------
+// One problem (per HL lanes), `sm` = its workspace of L.oEnd doubles -- shared memory, or (long horizons) global memory that the
+// L1/L2 caches keep close: the code is the same, `__syncwarp()` orders both.
 template <class LAY, int HL>
-__global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParams P, const BatchPtrs io, long long B, const LAY L)
+__device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtrs &io, long long B, const LAY &L, long long b, double *sm,
+                                              int lane, int half)
 {
     const int N = L.N, NC = L.NC, NU = 3 * NC, NV = NU * N, NCN = NC * N;
-    constexpr int PPW = 32 / HL;
-    extern __shared__ __align__(16) double sm_all[];
 #ifdef G1MPC_PHASE_CLOCKS
     const long long ph_k0 = clock64();
 #endif
-    const int lane = threadIdx.x & (HL - 1), half = (threadIdx.x & 31) / HL, warp = threadIdx.x >> 5;
-    double *sm = sm_all + (size_t)(warp * PPW + half) * L.oEnd;
-    long long b = ((long long)blockIdx.x * (blockDim.x >> 5) + warp) * PPW + half;
     if (b - half >= B) return;                     // whole warp out of range
     const bool valid = b < B;                      // odd batch: the last half-warp repeats the last problem and writes nothing
     if (!valid) b = B - 1;
@@ -1328,6 +1326,33 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
     PH(14)                                          // epilogue: outputs + rollout
     if (io.y_opt && lane == 0 && valid) { for (int i = 0; i < 16; i++) io.y_opt[b * (5 * NCN) + i] = (double)ph_t[i]; }
 #endif
+}
+
+// ------------------------------------------------------------------------------------------------
+// The launchable kernel.  WSG = false: warp -> problem(s), workspace in dynamic shared memory (the N = 10 path: everything
+// of a problem on chip).  WSG = true: the workspace of a problem lives in GLOBAL memory (io.workspace, one slot per resident
+// warp) and the grid is persistent -- warp w takes problems w, w + W, w + 2W, ... .  For the long-horizon shapes (n = 480-960,
+// 80-160 KB per problem) shared memory held one or two warps per SM; this way the register file is the only limit
+// (8 warps per SM) and the caches carry the working set.
+// ------------------------------------------------------------------------------------------------
+template <class LAY, int HL, bool WSG>
+__global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParams P, const BatchPtrs io, long long B, const LAY L)
+{
+    constexpr int PPW = 32 / HL;
+    extern __shared__ __align__(16) double sm_all[];
+    const int lane = threadIdx.x & (HL - 1), half = (threadIdx.x & 31) / HL, warp = threadIdx.x >> 5;
+    if (!WSG) {
+        double *sm = sm_all + (size_t)(warp * PPW + half) * L.oEnd;
+        const long long b = ((long long)blockIdx.x * (blockDim.x >> 5) + warp) * PPW + half;
+        solve_problem<LAY, HL>(P, io, B, L, b, sm, lane, half);
+    } else {
+        const long long w = (long long)blockIdx.x * (blockDim.x >> 5) + warp, nW = (long long)gridDim.x * (blockDim.x >> 5);
+        double *sm = io.workspace + (size_t)(w * PPW + half) * L.oEnd;
+        for (long long b0 = w * PPW; b0 < B; b0 += nW * PPW) {
+            solve_problem<LAY, HL>(P, io, B, L, b0 + half, sm, lane, half);
+            __syncwarp();
+        }
+    }
 }
 
 } // namespace v2

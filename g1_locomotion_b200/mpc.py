@@ -18,7 +18,7 @@ from .presets import get_preset, GRAVITY, ROBOT_MASS
 NS = 13
 
 
-def _c_params(p, gap_tol=0.0, max_iter=0, layout=0, dual_tol=0.0, warm_margin=0.0, warm_mu0=0.0):
+def _c_params(p, gap_tol=0.0, max_iter=0, layout=0, dual_tol=0.0, warm_margin=0.0, warm_mu0=0.0, workspace=0):
     cp = _lib.G1mpcParams()
     cp.horizon, cp.num_contacts = int(p["horizon"]), int(p["num_contacts"])
     cp.mu, cp.fz_min, cp.fz_max, cp.dt = float(p["mu"]), float(p["fz_min"]), float(p["fz_max"]), float(p["dt"])
@@ -28,6 +28,7 @@ def _c_params(p, gap_tol=0.0, max_iter=0, layout=0, dual_tol=0.0, warm_margin=0.
     cp.r_weight, cp.cost_scale = float(p["r_weight"]), float(p["cost_scale"])
     cp.gap_tol, cp.max_iter, cp.layout = float(gap_tol), int(max_iter), int(layout)
     cp.dual_tol, cp.warm_margin, cp.warm_mu0 = float(dual_tol), float(warm_margin), float(warm_mu0)
+    cp.workspace, cp.reserved = int(workspace), 0
     return cp
 
 
@@ -35,8 +36,9 @@ class BatchedMPC:
     """Batch of independent SRBD-MPC problems sharing one parameter set, on one CUDA device."""
 
     def __init__(self, preset="cpp_node", device=None, gap_tol=0.0, max_iter=0, layout=0, dual_tol=0.0, warm_margin=0.0,
-                 warm_mu0=0.0, **overrides):
+                 warm_mu0=0.0, workspace=0, **overrides):
         """layout: 0 = lane layout chosen per launch, 1 / 2 = one / two problems per warp (bit-identical results);
+        workspace: 0 = auto, 1 = shared memory, 2 = global memory behind the caches (long horizons; bit-identical results);
         dual_tol, warm_margin, warm_mu0: see include/g1mpc_b200.h (0 = defaults)."""
         self.params = get_preset(preset, **overrides) if isinstance(preset, str) else dict(preset, **overrides)
         if not torch.cuda.is_available():
@@ -48,7 +50,7 @@ class BatchedMPC:
         self._lib = _lib.load()
         self._h = C.c_void_p()
         self._pinned_keep, self._inflight = [], {}
-        cp = _c_params(self.params, gap_tol, max_iter, layout, dual_tol, warm_margin, warm_mu0)
+        cp = _c_params(self.params, gap_tol, max_iter, layout, dual_tol, warm_margin, warm_mu0, workspace)
         self._b1 = None
         _lib.check(self._lib.g1mpc_create(C.byref(cp), self.device.index, C.byref(self._h)), "g1mpc_create")
 

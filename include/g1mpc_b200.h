@@ -31,7 +31,7 @@ extern "C" {
 #endif
 
 #define G1MPC_NUM_STATES 13
-#define G1MPC_ABI_VERSION 5
+#define G1MPC_ABI_VERSION 6
 
 typedef enum g1mpc_error {
     G1MPC_OK = 0,
@@ -71,6 +71,11 @@ typedef struct g1mpc_params {
     double warm_margin;       /* warm start: newtons a previous solution is pulled inside every constraint row
                                                                               (<=0: default 0.01 mass |g|) */
     double warm_mu0;          /* warm start: initial complementarity s*lambda (<=0: default 0.1)    */
+    int32_t workspace;        /* where a problem's working set (stage factors, per-contact state) lives during the solve:
+                                 1 = shared memory (everything on chip; needs it to fit 227 KB), 2 = global memory behind
+                                 L1/L2 with a persistent grid (any horizon), 0 = shared where at least four problems fit an SM,
+                                 else global.  Same arithmetic, same bits.                                             */
+    int32_t reserved;
 } g1mpc_params;
 
 typedef struct g1mpc_handle g1mpc_handle;
@@ -243,7 +248,8 @@ int g1mpc_closed_loop_batch_ex(g1mpc_handle *h, int64_t B, int32_t ticks, int wa
                                double *contacts_now, double *sim_time, double *x_ref, double *x_opt, double *u_opt,
                                double *traj_x, double *traj_u, int32_t *status_any, int32_t *iters_sum, void *stream);
 
-/* Dynamic shared memory (bytes) and threads per CTA of the solve kernel for this handle's shape. */
+/* Dynamic shared memory (bytes; 0 = the workspace is in global memory) and threads per CTA of the solve kernel for this
+ * handle's shape, and how many such CTAs an SM holds. */
 int g1mpc_kernel_info(const g1mpc_handle *h, int32_t *smem_bytes, int32_t *threads, int32_t *ctas_per_sm);
 
 /*

@@ -25,12 +25,12 @@ def test_library_exports_every_declared_symbol():
     assert set(syms) == set(_lib.EXPORTS), (syms, _lib.EXPORTS)
     for s in syms:
         assert getattr(lib, s) is not None
-    assert lib.g1mpc_abi_version() == 5 == _lib.ABI_VERSION
+    assert lib.g1mpc_abi_version() == 6 == _lib.ABI_VERSION
 
 
 def test_params_struct_matches_header_layout():
-    # 2 int32 + 6 double + 9 + 13 + 2 double + 1 double + 2 int32 + 3 double
-    assert C.sizeof(_lib.G1mpcParams) == 8 + 8 * 6 + 8 * 9 + 8 * 13 + 8 * 2 + 8 + 8 + 8 * 3
+    # 2 int32 + 6 double + 9 + 13 + 2 double + 1 double + 2 int32 + 3 double + 2 int32
+    assert C.sizeof(_lib.G1mpcParams) == 8 + 8 * 6 + 8 * 9 + 8 * 13 + 8 * 2 + 8 + 8 + 8 * 3 + 8
     assert _lib.G1mpcParams.layout.offset == 260 and _lib.G1mpcParams.dual_tol.offset == 264
     assert _lib.G1mpcParams.mu.offset == 8 and _lib.G1mpcParams.inertia_body.offset == 56
 
