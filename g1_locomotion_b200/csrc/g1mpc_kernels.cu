@@ -397,7 +397,8 @@ struct g1mpc_handle {
     KernelEntry dyn_entry;                 // used when no compiled shape matches: run-time layout, one problem per warp
     v2::DLay dlay;
     // global-workspace variant (long horizons): workspace of ws_warps slots, launches serialised on it by ws_event
-    bool use_global = false;
+    bool use_global = false, fits_smem = true;
+    long long global_above = 0;             // launches of more problems than this use the global workspace (auto mode)
     double *d_ws = nullptr;
     int ws_warps = 0, ws_ctas_per_sm = 0;
     cudaEvent_t ws_event = nullptr;
@@ -481,6 +482,7 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
     }
     // workspace in global memory: forced, needed (does not fit shared memory), or -- auto -- where fewer than four problems fit an SM
     h->use_global = ke->fng && (p->workspace == 2 || !fits_smem || (p->workspace == 0 && 4 * dl.bytes > (size_t)max_smem));
+    h->fits_smem = fits_smem;
     if (p->workspace == 2 && !ke->fng) { g_last_error = "no global-workspace kernel compiled for this shape"; delete h; return G1MPC_ERR_UNSUPPORTED_SHAPE; }
     h->kernel = ke;
     if (!(h->params.gap_tol > 0)) h->params.gap_tol = 1e-10;
@@ -515,6 +517,13 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
     }
     cudaFuncSetAttribute((const void *)srbd_mpc_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
     if (fits_smem) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->ctas_per_sm, ke->fn, kWarpThreads * h->warps_per_block, ke->smem * h->warps_per_block);
+    if (h->use_global && fits_smem && p->workspace == 0) {
+        // auto: a launch that the shared-memory kernel holds in one wave stays on chip (measured equal or a few per cent
+        // faster there, profiles/r2_c_global_workspace.txt); larger ones gain from the eight warps per SM of the global variant
+        int sms = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        h->global_above = (long long)sms * h->ctas_per_sm;
+    }
     if (ke->fn2) {
         e = cudaFuncSetAttribute(ke->fn2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * ke->smem * h->warps_per_block));
         if (e != cudaSuccess) { g_last_error = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
@@ -578,7 +587,7 @@ static int solve_batch_impl(g1mpc_handle *h, int64_t B, int64_t load, const doub
     CUDA_TRY(cudaSetDevice(h->device));
     if (warm_shift < 0) { g_last_error = "warm_shift must be >= 0"; return G1MPC_ERR_INVALID_ARGUMENT; }
     BatchPtrs io{x0, x_ref, contact, c_horizon, p_com, x_current, u_opt, x_opt, resid, y_opt, status, iters, one_rollout, u_warm, warm_shift, h->d_ws};
-    if (h->use_global) {
+    if (h->use_global && load > h->global_above) {
         // persistent grid over the handle's workspace; launches on different streams take turns on it
         cudaStream_t st = (cudaStream_t)stream;
         CUDA_TRY(cudaStreamWaitEvent(st, h->ws_event, 0));
@@ -675,7 +684,7 @@ int g1mpc_set_host_warm_start(g1mpc_handle *h, int enable, int shift)
 int g1mpc_layout_info(const g1mpc_handle *h, int64_t B, int32_t *problems_per_warp, int32_t *smem_bytes, int32_t *ctas_per_sm)
 {
     if (!h) return G1MPC_ERR_INVALID_ARGUMENT;
-    if (h->use_global) {        // workspace in global memory: persistent grid, one problem per warp, no dynamic shared memory
+    if (h->use_global && B > h->global_above) {        // workspace in global memory: persistent grid, one problem per warp, no dynamic shared memory
         if (problems_per_warp) *problems_per_warp = 1;
         if (smem_bytes) *smem_bytes = 0;
         if (ctas_per_sm) *ctas_per_sm = h->ws_ctas_per_sm;
