@@ -411,6 +411,7 @@ struct g1mpc_handle {
     int host_warm = 0, host_warm_shift = 1;     // g1mpc_set_host_warm_start
     // host-API staging: kSlots batches in flight, each cut into up to kPipe chunks with a stream of their own
     static constexpr int kPipe = 4, kSlots = G1MPC_HOST_SLOTS;
+    static constexpr int64_t kZeroCopyMax = 4;  // host-API batches up to this size run without copies (see g1mpc_update_host_begin)
     struct Off { size_t x0, xr, ct, ch, pc, xc, xo, u, res, st; };
     struct Slot {
         cudaStream_t pipe[kPipe] = {nullptr, nullptr, nullptr, nullptr};
@@ -420,6 +421,7 @@ struct g1mpc_handle {
         int nchunk = 0;
         bool pending = false, staged_out = false;
         int64_t prev_B = -1;                    // batch size of the solution still lying in d_stage (host warm start)
+        bool prev_zero_copy = false;            // ... or in h_stage (zero-copy path)
         double *u_opt = nullptr, *x_opt = nullptr, *resid = nullptr;     // caller's output buffers (unpacked in _end)
         int32_t *status = nullptr, *iters = nullptr;
     } slot[kSlots];
@@ -771,9 +773,41 @@ int g1mpc_update_host_begin(g1mpc_handle *h, int slot, int64_t B, const double *
         CUDA_TRY(cudaMalloc((void **)&S.d_stage, bytes));
         S.stage_bytes = bytes;
     }
-    S.stride = stride; S.cap = cap; S.staged_out = !direct_out;
+    // A handful of problems (the reference's own use: ONE updateMPC per control tick, mpc_to_wbid_node.cpp:494): no copy engine at
+    // all.  The kernel reads its 2.7 KB of inputs straight from the slot's page-locked block over the bus and writes its results
+    // there (pinned memory is mapped into the device's address space under unified addressing) -- two cudaMemcpyAsync calls and
+    // their DMA start-up latency (~10-15 us) less on the one path where latency is the metric.
+    const bool zero_copy = B <= g1mpc_handle::kZeroCopyMax && !h->use_global;
+    S.stride = stride; S.cap = cap; S.staged_out = !direct_out || zero_copy;
     S.u_opt = u_opt; S.x_opt = x_opt; S.resid = resid; S.status = status; S.iters = iters;
     const size_t D = sizeof(double);
+    if (zero_copy) {
+        const size_t nb = (size_t)B;
+        S.nbs[0] = nb; S.nchunk = 1;
+        double *hs = (double *)S.h_stage;
+        g1mpc_handle::Off &f = S.off[0];
+        size_t q = 0;
+        f.x0 = q; q += nb * NS;  f.xr = q; q += nb * N * NS;  f.ct = q; q += nb * N * NC;  f.ch = q; q += nb * N * NU;
+        f.pc = q; q += nb * N * 3;  f.xc = q; q += nb * NS;  f.xo = q; q += nb * N * NS;
+        f.u = q; q += nb * N * NU;  f.res = q; q += nb * 4;  f.st = q;
+        memcpy(hs + f.x0, x0, D * nb * NS);
+        memcpy(hs + f.xr, x_ref, D * nb * N * NS);
+        memcpy(hs + f.ct, contact, D * nb * N * NC);
+        memcpy(hs + f.ch, c_horizon, D * nb * N * NU);
+        memcpy(hs + f.pc, p_com, D * nb * N * 3);
+        if (x_current) memcpy(hs + f.xc, x_current, D * nb * NS);
+        if (xopt_in) memcpy(hs + f.xo, x_opt, D * nb * N * NS);
+        int32_t *hs_i = (int32_t *)(hs + f.st);
+        // (a warm start reads the previous call's u_opt where that call left it: the same place of the same block)
+        int rc = solve_batch_impl(h, (int64_t)nb, B, hs + f.x0, hs + f.xr, hs + f.ct, hs + f.ch, hs + f.pc, x_current ? hs + f.xc : nullptr,
+                                  one_rollout, hs + f.u, hs + f.xo, hs_i, hs_i + nb, hs + f.res, nullptr, S.pipe[0],
+                                  (warm && S.prev_zero_copy) ? hs + f.u : nullptr, h->host_warm_shift);
+        if (rc) return rc;
+        S.prev_zero_copy = true;
+        S.pending = true;
+        return G1MPC_OK;
+    }
+    S.prev_zero_copy = false;
     for (int c = 0; c < nchunk; c++) {
         const size_t b0 = cap * c, nb = b0 < (size_t)B ? (((size_t)B - b0) < cap ? ((size_t)B - b0) : cap) : 0;
         S.nbs[c] = nb;

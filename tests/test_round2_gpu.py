@@ -198,11 +198,46 @@ def test_runtime_shape_kernel_kkt(orc, N, nc, pname):
             assert cert["rc"] == 0 and np.abs(uh[b].ravel() - xs).max() <= 1e-3
 
 
-def test_shape_that_does_not_fit_is_refused_with_the_supported_range():
+def test_shape_beyond_shared_memory_runs_from_the_global_workspace(orc):
+    """N = 120, nc = 8 needs 480 KB per problem: refused with workspace = 1 (shared memory), solved with the default (the
+    global-memory workspace behind L1/L2, persistent grid).  Horizons this long sit on the accuracy floor of FP64 (status 4 is
+    allowed), the returned point is still primal feasible and stationary to 1e-3 relative, OSQP's own tolerance."""
+    preset = presets.get_preset("cpp_node", horizon=120, num_contacts=8)
     with pytest.raises(RuntimeError, match="exceeds shared memory"):
-        BatchedMPC(presets.get_preset("cpp_node", horizon=120, num_contacts=8), device=0)
+        BatchedMPC(preset, device=0, workspace=1)
     with pytest.raises(RuntimeError):
         BatchedMPC(presets.get_preset("cpp_node", horizon=1), device=0)
+    s = BatchedMPC(preset, device=0)
+    assert s.kernel_info(16)["smem_bytes"] == 0
+    ins = list(inputs.random_batch(preset, 16, seed=3, device="cuda"))
+    u, x, info = s.update_batch(*ins, x_current=ins[0], want_multipliers=True)
+    assert set(info["status"].tolist()) <= {0, 1, 4}
+    p = orc.params_from_dict(preset)
+    m = orc.build(p, *[t[0].cpu().numpy() for t in ins])
+    k = orc.kkt_residuals(m["H"], m["g"], m["Acon"], m["l"], m["u"], u[0].cpu().numpy().ravel(), info["y"][0].cpu().numpy())
+    assert k["primal"] <= 1e-9 and k["stationarity"] <= 1e-3 * (1 + np.abs(m["g"]).max()), k
+
+
+@pytest.mark.parametrize("N,nc,B", [(20, 8, 2048), (40, 4, 1500), (30, 4, 777)])
+def test_global_workspace_gives_the_same_bits_as_shared_memory(N, nc, B):
+    """The long-horizon kernel variant keeps a problem's working set in global memory (one slot per resident warp, persistent
+    grid, eight warps per SM instead of one or two): same code, same arithmetic, so every output must be bit-identical to the
+    shared-memory variant -- including a launch larger than the grid (each warp walks several problems)."""
+    preset = presets.get_preset("cpp_node", horizon=N, num_contacts=nc)
+    ins = list(inputs.random_batch(preset, B, seed=29, device="cuda"))
+    a = BatchedMPC(preset, device=0, workspace=1).update_batch(*ins, x_current=ins[0], want_multipliers=True)
+    sg = BatchedMPC(preset, device=0, workspace=2)
+    assert sg.kernel_info(B)["smem_bytes"] == 0
+    b = sg.update_batch(*ins, x_current=ins[0], want_multipliers=True)
+    c = sg.update_batch(*ins, x_current=ins[0], want_multipliers=True)          # and again on the used workspace
+    for r in (b, c):
+        assert torch.equal(a[0], r[0]) and torch.equal(a[1], r[1])
+        for k in ("status", "iters", "resid", "y"):
+            assert torch.equal(a[2][k], r[2][k]), k
+    # the host API's chunks (four streams) take turns on the one workspace
+    host = [t.cpu().numpy() for t in ins]
+    uh, xh, ih = sg.update_host(*host, x_current=host[0])
+    assert np.array_equal(uh, a[0].cpu().numpy()) and np.array_equal(ih["iters"], a[2]["iters"].cpu().numpy())
 
 
 # --------------------------------------------------------------------------------------------------------------------
