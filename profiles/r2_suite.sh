@@ -1,15 +1,22 @@
 #!/bin/bash
 # full GPU suite + bench (both arms) -> gpurun_out/<tag>/
 tag=${1:-suite}; out=gpurun_out/$tag; mkdir -p $out
-python -m pytest tests -m gpu -q 2>&1 | grep -E "^E  |FAILED|passed|failed|Error" | cut -c1-300 | head -80 > $out/pytest.log; cat $out/pytest.log
+( time python -m pytest tests -m gpu -q --durations=8 ) 2>&1 | grep -E "^E  |FAILED|passed|failed|Error|^real|s call" | cut -c1-300 | head -80 > $out/pytest.log; cat $out/pytest.log
 python bench.py --steps 20 --warmup 5 > $out/bench.json 2> $out/bench.err; echo "bench rc=$?"; tail -5 $out/bench.err
-python bench.py --impl reference --steps 5 --warmup 1 > $out/bench_ref.json 2>> $out/bench.err; cat $out/bench_ref.json | cut -c1-600
+python bench.py --impl reference --steps 5 --warmup 1 > $out/bench_ref.json 2>> $out/bench.err
 python - <<PY
 import json
 d = json.load(open("$out/bench.json"))
 ex = d.pop("extras", {})
-print(json.dumps({k: d[k] for k in ("value", "ms_per_step", "roofline", "solver", "cpu_baseline") if k in d})[:1800])
+print("value", d["value"], "ms", d["ms_per_step"], "frac", d["roofline"]["frac"], "cpu", d.get("cpu_baseline", {}).get("value"))
 print("e2e", d["e2e"]["value"], d["e2e"]["sync"]["value"], d["e2e"]["per_rank"])
 for k, v in ex.items():
-    print(k, json.dumps(v)[:900])
+    if k.startswith("single") or k.startswith("mpc_"):
+        print(k, {a: b for a, b in v.items() if a in ("device_p50", "p50", "wall_p50", "device_p99", "wall_p99", "warm_start_attribute")})
+    elif k == "config4_horizon_sweep":
+        for a, b in v.items(): print("  ", a, round(b["problems_per_s"]), b["status_counts"], b["kernel"])
+    elif k == "next_rows":
+        for a, b in v.items(): print("  ", a, {c: e for c, e in b.items() if c in ("problems_per_s", "walker_ticks_per_s", "ipm_iters_mean_per_tick", "status_any_values")})
+    else:
+        print(k, json.dumps(v)[:300])
 PY

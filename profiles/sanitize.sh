@@ -3,6 +3,10 @@
 # hazards: the solve kernel aliases shared-memory regions by lifetime and synchronises with __syncwarp() only), synccheck
 # (divergent barriers / shuffles: the two-problems-per-warp layout keeps control flow warp-uniform by construction).
 #   bash profiles/sanitize.sh [outdir]      -> <outdir>/sanitize_{memcheck,racecheck,synccheck}.log + summary on stdout
+# NOTE (round 2): compute-sanitizer is CLOSED on this GPU pool ("runs under it have left GPUs needing a reset"): the tool prints
+# that notice and exits 86 without running anything (gpurun_out/r2e/sanitize_memcheck.log).  The script stays for a machine
+# where the tool is available; on this pool the evidence is tests/test_round2_gpu.py::test_no_write_lands_outside_the_output_arrays
+# (guard bands), the bit-identity of the two lane layouts / the two workspaces, and run-to-run determinism.
 out=${1:-gpurun_out/sanitize}; mkdir -p $out
 cat > /tmp/sanitize_case.py <<'PY'
 import sys, numpy as np, torch
