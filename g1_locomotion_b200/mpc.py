@@ -9,6 +9,8 @@ There is no CPU path: every numeric result comes from the CUDA kernels.
 """
 import ctypes as C
 
+import contextlib
+
 import numpy as np
 import torch
 
@@ -36,9 +38,11 @@ class BatchedMPC:
     """Batch of independent SRBD-MPC problems sharing one parameter set, on one CUDA device."""
 
     def __init__(self, preset="cpp_node", device=None, gap_tol=0.0, max_iter=0, layout=0, dual_tol=0.0, warm_margin=0.0,
-                 warm_mu0=0.0, workspace=0, **overrides):
+                 warm_mu0=0.0, workspace=0, nvtx=False, **overrides):
         """layout: 0 = lane layout chosen per launch, 1 / 2 = one / two problems per warp (bit-identical results);
         workspace: 0 = auto, 1 = shared memory, 2 = global memory behind the caches (long horizons; bit-identical results);
+        nvtx: wrap every entry point in an NVTX range "g1mpc.<call>" (what the reference's chrono / ros::WallTime timers around
+        updateMPC become on a GPU timeline, mpc.cpp:382,404-412, mpc_to_wbid_node.cpp:476,496);
         dual_tol, warm_margin, warm_mu0: see include/g1mpc_b200.h (0 = defaults)."""
         self.params = get_preset(preset, **overrides) if isinstance(preset, str) else dict(preset, **overrides)
         if not torch.cuda.is_available():
@@ -50,6 +54,7 @@ class BatchedMPC:
         self._lib = _lib.load()
         self._h = C.c_void_p()
         self._pinned_keep, self._inflight = [], {}
+        self._nvtx = bool(nvtx)
         cp = _c_params(self.params, gap_tol, max_iter, layout, dual_tol, warm_margin, warm_mu0, workspace)
         self._b1 = None
         _lib.check(self._lib.g1mpc_create(C.byref(cp), self.device.index, C.byref(self._h)), "g1mpc_create")
@@ -66,6 +71,9 @@ class BatchedMPC:
             pass
 
     # -- helpers ---------------------------------------------------------------------------------
+    def _range(self, name):
+        return torch.cuda.nvtx.range("g1mpc." + name) if self._nvtx else contextlib.nullcontext()
+
     def _chk(self, t, shape, name):
         if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == torch.float64 and t.is_contiguous()):
             raise TypeError(f"{name}: expected a contiguous CUDA float64 tensor")
@@ -112,7 +120,7 @@ class BatchedMPC:
         y = torch.empty(B, 5 * nc * N, device=self.device, dtype=torch.float64) if want_multipliers else None
         pw = self._chk(u_warm, (B, N, nu), "u_warm") if u_warm is not None else None
         stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
-        with torch.cuda.device(self.device):
+        with torch.cuda.device(self.device), self._range("solve_batch"):
             rc = self._lib.g1mpc_solve_batch_warm(self._h, B, px0, pxr, pct, pch, ppc, pxc, int(one_rollout), pw, int(warm_shift),
                                                   pu, pxo, C.c_void_p(status.data_ptr()), C.c_void_p(iters.data_ptr()),
                                                   C.c_void_p(resid.data_ptr()) if want_resid else None,
@@ -138,7 +146,7 @@ class BatchedMPC:
         out = {k: torch.empty(shapes[k], device=self.device, dtype=torch.float64) for k in shapes if k in which}
         ptr = lambda k: C.c_void_p(out[k].data_ptr()) if k in out else None
         stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
-        with torch.cuda.device(self.device):
+        with torch.cuda.device(self.device), self._range("emit_qp_batch"):
             rc = self._lib.g1mpc_emit_qp_batch(self._h, B, px0, pxr, pct, pch, ppc, ptr("A"), ptr("Bd"), ptr("Aqp"),
                                                ptr("Bqp"), ptr("H"), ptr("g"), ptr("Acon"), ptr("l"), ptr("u"), stream)
         _lib.check(rc, "g1mpc_emit_qp_batch")
@@ -155,7 +163,7 @@ class BatchedMPC:
             x_opt = torch.zeros(B, N, NS, device=self.device, dtype=torch.float64)
         pxo = self._chk(x_opt, (B, N, NS), "x_opt")
         stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
-        with torch.cuda.device(self.device):
+        with torch.cuda.device(self.device), self._range("rollout_batch"):
             rc = self._lib.g1mpc_rollout_batch(self._h, B, pxr, pch, ppc, pu, pxc, int(one_rollout), pxo, stream)
         _lib.check(rc, "g1mpc_rollout_batch")
         return x_opt
@@ -270,7 +278,7 @@ class BatchedMPC:
         status_any = torch.zeros(B, device=self.device, dtype=torch.int32)
         iters_sum = torch.zeros(B, device=self.device, dtype=torch.int32)
         stream = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
-        with torch.cuda.device(self.device):
+        with torch.cuda.device(self.device), self._range("closed_loop_batch"):
             rc = self._lib.g1mpc_closed_loop_batch_ex(self._h, B, int(ticks), int(bool(warm_start)), px0, pc, pt, pxr, pxo,
                                                       C.c_void_p(u_opt.data_ptr()),
                                                       C.c_void_p(traj_x.data_ptr()) if record else None,
@@ -292,8 +300,9 @@ class BatchedMPC:
         x_opt = np.zeros((B, N, NS)) if x_opt is None else f(x_opt, (B, N, NS)).copy()
         resid = np.empty((B, 4))
         p = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
-        rc = self._lib.g1mpc_update_host(self._h, B, p(x0), p(x_ref), p(contact), p(c_horizon), p(p_com), p(xc),
-                                         int(one_rollout), p(u_opt), p(x_opt), p(status), p(iters), p(resid))
+        with self._range("update_host"):
+            rc = self._lib.g1mpc_update_host(self._h, B, p(x0), p(x_ref), p(contact), p(c_horizon), p(p_com), p(xc),
+                                             int(one_rollout), p(u_opt), p(x_opt), p(status), p(iters), p(resid))
         _lib.check(rc, "g1mpc_update_host")
         return u_opt, x_opt, dict(status=status, iters=iters, resid=resid)
 

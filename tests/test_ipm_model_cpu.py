@@ -6,6 +6,7 @@ import pytest
 
 from g1_locomotion_b200 import presets, inputs
 from ipm_model import Problem, RiccatiFactor, StageFactor, solve_ipm
+import ipm_model as im
 
 GRF_TOL = 1e-3
 
@@ -112,3 +113,29 @@ def test_illconditioned_problems_need_theta_in_the_stage_form(orc):
         u, it, gap = solve_ipm(Problem(preset, *args), linear="stage_s")        # S_k (Gamma p2) as a product
         lost += int(it == 40 or np.abs(u.ravel() - xs).max() > GRF_TOL)
     assert lost >= 1            # stalls, or ends off the minimiser (which of the two depends on the rounding)
+
+
+def test_warm_start_model_halves_the_iterations_and_the_safeguard_bounds_a_bad_start():
+    """The kernel's warm start (srbd_solve_warp.cuh: start_point + cold restart), in the numpy model: on consecutive ticks of
+    the configs[0] replay the previous minimiser shifted by one stage, pulled 0.01 m g inside every constraint row, with
+    lambda = 0.1 / s, needs about half the iterations of the cold start and reaches the same minimiser; a start that has
+    nothing to do with the problem stalls, is detected after 5 iterations (gap not halved) and costs at most those 5."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "config1_replay.npz"))
+    pr = presets.get_preset("cpp_node")
+    W = pr["mass"] * 9.80665
+    cold, warm = [], []
+    for k in range(40, 70):
+        P = im.Problem(pr, z["x0"][k], z["x_ref"][k], z["contact"][k], z["c_horizon"][k], z["p_com"][k])
+        u0, it0, _ = im.solve_ipm(P, linear="dense")
+        u1, it1, _ = im.solve_ipm(P, linear="dense", warm=dict(u=z["u_star"][k - 1].reshape(10, 4, 3), margin=0.01 * W, mu0=0.1))
+        assert np.abs(u0.reshape(10, 12) - z["u_star"][k]).max() <= 1e-3 and np.abs(u1.reshape(10, 12) - z["u_star"][k]).max() <= 1e-3
+        cold.append(it0); warm.append(it1)
+        s0 = im.warm_point(P, z["u_star"][k - 1].reshape(10, 4, 3), 0.01 * W)[1]
+        assert s0[P.stance].min() >= 0.01 * W - 1e-12              # every slack of the warm point is at least the margin
+    assert np.mean(warm) <= 0.65 * np.mean(cold), (np.mean(cold), np.mean(warm))
+    rng = np.random.default_rng(0)
+    P = im.Problem(pr, z["x0"][50], z["x_ref"][50], z["contact"][50], z["c_horizon"][50], z["p_com"][50])
+    _, it_cold, _ = im.solve_ipm(P, linear="dense")
+    u2, it2, _ = im.solve_ipm(P, linear="dense", warm=dict(u=rng.uniform(-300, 900, (10, 4, 3)), margin=0.01 * W, mu0=0.1))
+    assert np.abs(u2.reshape(10, 12) - z["u_star"][50]).max() <= 1e-3 and it2 <= it_cold + 5
