@@ -554,8 +554,19 @@ def extras(solver, preset, dev):
             h1.record(); torch.cuda.synchronize()
             ms_h = h0.elapsed_time(h1) / 3
             st = torch.bincount(info_h["status"], minlength=5).tolist()
+            ki = sv.kernel_info(bb)
             sweep["N%d_nc8_%s" % (n_h, tag)] = {"problems_per_s": bb / (ms_h * 1e-3), "ms_per_launch": ms_h, "status_counts": st,
-                                                "ipm_iters_mean": float(info_h["iters"].double().mean()), "kernel": sv.kernel_info(bb)}
+                                                "ipm_iters_mean": float(info_h["iters"].double().mean()), "kernel": ki}
+            if ki["smem_bytes"] == 0:
+                # global-workspace kernel: HBM traffic is the interesting number here (SURVEY 8d "report both") -- from the committed
+                # ncu capture of this very launch (kernel name and grid must match), against the algorithmic bytes of the API arrays
+                tr, src = ncu_traffic("WLay<%d, 8>" % n_h, "(%d,1,1)" % min(bb, 148 * ki["ctas_per_sm"]))
+                alg = algorithmic_bytes(n_h, 8) * bb
+                sweep["N%d_nc8_%s" % (n_h, tag)]["hbm"] = {
+                    "traffic": tr, "traffic_source": src, "algorithmic_bytes": alg,
+                    "achieved_GBps_on_traffic": None if tr is None else tr / (ms_h * 1e-3) / 1e9,
+                    "note": "the per-warp workspace (stage factors + per-contact state) streams through L2/HBM: traffic >> algorithmic by design "
+                            "of this variant; it buys eight resident warps per SM instead of one or two"}
             del ins_h
         sv.close()
     out["config4_horizon_sweep"] = sweep
