@@ -453,11 +453,28 @@ __device__ __forceinline__ void assemble_stage(const LAY &L, double *sm, const D
 // column of [ I | P21 | P22 ] (18 lanes), one 6x6 mat-vec and two substitutions each; then Psi = P12 S Gamma,
 // A11 = P11 - P12 S A21.
 // P11 stays in the registers of the six A21 lanes (one column each).  Returns false if a minor was not positive.
-template <class LAY, int HL>
-__device__ __forceinline__ bool factor_stages(const LAY &L, double *sm, const DevParams &P, const StageC &C, int lane PH_PARAMS)
+// Latency mode (LAT, one problem per two-warp CTA, see srbd_mpc_solve_lat_kernel): a partner warp runs the predictor's pre-pass
+// and backward sweep one stage behind this loop.  `lat` = 40 doubles of extra shared memory (the A21 exchange buffer, which
+// otherwise lives in vD where the partner writes, and dt cos, dt sin, dt) followed by the two signal words; `fcount` = how
+// many factorisations this problem has had (the signal is a monotone counter: fcount (N+1) + stages done).
+constexpr int kLatDoubles = 44;
+__device__ __forceinline__ int *lat_sig(double *lat) { return reinterpret_cast<int *>(lat + 40); }       // [0]: end-of-problem flag
+// The two warps meet on NAMED BARRIERS (bar.arrive by the producer, bar.sync by the consumer, 64 threads each): barrier 1 + k
+// = "stage k of the running factorisation is stored", barrier 15 = "the partner has finished its sweep" -- hence N <= 14.  A
+// barrier id is only re-armed after the main warp has waited on barrier 15, so a lagging partner can never see two arrivals on
+// one id.  (Polling a shared-memory word instead -- volatile, or ld.acquire with a back-off -- slowed the MAIN warp's own
+// shared-memory chains 1.7-2.5x: measured 524 / 356 us against 213 us for the single warp.  The barrier costs nothing while waiting.)
+__device__ __forceinline__ void bar_arrive64(int id) { asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory"); }
+__device__ __forceinline__ void bar_sync64(int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
+constexpr int kLatDoneBar = 15;
+
+template <class LAY, int HL, bool LAT = false>
+__device__ __forceinline__ bool factor_stages(const LAY &L, double *sm, const DevParams &P, const StageC &C, int lane PH_PARAMS,
+                                              double *lat = nullptr, int fcount = 0)
 {
     const int N = L.N;
-    double *Ex = sm + L.oEx, *PiX = sm + L.oVb;             // (vB | vC are dead between the assembly and the solve)
+    (void)fcount;
+    double *Ex = LAT ? lat : sm + L.oEx;
     // HL = 32: lanes >= 18 shadow group 2 and never store.  HL = 16 (two problems per warp): groups 0 and 1 as before,
     // lanes 12..15 are columns 0..3 of group 2, and lanes 4, 5 (group 0) take over the P22 update of columns 4, 5.
     const int grp = lane < 18 ? lane / 6 : 2, cb = lane % 6;
@@ -568,6 +585,9 @@ __device__ __forceinline__ bool factor_stages(const LAY &L, double *sm, const De
         }
         double *Sn = St - L.STG;                              // slot of stage k-1: receives P12 | P22 of P_k
         __syncwarp();
+        if (LAT) {      // G2 | Psi | Gamma of stage k and P12 | P22 of P_{k+1} are in place: the partner warp may run stage k
+            bar_arrive64(1 + k);
+        }
         // Theta_k (lower triangle, column cb from group 0) replaces S_k, which nobody reads after this point: the solves
         // form b_k = Gamma' t - Theta p2 with it
         if (lane < 6) {
@@ -609,31 +629,42 @@ __device__ __forceinline__ bool factor_stages(const LAY &L, double *sm, const De
 // per-contact step needs: W_c^T y = zeta~_tau x r + zeta~_F).  The two sequential sweeps run on 12 lanes (one state
 // component each) and exchange the 12-vector through shared memory once per stage (42 cycles measured for
 // STS + sync + LDS against 27 for one dependent shuffle, but 8 instructions instead of 16-28 SHFL).
-template <class LAY, int HL>
+// pre-pass of one stage (one lane): gt = Gamma^T t, c1 = P12 gt, c2 = Phi^T c1 + P22 gt
+template <class LAY>
+__device__ __forceinline__ void solve_pre_stage(const LAY &L, double *sm, const PhiC &F, int k)
+{
+    double *vA = sm + L.oVa, *vB = sm + L.oVb, *vC = sm + L.oVc;
+    const double *St = sm + L.oRic + k * L.STG;
+    double t[6], gt[6], c1[6], c2[6], pc1[6], row[6], p22[22];
+    ld6(vA + 6 * k, t);
+#pragma unroll
+    for (int j = 0; j < 6; j++) { ld6(St + L.sGam + 6 * j, row); gt[j] = dot6(row, t); }      // (columns of Gamma are stored)
+#pragma unroll
+    for (int i = 0; i < 6; i++) { ld6(St + L.sP12 + 6 * i, row); c1[i] = dot6(row, gt); }
+    ld22(St + L.sP22, p22);
+    symmv6(p22, gt, c2);
+    phiT6(F, c1, pc1);
+#pragma unroll
+    for (int i = 0; i < 6; i++) c2[i] += pc1[i];
+    st6(vA + 6 * k, gt); st6(vB + 6 * k, c1); st6(vC + 6 * k, c2);
+}
+
+// LATP: the pre-pass and the backward sweep of THIS solve have been done by the partner warp (latency mode, predictor only)
+template <class LAY, int HL, bool LATP = false>
 __device__ __forceinline__ void solve_stages(const LAY &L, double *sm, const StageC &C, int lane PH_PARAMS)
 {
     const int N = L.N;
     double *vA = sm + L.oVa, *vB = sm + L.oVb, *vC = sm + L.oVc, *vD = sm + L.oVd, *pbuf = sm + L.oPb;
     const PhiC F = C.F;
-    // ---- pre (lane = stage): gt = Gamma^T t, c1 = P12 gt, c2 = Phi^T c1 + P22 gt
-    for (int k = lane; k < N; k += HL) {
-        const double *St = sm + L.oRic + k * L.STG;
-        double t[6], gt[6], c1[6], c2[6], pc1[6], row[6], p22[22];
-        ld6(vA + 6 * k, t);
-#pragma unroll
-        for (int j = 0; j < 6; j++) { ld6(St + L.sGam + 6 * j, row); gt[j] = dot6(row, t); }      // (columns of Gamma are stored)
-#pragma unroll
-        for (int i = 0; i < 6; i++) { ld6(St + L.sP12 + 6 * i, row); c1[i] = dot6(row, gt); }
-        ld22(St + L.sP22, p22);
-        symmv6(p22, gt, c2);
-        phiT6(F, c1, pc1);
-#pragma unroll
-        for (int i = 0; i < 6; i++) c2[i] += pc1[i];
-        st6(vA + 6 * k, gt); st6(vB + 6 * k, c1); st6(vC + 6 * k, c2);
+    // ---- pre (lane = stage)
+    if (!LATP) {
+        for (int k = lane; k < N; k += HL) solve_pre_stage<LAY>(L, sm, F, k);
     }
     PHS(8)
     const int r6 = lane % 6;
-    if (lane < 6) { vD[6 * (N - 1) + r6] = 0.0; pbuf[6 * (N & 1) + r6] = 0.0; }     // zero terminal co-state
+    if (!LATP) {
+        if (lane < 6) { vD[6 * (N - 1) + r6] = 0.0; pbuf[6 * (N & 1) + r6] = 0.0; }     // zero terminal co-state
+    }
     __syncwarp();
     // Phi column r6 (for Phi^T x) and Phi row r6 (for Phi x)
     const double ga = r6 == 0 ? F.dc : (r6 == 1 ? -F.dsn : F.dt), gb = r6 == 0 ? F.dsn : (r6 == 1 ? F.dc : 0.0);
@@ -644,7 +675,7 @@ __device__ __forceinline__ void solve_stages(const LAY &L, double *sm, const Sta
     //      Branch-free: one predicated store per step; the loads that do not depend on the recurrence (matrix row,
     //      constant term) are issued one step ahead, before the barrier.
     const bool lo6 = lane < 6;
-    {
+    if (!LATP) {
         const double *rowp = sm + L.oRic + (lo6 ? L.sPsi : L.sG2) + r6;          // row r6 of column storage: + k STG + 6 j
         const double *cp = (lo6 ? vB : vC) + r6;                                        // + 6 k
         double *dstp = lo6 ? pbuf + r6 : vD + r6 - 6;                                   // p1 -> pbuf[6 (k&1)], p2 -> vD[6 (k-1)]
@@ -744,6 +775,53 @@ __device__ __forceinline__ void solve_stages(const LAY &L, double *sm, const Sta
     PHS(12)
 }
 
+
+// Latency mode, partner warp: for every factorisation of the problem, pre-pass + backward-sweep step of stage k as soon as the
+// main warp has signalled that stage (one stage behind the factor loop: ~600 cycles of work against ~1,900 per factor stage).
+// Same functions, same operations as solve_stages<.., false>: the results are bit-identical.  Returns when the main warp
+// signals the end of the problem (a negative value).
+template <class LAY>
+__device__ __forceinline__ void lat_helper(const LAY &L, double *sm, double *lat, int lane)
+{
+    const int N = L.N;
+    int *sig = lat_sig(lat);
+    double *vB = sm + L.oVb, *vC = sm + L.oVc, *vD = sm + L.oVd, *pbuf = sm + L.oPb;
+    const int r6 = lane % 6;
+    const bool lo6 = lane < 6, wr = lane < 12;
+    const int ja = r6 < 2 ? 0 : r6, jb = r6 < 2 ? 1 : r6;
+    const double *rowp = sm + L.oRic + (lo6 ? L.sPsi : L.sG2) + r6;
+    const double *cp = (lo6 ? vB : vC) + r6;
+    double *dstp = lo6 ? pbuf + r6 : vD + r6 - 6;
+    for (;;) {
+        PhiC F = {0.0, 0.0, 0.0};
+        double ga = 0.0, gb = 0.0, pown = 0.0;
+        for (int k = N - 1; k >= 0; k--) {
+            bar_sync64(1 + k);                          // stage k is stored (or, at k = N-1, the problem is over)
+            if (k == N - 1) {
+                if (sig[0] != 0) return;
+                F.dc = lat[36]; F.dsn = lat[37]; F.dt = lat[38];
+                ga = r6 == 0 ? F.dc : (r6 == 1 ? -F.dsn : F.dt); gb = r6 == 0 ? F.dsn : (r6 == 1 ? F.dc : 0.0);
+                if (lane < 6) { vD[6 * (N - 1) + r6] = 0.0; pbuf[6 * (N & 1) + r6] = 0.0; }     // zero terminal co-state
+            }
+            if (lane == 0) solve_pre_stage<LAY>(L, sm, F, k);
+            __syncwarp();
+            double row[6], p2[6];
+#pragma unroll
+            for (int j = 0; j < 6; j++) row[j] = rowp[k * L.STG + 6 * j];
+            const double cadd = cp[6 * k];
+            ld6(vD + 6 * k, p2);
+            const double *pp = pbuf + 6 * ((k + 1) & 1);
+            const double pa = pp[ja], pb = pp[jb];
+            double acc = dot6(row, p2);
+            double b_lo = pown + cadd, b_hi = fma(ga, pa, fma(gb, pb, cadd));
+            asm volatile("" : "+d"(acc), "+d"(b_lo), "+d"(b_hi));
+            pown = lo6 ? b_lo - acc : b_hi + acc;
+            if (wr && (lo6 || k > 0)) dstp[lo6 ? 6 * (k & 1) : 6 * k] = pown;
+            __syncwarp();
+        }
+        bar_arrive64(kLatDoneBar);
+    }
+}
 
 // grad f(u) = s r u + W^T (M W u + h): per-stage wrench, state rollout, adjoint sweep (all O(N)), then the
 // per-stage co-state wrench in physical units (Bm^T v) is left in V for the per-contact pass.
@@ -908,9 +986,9 @@ __device__ __forceinline__ void start_point(const LAY &L, double *sm, const DevP
 // ------------------------------------------------------------------------------------------------
 // One problem (per HL lanes), `sm` = its workspace of L.oEnd doubles -- shared memory, or (long horizons) global memory that the
 // L1/L2 caches keep close: the code is the same, `__syncwarp()` orders both.
-template <class LAY, int HL>
+template <class LAY, int HL, bool LAT = false>
 __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtrs &io, long long B, const LAY &L, long long b, double *sm,
-                                              int lane, int half)
+                                              int lane, int half, double *lat = nullptr)
 {
     const int N = L.N, NC = L.NC, NU = 3 * NC, NV = NU * N, NCN = NC * N;
 #ifdef G1MPC_PHASE_CLOCKS
@@ -935,6 +1013,8 @@ __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtr
     for (int i = 0; i < 9; i++) C.J[i] = lin.Iwi[i] * P.dt;
     C.bv = P.bv;
     C.F.dc = P.dt * lin.c; C.F.dsn = P.dt * lin.s; C.F.dt = P.dt;
+    if (LAT) { if (lane == 0) { lat[36] = C.F.dc; lat[37] = C.F.dsn; lat[38] = C.F.dt; } }      // (published with the first stage signal)
+    int fcount = 0;
     const double cz = lin.c, sz = lin.s;
     int bad_bounds = 0, n_stance = 0;
     for (int c0 = 0; c0 < NCN; c0 += HL) {
@@ -1116,13 +1196,18 @@ __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtr
         assemble_stage<LAY, HL, true>(L, sm, P, C, lane);
         __syncwarp();
         PH(2)
-        if (!factor_stages<LAY, HL>(L, sm, P, C, lane PH_ARGS) && !frozen) { status = G1MPC_NUMERICAL; frozen = true; }
+        const bool fac_ok = factor_stages<LAY, HL, LAT>(L, sm, P, C, lane PH_ARGS, lat, fcount);
+        if (LAT) {      // the partner warp is at most one stage behind: wait for its last step (also when the factorisation failed)
+            fcount++;
+            bar_sync64(kLatDoneBar);
+        }
+        if (!fac_ok && !frozen) { status = G1MPC_NUMERICAL; frozen = true; }
         if (HL == 32 ? frozen : __all_sync(kFullMask, frozen)) break;
         n_act = frozen ? 0 : n_stance;
         PH(3)
         // (4) predictor.  With x = ds/s:  dl = -lam (1 + x), and the largest feasible step is
         //     1 / max_i max(-x_i, 1 + x_i)  -- no division per constraint.
-        solve_stages<LAY, HL>(L, sm, C, lane PH_ARGS);
+        solve_stages<LAY, HL, LAT>(L, sm, C, lane PH_ARGS);
         PH(4)
         const double *zt = sm + L.oVa;
         double p_rmax = 0.0, p_sum2[2] = {0.0, 0.0};
@@ -1352,6 +1437,34 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
             solve_problem<LAY, HL>(P, io, B, L, b0 + half, sm, lane, half);
             __syncwarp();
         }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Latency mode: ONE problem per CTA of two warps (small batches -- the reference's own use is one updateMPC per control tick,
+// mpc_to_wbid_node.cpp:494).  Warp 0 runs solve_problem as above; warp 1 runs the predictor's pre-pass and backward sweep one
+// stage behind warp 0's factor loop (lat_helper), so that ~3 k of the ~36 k cycles of an interior-point iteration leave the
+// critical path; ~1.4 k come back as the wait for the partner's last stage and as contention in the factor loop.  The
+// corrector's right-hand side depends on the predictor's result, so only this one of the four sweeps of an iteration can hide.
+// Measured (profiles/r2_f_latency_mode.txt): 213.0 -> 203.7 us p50 over the configs[0] replay, 342.9 -> 328.6 us at 148
+// problems, bit-identical to the one-warp kernel.  The warps meet on named barriers (see factor_stages).
+// ------------------------------------------------------------------------------------------------
+template <class LAY>
+__global__ void __launch_bounds__(64) srbd_mpc_solve_lat_kernel(const DevParams P, const BatchPtrs io, long long B, const LAY L)
+{
+    extern __shared__ __align__(16) double sm_all[];
+    double *sm = sm_all, *lat = sm_all + L.oEnd;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) lat_sig(lat)[0] = 0;
+    __syncthreads();
+    if (warp == 0) {
+        solve_problem<LAY, 32, true>(P, io, B, L, (long long)blockIdx.x, sm, lane, 0, lat);
+        // release the partner, which waits for a stage that will not come
+        if (lane == 0) lat_sig(lat)[0] = 1;
+        __syncwarp();
+        bar_arrive64(1 + (L.N - 1));
+    } else {
+        lat_helper<LAY>(L, sm, lat, lane);
     }
 }
 

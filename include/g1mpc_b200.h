@@ -65,8 +65,10 @@ typedef struct g1mpc_params {
     double cost_scale;        /* 2: H=2(B'QB+R) (mpc.cpp:361,375); 1: Python (mpc.py:301,317) */
     double gap_tol;           /* stop when mean complementarity s'lambda/m <= gap_tol  (<=0: default 1e-10) */
     int32_t max_iter;         /* interior-point iteration limit               (<=0: default 40)     */
-    int32_t layout;           /* lane layout of the solve kernel: 0 = chosen per launch (g1mpc_layout_info), 1 = one problem
-                                 per warp, 2 = two (where compiled).  Results do not depend on it (bit-identical).       */
+    int32_t layout;           /* lane layout of the solve kernel: 0 = chosen per launch (g1mpc_layout_info: latency mode -- two
+                                 warps per problem -- up to 2 problems per SM, one problem per warp up to 4 per SM, two per
+                                 warp above), 1 = one problem per warp, 2 = two per warp, 3 = latency mode (the last two where
+                                 compiled: horizon <= 16 resp. <= 14, 4 contacts).  Results do not depend on it (bit-identical). */
     double dual_tol;          /* see G1MPC_SOLVED                             (<=0: default 1e-6)   */
     double warm_margin;       /* warm start: newtons a previous solution is pulled inside every constraint row
                                                                               (<=0: default 0.01 mass |g|) */

@@ -6,7 +6,7 @@ import torch
 from g1_locomotion_b200 import BatchedMPC, presets, inputs
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 1
 preset = presets.get_preset("cpp_node")
-s = BatchedMPC(preset, device=0)
+s = BatchedMPC(preset, device=0, layout=int(sys.argv[2]) if len(sys.argv) > 2 else 0)
 ins = [torch.as_tensor(a, dtype=torch.float64).cuda() for a in inputs.walking_batch(preset, max(B, 8))]
 ins = [t[:B].contiguous() for t in ins]
 for _ in range(3):

@@ -163,6 +163,48 @@ def test_closed_loop_warm_start_halves_the_iterations():
 
 
 # --------------------------------------------------------------------------------------------------------------------
+# latency mode: two warps per problem for small batches
+# --------------------------------------------------------------------------------------------------------------------
+def test_latency_mode_kernel_gives_the_same_bits_as_the_one_warp_kernel():
+    """Up to two problems per SM the library runs ONE problem per two-warp CTA: the partner warp does the predictor's pre-pass
+    and backward sweep one stage behind the factor loop (srbd_mpc_solve_lat_kernel).  Same functions, same operations: every
+    output is bit-identical to the one-warp kernel (layout 1) -- cold, warm (cold restarts included), one-step rollout, no
+    x_current, problems that never reach a factorisation (all contacts in swing; NaN input), B = 1 and launches beyond 2 per SM."""
+    preset = presets.get_preset("cpp_node")
+    one, lat, auto = BatchedMPC(preset, device=0, layout=1), BatchedMPC(preset, device=0, layout=3), BatchedMPC(preset, device=0)
+    assert auto.kernel_info(1)["smem_bytes"] == lat.kernel_info(1)["smem_bytes"] == one.kernel_info(1)["smem_bytes"] + 352
+    assert auto.kernel_info(297)["smem_bytes"] == one.kernel_info(297)["smem_bytes"]          # above 2 per SM: the one-warp kernel
+    z = _replay()
+    rep = [_dev(z[k]) for k in ("x0", "x_ref", "contact", "c_horizon", "p_com")]
+    rnd = list(inputs.random_batch(preset, 700, seed=41, device="cuda"))
+    odd = [t.clone() for t in rnd]
+    odd[2][3] = 0.0                                     # all swing: no factorisation at all
+    odd[0][5, 4] = float("nan")                         # contained failure
+    def same(a, b):
+        ok = torch.equal(a[0].nan_to_num(nan=-1.0), b[0].nan_to_num(nan=-1.0)) and torch.equal(a[1].nan_to_num(nan=-1.0), b[1].nan_to_num(nan=-1.0))
+        return ok and all(torch.equal(a[2][k].nan_to_num(nan=-1.0) if a[2][k].is_floating_point() else a[2][k],
+                                      b[2][k].nan_to_num(nan=-1.0) if b[2][k].is_floating_point() else b[2][k]) for k in ("status", "iters", "resid", "y"))
+    for ins in (rep, rnd, odd, [t[:1].contiguous() for t in rnd]):
+        for kw in (dict(x_current=ins[0]), dict(x_current=ins[0], one_rollout=True), dict()):
+            xp = torch.full((ins[0].shape[0], 10, 13), 2.0, dtype=torch.float64, device="cuda")
+            a = one.update_batch(*ins, x_opt=xp.clone(), want_multipliers=True, **kw)
+            for _ in range(2):
+                assert same(a, lat.update_batch(*ins, x_opt=xp.clone(), want_multipliers=True, **kw))
+    assert set(a[2]["status"].tolist()) == {0}
+    st_odd = one.update_batch(*odd, x_current=odd[0])[2]["status"]
+    assert int(st_odd[5]) == 3 and int(st_odd[3]) == 0
+    # warm start (good starts, and junk that triggers the cold restart inside the kernel)
+    u = one.update_batch(*rep, x_current=rep[0])[0]
+    for w in (torch.cat([u[:1], u[:-1]]).contiguous(), torch.full_like(u, 700.0)):
+        a = one.update_batch(*rep, x_current=rep[0], u_warm=w, want_multipliers=True)
+        assert same(a, lat.update_batch(*rep, x_current=rep[0], u_warm=w, want_multipliers=True))
+    # the host API with one problem (zero-copy path) lands on the latency kernel too
+    host = [t[7:8].cpu().numpy() for t in rep]
+    uh, xh, ih = auto.update_host(*host, x_current=host[0])
+    assert np.array_equal(uh[0], u[7].cpu().numpy())
+
+
+# --------------------------------------------------------------------------------------------------------------------
 # run-time shapes: any (N, nc) that fits shared memory
 # --------------------------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("N,nc,pname", [(12, 4, "cpp_node"), (30, 4, "cpp_node"), (7, 8, "cpp_node"), (3, 4, "python_default"),
