@@ -349,18 +349,19 @@ void launch_dynamic(unsigned grid, unsigned block, size_t smem, cudaStream_t st,
 {
     v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, WSG><<<grid, block, smem, st>>>(P, io, B, L);
 }
-template <class LAY>
+template <class LAY, int HL>
 void launch_lat(unsigned grid, unsigned block, size_t smem, cudaStream_t st, const DevParams &P, const BatchPtrs &io, long long B,
                 const v2::DLay &)
 {
-    v2::srbd_mpc_solve_lat_kernel<LAY><<<grid, block, smem, st>>>(P, io, B, LAY());
+    v2::srbd_mpc_solve_lat_kernel<LAY, HL><<<grid, block, smem, st>>>(P, io, B, LAY());
 }
 struct KernelEntry {
     int N, NC;
     const void *fn; launch_fn launch; size_t smem;      // workspace in shared memory; smem = bytes per problem
     const void *fn2; launch_fn launch2;                 // ... two problems per warp (or null)
     const void *fng; launch_fn launchg;                 // workspace in global memory, persistent grid (or null)
-    const void *fnl; launch_fn launchl;                 // latency mode: one problem per two-warp CTA (or null)
+    const void *fnl; launch_fn launchl;                 // partner-warp mode: one problem per two-warp CTA (or null)
+    const void *fnl2; launch_fn launchl2;               // ... two problems per two-warp CTA (or null)
 };
 // the two-problems-per-warp layout is compiled for the shapes whose stages fit the 16 lanes of a half-warp in one round
 template <int N, int NC>
@@ -373,14 +374,16 @@ KernelEntry make_entry()
 {
     using LAY = v2::WLay<N, NC>;
     KernelEntry e{N, NC, (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 32, false>, launch_static<LAY, 32, false>, LAY::bytes,
-                  nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+                  nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     if constexpr (two_per_warp<N, NC>()) {
         e.fn2 = (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 16, false>;
         e.launch2 = launch_static<LAY, 16, false>;
     }
     if constexpr (two_per_warp<N, NC>() && N <= 14) {                   // (one named barrier per stage: N <= 14)
-        e.fnl = (const void *)v2::srbd_mpc_solve_lat_kernel<LAY>;       // the short-horizon shapes: where latency is the metric
-        e.launchl = launch_lat<LAY>;
+        e.fnl = (const void *)v2::srbd_mpc_solve_lat_kernel<LAY, 32>;   // the short-horizon shapes: where latency is the metric
+        e.launchl = launch_lat<LAY, 32>;
+        e.fnl2 = (const void *)v2::srbd_mpc_solve_lat_kernel<LAY, 16>;
+        e.launchl2 = launch_lat<LAY, 16>;
     }
     if constexpr (global_ws<N, NC>()) {
         e.fng = (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 32, true>;
@@ -418,6 +421,7 @@ struct g1mpc_handle {
     // two problems per warp pay off once a scheduler would otherwise hold two warps: above 4 problems per SM
     // (G1MPC_PPW=1|2 in the environment forces one layout -- tests compare the two bit for bit)
     long long two_above = 0, lat_upto = 0;      // launches of at most lat_upto problems run the latency-mode kernel
+    int lat2 = 0;                               // partner-warp kernel with two problems per warp: 0 off, 1 in place of the plain one, 2 always
     int force_ppw = 0;
     int host_warm = 0, host_warm_shift = 1;     // g1mpc_set_host_warm_start
     // host-API staging: kSlots batches in flight, each cut into up to kPipe chunks with a stream of their own
@@ -466,7 +470,7 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
         g_last_error = "q_weights[12] (gravity state) must be 0: the state is constant and is not part of the tracked cost";
         return G1MPC_ERR_INVALID_ARGUMENT;
     }
-    if (p->layout < 0 || p->layout > 3) { g_last_error = "layout must be 0 (auto), 1, 2 or 3"; return G1MPC_ERR_INVALID_ARGUMENT; }
+    if (p->layout < 0 || p->layout > 4) { g_last_error = "layout must be 0 (auto), 1, 2, 3 or 4"; return G1MPC_ERR_INVALID_ARGUMENT; }
     const KernelEntry *ke = nullptr;
     for (const auto &k : kKernels) if (k.N == p->horizon && k.NC == p->num_contacts) ke = &k;
     const v2::DLay dl(p->horizon, p->num_contacts);
@@ -491,7 +495,7 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
         // no compile-time instantiation for this shape: the run-time-layout instantiation of the same kernel
         h->dyn_entry = KernelEntry{p->horizon, p->num_contacts, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, false>, launch_dynamic<false>,
                                    dl.bytes, nullptr, nullptr, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, true>, launch_dynamic<true>,
-                                   nullptr, nullptr};
+                                   nullptr, nullptr, nullptr, nullptr};
         ke = &h->dyn_entry;
     }
     // workspace in global memory: forced, needed (does not fit shared memory), or -- auto -- where fewer than four problems fit an SM
@@ -551,10 +555,15 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
         if (ke->fn2) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas2, ke->fn2, kWarpThreads * h->warps_per_block, 2 * ke->smem * h->warps_per_block);
         if (2 * ctas2 < h->ctas_per_sm) h->two_above = 0x7fffffffffffLL;
         h->force_ppw = (p->layout == 1 || p->layout == 2) ? p->layout : 0;
+        if (ke->fnl2 && p->layout == 4) {       // (never chosen automatically: measured slower than the plain two-per-warp layout)
+            e = cudaFuncSetAttribute(ke->fnl2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * ke->smem));
+            if (e != cudaSuccess) { g_last_error = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
+            h->lat2 = 2;
+        }
         // latency mode: two warps per problem while every warp still has a scheduler to itself (2 problems per SM); layout = 3 forces
         // it for any batch, layout = 1 / 2 switch it off
         if (ke->fnl && (p->layout == 0 || p->layout == 3)) {
-            e = cudaFuncSetAttribute(ke->fnl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ke->smem + sizeof(double) * v2::kLatDoubles));
+            e = cudaFuncSetAttribute(ke->fnl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ke->smem);
             if (e != cudaSuccess) { g_last_error = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
             h->lat_upto = p->layout == 3 ? 0x7fffffffLL : 2LL * sms;
         }
@@ -619,13 +628,19 @@ static int solve_batch_impl(g1mpc_handle *h, int64_t B, int64_t load, const doub
         return G1MPC_OK;
     }
     if (h->kernel->launchl && load <= h->lat_upto) {
-        h->kernel->launchl((unsigned)B, 2 * kWarpThreads, h->kernel->smem + sizeof(double) * v2::kLatDoubles, (cudaStream_t)stream, h->dev, io,
+        h->kernel->launchl((unsigned)B, 2 * kWarpThreads, h->kernel->smem, (cudaStream_t)stream, h->dev, io,
                            (long long)B, h->dlay);
         CUDA_TRY(cudaGetLastError());
         return G1MPC_OK;
     }
     const int wpb = h->warps_per_block;
     const bool two = h->kernel->fn2 && (h->force_ppw == 2 || (h->force_ppw != 1 && load > h->two_above));
+    if (h->kernel->launchl2 && (h->lat2 == 2 || (h->lat2 == 1 && two))) {
+        h->kernel->launchl2((unsigned)((B + 1) / 2), 2 * kWarpThreads, 2 * h->kernel->smem, (cudaStream_t)stream,
+                            h->dev, io, (long long)B, h->dlay);
+        CUDA_TRY(cudaGetLastError());
+        return G1MPC_OK;
+    }
     if (two)
         h->kernel->launch2((unsigned)((B + 2 * wpb - 1) / (2 * wpb)), kWarpThreads * wpb, 2 * h->kernel->smem * wpb, (cudaStream_t)stream, h->dev, io, (long long)B, h->dlay);
     else
@@ -719,10 +734,11 @@ int g1mpc_layout_info(const g1mpc_handle *h, int64_t B, int32_t *problems_per_wa
     }
     if (h->kernel->launchl && B <= h->lat_upto) {       // latency mode: one problem per CTA of two warps
         if (problems_per_warp) *problems_per_warp = 1;
-        if (smem_bytes) *smem_bytes = (int32_t)(h->kernel->smem + sizeof(double) * v2::kLatDoubles);
+        if (problems_per_warp) *problems_per_warp = -1;    // (marks the partner-warp mode: one problem per TWO warps)
+        if (smem_bytes) *smem_bytes = (int32_t)h->kernel->smem;
         if (ctas_per_sm) {
             int n = 0;
-            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, h->kernel->fnl, 2 * kWarpThreads, h->kernel->smem + sizeof(double) * v2::kLatDoubles);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, h->kernel->fnl, 2 * kWarpThreads, h->kernel->smem);
             *ctas_per_sm = n;
         }
         return G1MPC_OK;

@@ -455,10 +455,9 @@ __device__ __forceinline__ void assemble_stage(const LAY &L, double *sm, const D
 // P11 stays in the registers of the six A21 lanes (one column each).  Returns false if a minor was not positive.
 // Latency mode (LAT, one problem per two-warp CTA, see srbd_mpc_solve_lat_kernel): a partner warp runs the predictor's pre-pass
 // and backward sweep one stage behind this loop.  `lat` = 40 doubles of extra shared memory (the A21 exchange buffer, which
-// otherwise lives in vD where the partner writes, and dt cos, dt sin, dt) followed by the two signal words; `fcount` = how
-// many factorisations this problem has had (the signal is a monotone counter: fcount (N+1) + stages done).
-constexpr int kLatDoubles = 44;
-__device__ __forceinline__ int *lat_sig(double *lat) { return reinterpret_cast<int *>(lat + 40); }       // [0]: end-of-problem flag
+// otherwise lives in vD where the partner writes, and dt cos, dt sin, dt); `fcount` = how
+// many factorisations this problem has had.  `lat` costs no shared memory of its own: it is the `prod` region of the layout
+// (6 NCN >= 39 doubles), which is dead from the assembly of S_k to the predictor's per-contact pass and which the partner never touches.
 // The two warps meet on NAMED BARRIERS (bar.arrive by the producer, bar.sync by the consumer, 64 threads each): barrier 1 + k
 // = "stage k of the running factorisation is stored", barrier 15 = "the partner has finished its sweep" -- hence N <= 14.  A
 // barrier id is only re-armed after the main warp has waited on barrier 15, so a lagging partner can never see two arrivals on
@@ -781,10 +780,9 @@ __device__ __forceinline__ void solve_stages(const LAY &L, double *sm, const Sta
 // Same functions, same operations as solve_stages<.., false>: the results are bit-identical.  Returns when the main warp
 // signals the end of the problem (a negative value).
 template <class LAY>
-__device__ __forceinline__ void lat_helper(const LAY &L, double *sm, double *lat, int lane)
+__device__ __forceinline__ void lat_helper(const LAY &L, double *sm, double *lat, const int *sig, int lane)
 {
     const int N = L.N;
-    int *sig = lat_sig(lat);
     double *vB = sm + L.oVb, *vC = sm + L.oVc, *vD = sm + L.oVd, *pbuf = sm + L.oPb;
     const int r6 = lane % 6;
     const bool lo6 = lane < 6, wr = lane < 12;
@@ -1013,7 +1011,6 @@ __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtr
     for (int i = 0; i < 9; i++) C.J[i] = lin.Iwi[i] * P.dt;
     C.bv = P.bv;
     C.F.dc = P.dt * lin.c; C.F.dsn = P.dt * lin.s; C.F.dt = P.dt;
-    if (LAT) { if (lane == 0) { lat[36] = C.F.dc; lat[37] = C.F.dsn; lat[38] = C.F.dt; } }      // (published with the first stage signal)
     int fcount = 0;
     const double cz = lin.c, sz = lin.s;
     int bad_bounds = 0, n_stance = 0;
@@ -1196,6 +1193,7 @@ __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtr
         assemble_stage<LAY, HL, true>(L, sm, P, C, lane);
         __syncwarp();
         PH(2)
+        if (LAT) { if (lane == 0) { lat[36] = C.F.dc; lat[37] = C.F.dsn; lat[38] = C.F.dt; } }      // (published with the first stage barrier)
         const bool fac_ok = factor_stages<LAY, HL, LAT>(L, sm, P, C, lane PH_ARGS, lat, fcount);
         if (LAT) {      // the partner warp is at most one stage behind: wait for its last step (also when the factorisation failed)
             fcount++;
@@ -1449,22 +1447,35 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
 // Measured (profiles/r2_f_latency_mode.txt): 213.0 -> 203.7 us p50 over the configs[0] replay, 342.9 -> 328.6 us at 148
 // problems, bit-identical to the one-warp kernel.  The warps meet on named barriers (see factor_stages).
 // ------------------------------------------------------------------------------------------------
-template <class LAY>
+template <class LAY, int HL>
 __global__ void __launch_bounds__(64) srbd_mpc_solve_lat_kernel(const DevParams P, const BatchPtrs io, long long B, const LAY L)
 {
+    // HL = 32: one problem per CTA.  HL = 16: two (one per half-warp of BOTH warps: the partner warp sweeps the two problems of
+    // its main warp in the same instructions).
+    constexpr int PPW = 32 / HL;
     extern __shared__ __align__(16) double sm_all[];
-    double *sm = sm_all, *lat = sm_all + L.oEnd;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) lat_sig(lat)[0] = 0;
+    __shared__ int cta_done;                            // end-of-CTA flag for the partner warp
+    __shared__ unsigned slot[2];                        // hardware warp slots of the two warps
+    const int lane = threadIdx.x & (HL - 1), half = (threadIdx.x & 31) / HL, warp = threadIdx.x >> 5;
+    double *sm = sm_all + (size_t)half * L.oEnd, *lat = sm + L.oProd;
+    if (threadIdx.x == 0) cta_done = 0;
+    if ((threadIdx.x & 31) == 0) { unsigned w; asm volatile("mov.u32 %0, %%warpid;" : "=r"(w)); slot[warp] = w; }
     __syncthreads();
-    if (warp == 0) {
-        solve_problem<LAY, 32, true>(P, io, B, L, (long long)blockIdx.x, sm, lane, 0, lat);
+    // Which of the two warps is the main one: a scheduler serves the warp slots congruent to it mod 4, and the two warps of a
+    // CTA sit on neighbouring slots.  If warp 0 were always the main warp, the four CTAs of an SM would put their main warps on
+    // schedulers 0, 2, 0, 2 and leave 1 and 3 to partners that mostly wait (measured: 2.91 against 3.59 M/s at 65,536 problems).
+    // Alternating by slot group (slots 0-3, 4-7, ...) puts one main warp on every scheduler.  Both warps evaluate the same rule.
+    const unsigned s_lo = slot[0] < slot[1] ? slot[0] : slot[1];
+    const int main_warp = (((s_lo >> 2) & 1) == 0) == (slot[0] <= slot[1]) ? 0 : 1;
+    if (warp == main_warp) {
+        solve_problem<LAY, HL, true>(P, io, B, L, (long long)blockIdx.x * PPW + half, sm, lane, half, lat);
         // release the partner, which waits for a stage that will not come
-        if (lane == 0) lat_sig(lat)[0] = 1;
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) cta_done = 1;
         __syncwarp();
         bar_arrive64(1 + (L.N - 1));
     } else {
-        lat_helper<LAY>(L, sm, lat, lane);
+        lat_helper<LAY>(L, sm, lat, &cta_done, lane);
     }
 }
 

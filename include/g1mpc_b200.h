@@ -67,7 +67,8 @@ typedef struct g1mpc_params {
     int32_t max_iter;         /* interior-point iteration limit               (<=0: default 40)     */
     int32_t layout;           /* lane layout of the solve kernel: 0 = chosen per launch (g1mpc_layout_info: latency mode -- two
                                  warps per problem -- up to 2 problems per SM, one problem per warp up to 4 per SM, two per
-                                 warp above), 1 = one problem per warp, 2 = two per warp, 3 = latency mode (the last two where
+                                 warp above), 1 = one problem per warp, 2 = two per warp, 3 = latency mode, 4 = latency mode with
+                                 two problems per main warp (measured slower than 2, never chosen automatically; 2-4 where
                                  compiled: horizon <= 16 resp. <= 14, 4 contacts).  Results do not depend on it (bit-identical). */
     double dual_tol;          /* see G1MPC_SOLVED                             (<=0: default 1e-6)   */
     double warm_margin;       /* warm start: newtons a previous solution is pulled inside every constraint row
@@ -255,10 +256,11 @@ int g1mpc_closed_loop_batch_ex(g1mpc_handle *h, int64_t B, int32_t ticks, int wa
 int g1mpc_kernel_info(const g1mpc_handle *h, int32_t *smem_bytes, int32_t *threads, int32_t *ctas_per_sm);
 
 /*
- * Lane layout a launch of B problems uses: one problem per warp, or -- for the shapes it is compiled for and above 4
- * problems per SM -- two (a half-warp each: the per-stage 6x6 factorisations, identical in every lane, are then issued
- * once for two problems).  Results do not depend on the layout (bit-identical).  smem_bytes / ctas_per_sm are per CTA
- * of that layout.
+ * Lane layout a launch of B problems uses: problems_per_warp = 1, or -- for the shapes it is compiled for and above 4
+ * problems per SM -- 2 (a half-warp each: the per-stage 6x6 factorisations, identical in every lane, are then issued
+ * once for two problems), or -1 for the latency mode (up to 2 problems per SM: one problem per CTA of TWO warps, the
+ * second sweeping behind the first's factorisation).  Results do not depend on the layout (bit-identical).
+ * smem_bytes / ctas_per_sm are per CTA of that layout.
  */
 int g1mpc_layout_info(const g1mpc_handle *h, int64_t B, int32_t *problems_per_warp, int32_t *smem_bytes, int32_t *ctas_per_sm);
 

@@ -172,8 +172,9 @@ def test_latency_mode_kernel_gives_the_same_bits_as_the_one_warp_kernel():
     x_current, problems that never reach a factorisation (all contacts in swing; NaN input), B = 1 and launches beyond 2 per SM."""
     preset = presets.get_preset("cpp_node")
     one, lat, auto = BatchedMPC(preset, device=0, layout=1), BatchedMPC(preset, device=0, layout=3), BatchedMPC(preset, device=0)
-    assert auto.kernel_info(1)["smem_bytes"] == lat.kernel_info(1)["smem_bytes"] == one.kernel_info(1)["smem_bytes"] + 352
-    assert auto.kernel_info(297)["smem_bytes"] == one.kernel_info(297)["smem_bytes"]          # above 2 per SM: the one-warp kernel
+    assert auto.kernel_info(1)["problems_per_warp"] == lat.kernel_info(700)["problems_per_warp"] == -1      # one problem per TWO warps
+    assert auto.kernel_info(297)["problems_per_warp"] == 1 and one.kernel_info(1)["problems_per_warp"] == 1   # above 2 per SM: one warp
+    lat2 = BatchedMPC(preset, device=0, layout=4)       # the same with two problems per main warp (not chosen automatically)
     z = _replay()
     rep = [_dev(z[k]) for k in ("x0", "x_ref", "contact", "c_horizon", "p_com")]
     rnd = list(inputs.random_batch(preset, 700, seed=41, device="cuda"))
@@ -190,6 +191,7 @@ def test_latency_mode_kernel_gives_the_same_bits_as_the_one_warp_kernel():
             a = one.update_batch(*ins, x_opt=xp.clone(), want_multipliers=True, **kw)
             for _ in range(2):
                 assert same(a, lat.update_batch(*ins, x_opt=xp.clone(), want_multipliers=True, **kw))
+            assert same(a, lat2.update_batch(*ins, x_opt=xp.clone(), want_multipliers=True, **kw))
     assert set(a[2]["status"].tolist()) == {0}
     st_odd = one.update_batch(*odd, x_current=odd[0])[2]["status"]
     assert int(st_odd[5]) == 3 and int(st_odd[3]) == 0
