@@ -134,7 +134,7 @@ def test_closed_loop_of_a_large_fleet_equals_the_small_one():
     cur[:, :, 0] = x0[:, 3:4] + np.array([-0.0293, 0.1406, -0.0293, 0.1406])
     cur[:, :, 1] = np.array([0.118508, 0.118508, -0.118508, -0.118508])
     t0 = (rng.integers(0, 30, B) + 0.5) * dt
-    assert s.kernel_info(B)["problems_per_warp"] == 2 and s.kernel_info(6)["problems_per_warp"] == 1
+    assert s.kernel_info(B)["problems_per_warp"] == 2 and s.kernel_info(6)["problems_per_warp"] == -1      # (-1: latency mode, one problem per two warps)
     big = s.closed_loop(_dev(x0), _dev(cur.reshape(B, 12)), _dev(t0), T)
     small = s.closed_loop(_dev(x0[:6]), _dev(cur[:6].reshape(6, 12)), _dev(t0[:6]), T)
     torch.cuda.synchronize()
