@@ -91,7 +91,10 @@ class BatchedMPC:
             return dict(smem_bytes=a.value, threads=b.value, ctas_per_sm=c.value)
         ppw = C.c_int32()
         _lib.check(self._lib.g1mpc_layout_info(self._h, int(B), C.byref(ppw), C.byref(a), C.byref(c)), "g1mpc_layout_info")
-        return dict(smem_bytes=a.value, threads=b.value, ctas_per_sm=c.value, problems_per_warp=ppw.value)
+        mode = ("latency: one problem per two-warp CTA" if ppw.value < 0 else "global-memory workspace, persistent grid" if a.value == 0
+                else "two problems per warp" if ppw.value == 2 else "one problem per warp")
+        return dict(smem_bytes=a.value, threads=64 if ppw.value < 0 else b.value, ctas_per_sm=c.value, problems_per_warp=ppw.value,
+                    mode=mode)
 
     # -- device API ------------------------------------------------------------------------------
     def update_batch(self, x0, x_ref, contact, c_horizon, p_com, x_current=None, *, one_rollout=False,
