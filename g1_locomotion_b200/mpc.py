@@ -503,8 +503,16 @@ class MPC:
 
     # ---- the reference's step methods (mpc.py:109-321) -------------------------------------------
     def extract_psi(self):
-        self.psi = float(np.mean(np.asarray(self.x_ref_hor, float)[:, 2]))
+        xr = np.asarray(self.x_ref_hor, float)
+        self.psi = float(xr[:, 2].sum() / xr.shape[0])          # = np.mean (same pairwise sum), without its call overhead
         return self.psi
+
+    def _contact_array(self, contact):
+        """contact[step][leg] of the reference (lists of arrays accepted, mpc.py:264) as a float [N, nc] array."""
+        N, nc = self.HORIZON_LENGTH, self.NUM_CONTACTS
+        if isinstance(contact, np.ndarray) and contact.shape == (N, nc):
+            return contact.astype(np.float64)
+        return np.array([[float(contact[i][j]) for j in range(nc)] for i in range(N)])
 
     def vector_to_skew_symmetric_matrix(self, v):
         return np.array([[0, -v[2], v[1]], [v[2], 0, -v[0]], [-v[1], v[0], 0]])
@@ -542,8 +550,7 @@ class MPC:
         self._snapshot()
 
     def calculate_bounds(self, contact):
-        self._contact = np.array([[float(contact[i][j]) for j in range(self.NUM_CONTACTS)]
-                                  for i in range(self.HORIZON_LENGTH)])
+        self._contact = self._contact_array(contact)
         self._snapshot()
 
     def calculate_hessian(self):
@@ -594,12 +601,13 @@ class MPC:
         """mpc.py:360-377 -- one fused kernel launch; returns (u_opt[N,nu], x_opt[N,13])."""
         self.c_horizon = np.array(c_horizon, float)
         self.p_com_horizon = np.array(p_com_horizon, float)
-        self._contact = np.array([[float(contact[i][j]) for j in range(self.NUM_CONTACTS)]
-                                  for i in range(self.HORIZON_LENGTH)])
+        self._contact = self._contact_array(contact)
         self.extract_psi()
         xc = None if x_current is None else np.asarray(x_current, float).reshape(self.NUM_STATES)
         self._solve(xc, one_rollout, True)
-        self._snapshot()                                   # the intermediates of THIS call, refreshed on first read
+        hb = self._hb                                      # the intermediates of THIS call, refreshed on first read
+        self._snap = (hb["x0"].copy(), hb["xr"].copy(), hb["ct"].copy(), hb["ch"].copy(), hb["pc"].copy())
+        self._stale = True
         return self.u_opt, self.x_opt
 
     def compute_rollout(self, x_current=None, only_first_step=False):
