@@ -379,7 +379,7 @@ KernelEntry make_entry()
         e.fn2 = (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 16, false>;
         e.launch2 = launch_static<LAY, 16, false>;
     }
-    if constexpr (two_per_warp<N, NC>() && N <= 14) {                   // (one named barrier per stage: N <= 14)
+    if constexpr (two_per_warp<N, NC>() && N <= 15) {                   // (one named barrier per stage: N <= 15)
         e.fnl = (const void *)v2::srbd_mpc_solve_lat_kernel<LAY, 32>;   // the short-horizon shapes: where latency is the metric
         e.launchl = launch_lat<LAY, 32>;
         e.fnl2 = (const void *)v2::srbd_mpc_solve_lat_kernel<LAY, 16>;

@@ -459,13 +459,14 @@ __device__ __forceinline__ void assemble_stage(const LAY &L, double *sm, const D
 // many factorisations this problem has had.  `lat` costs no shared memory of its own: it is the `prod` region of the layout
 // (6 NCN >= 39 doubles), which is dead from the assembly of S_k to the predictor's per-contact pass and which the partner never touches.
 // The two warps meet on NAMED BARRIERS (bar.arrive by the producer, bar.sync by the consumer, 64 threads each): barrier 1 + k
-// = "stage k of the running factorisation is stored", barrier 15 = "the partner has finished its sweep" -- hence N <= 14.  A
-// barrier id is only re-armed after the main warp has waited on barrier 15, so a lagging partner can never see two arrivals on
+// = "stage k of the running factorisation is stored", barrier 0 (free again once the kernel's opening __syncthreads has
+// passed) = "the partner has finished its sweep" -- sixteen hardware barriers, hence N <= 15.  A
+// barrier id is only re-armed after the main warp has waited on barrier 0, so a lagging partner can never see two arrivals on
 // one id.  (Polling a shared-memory word instead -- volatile, or ld.acquire with a back-off -- slowed the MAIN warp's own
 // shared-memory chains 1.7-2.5x: measured 524 / 356 us against 213 us for the single warp.  The barrier costs nothing while waiting.)
 __device__ __forceinline__ void bar_arrive64(int id) { asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory"); }
 __device__ __forceinline__ void bar_sync64(int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
-constexpr int kLatDoneBar = 15;
+constexpr int kLatDoneBar = 0;
 
 template <class LAY, int HL, bool LAT = false>
 __device__ __forceinline__ bool factor_stages(const LAY &L, double *sm, const DevParams &P, const StageC &C, int lane PH_PARAMS,

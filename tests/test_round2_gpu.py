@@ -200,6 +200,12 @@ def test_latency_mode_kernel_gives_the_same_bits_as_the_one_warp_kernel():
     for w in (torch.cat([u[:1], u[:-1]]).contiguous(), torch.full_like(u, 700.0)):
         a = one.update_batch(*rep, x_current=rep[0], u_warm=w, want_multipliers=True)
         assert same(a, lat.update_batch(*rep, x_current=rep[0], u_warm=w, want_multipliers=True))
+    # the Python default shape (N = 15: every one of the sixteen hardware barriers is in use)
+    p15 = presets.get_preset("python_default")
+    r15 = list(inputs.random_batch(p15, 200, seed=4, device="cuda"))
+    a15, l15 = BatchedMPC(p15, device=0, layout=1), BatchedMPC(p15, device=0)
+    assert l15.kernel_info(200)["problems_per_warp"] == -1
+    assert same(a15.update_batch(*r15, x_current=r15[0], want_multipliers=True), l15.update_batch(*r15, x_current=r15[0], want_multipliers=True))
     # the host API with one problem (zero-copy path) lands on the latency kernel too
     host = [t[7:8].cpu().numpy() for t in rep]
     uh, xh, ih = auto.update_host(*host, x_current=host[0])
