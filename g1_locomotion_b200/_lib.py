@@ -10,11 +10,11 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("G1MPC_B200_LIB") or os.path.join(_HERE, "libg1mpc_b200.so")   # override: A/B runs of two builds
 _lib = None
 
-EXPORTS = ["g1mpc_create", "g1mpc_destroy", "g1mpc_solve_batch", "g1mpc_solve_batch_warm", "g1mpc_rollout_batch", "g1mpc_rollout_host", "g1mpc_emit_qp_batch",
+EXPORTS = ["g1mpc_create", "g1mpc_destroy", "g1mpc_solve_batch", "g1mpc_solve_batch_warm", "g1mpc_solve_batch_static_ws", "g1mpc_rollout_batch", "g1mpc_rollout_host", "g1mpc_emit_qp_batch",
            "g1mpc_update_host", "g1mpc_update_host_begin", "g1mpc_update_host_end", "g1mpc_set_host_warm_start", "g1mpc_layout_info",
            "g1mpc_walk_inputs_batch", "g1mpc_wbid_refs_batch", "g1mpc_closed_loop_batch", "g1mpc_closed_loop_batch_ex", "g1mpc_plan_gait_batch",
            "g1mpc_main_loop_batch", "g1mpc_kernel_info", "g1mpc_fp64_peak_tflops", "g1mpc_last_error", "g1mpc_abi_version"]
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 
 class G1mpcParams(C.Structure):
@@ -56,6 +56,8 @@ def load():
     lib.g1mpc_destroy.restype = None
     lib.g1mpc_solve_batch.argtypes = [vp, i64, dp, dp, dp, dp, dp, dp, C.c_int, dp, dp, i32p, i32p, dp, dp, vp]
     lib.g1mpc_solve_batch.restype = C.c_int
+    lib.g1mpc_solve_batch_static_ws.argtypes = [vp, i64, dp, dp, dp, dp, dp, dp, C.c_int, dp, dp, i32p, i32p, dp, dp, vp]
+    lib.g1mpc_solve_batch_static_ws.restype = C.c_int
     lib.g1mpc_solve_batch_warm.argtypes = [vp, i64, dp, dp, dp, dp, dp, dp, C.c_int, dp, C.c_int, dp, dp, i32p, i32p, dp, dp, vp]
     lib.g1mpc_solve_batch_warm.restype = C.c_int
     lib.g1mpc_rollout_batch.argtypes = [vp, i64, dp, dp, dp, dp, dp, C.c_int, dp, vp]

@@ -403,6 +403,40 @@ const KernelEntry kKernels[] = {G1MPC_SHAPES(X_ENTRY)};
 
 } // namespace
 
+// ------------------------------------------------------------------------------------------------
+// Scratch of the no-allocation entry point (g1mpc_solve_batch_static_ws, below): the global-workspace variant of the solve
+// kernel needs one working-set slot per resident warp; here the slots lie in this file-scope array instead of a cudaMalloc'ed
+// block, so the call allocates nothing.  Every GPU that loads the library holds the array's G1MPC_STATIC_WS_BYTES until the
+// process exits.  In HOST code the name `g_static_ws` is a host-side stand-in, not a device address: the address the kernel
+// gets is the one cudaGetSymbolAddress returns, looked up once per device with that device current (static_ws_setup, called
+// from g1mpc_create).
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) double g_static_ws[G1MPC_STATIC_WS_BYTES / sizeof(double)];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_sws_mutex;
+bool g_sws_done[kMaxDevices];
+double *g_sws_ptr[kMaxDevices];         // DEVICE address of g_static_ws on device d (null: look-up failed, see g_sws_err)
+cudaError_t g_sws_err[kMaxDevices];
+
+// once per device; `device` must be the current device
+double *static_ws_setup(int device, cudaError_t *err)
+{
+    if (device < 0 || device >= kMaxDevices) { *err = cudaErrorInvalidDevice; return nullptr; }
+    std::lock_guard<std::mutex> lock(g_sws_mutex);
+    if (!g_sws_done[device]) {
+        void *ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_ws);
+        g_sws_err[device] = e;
+        g_sws_ptr[device] = e == cudaSuccess ? (double *)ptr : nullptr;
+        g_sws_done[device] = true;
+    }
+    *err = g_sws_err[device];
+    return g_sws_ptr[device];
+}
+} // namespace
+
 struct g1mpc_handle {
     g1mpc_params params;
     DevParams dev;
@@ -442,7 +476,12 @@ struct g1mpc_handle {
     } slot[kSlots];
     // closed-loop workspace
     char *d_loop = nullptr;
-    size_t loop_bytes = 0;
+    size_t loop_bytes = 0;    // no-allocation entry point (g1mpc_solve_batch_static_ws): device address of the static scratch array on this handle's
+    // device, the global-workspace kernel it runs and that kernel's resident warps per SM -- all looked up in g1mpc_create
+    double *sws_ptr = nullptr;
+    cudaError_t sws_err = cudaSuccess;
+    launch_fn sws_launch = nullptr;
+    int sws_ctas_per_sm = 0, sws_sms = 0;
 };
 
 extern "C" {
@@ -573,6 +612,17 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
             e = cudaStreamCreateWithFlags(&h->slot[sl].pipe[i], cudaStreamNonBlocking);
             if (e != cudaSuccess) { g_last_error = "cudaStreamCreate failed"; g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
         }
+    {
+        // set-up of the no-allocation entry point: address of the static scratch array on this device, and the kernel variant
+        // with the workspace in global memory (the compile-time instantiation where the shape has one, else the run-time layout)
+        h->sws_ptr = static_ws_setup(device, &h->sws_err);
+        const void *fn = h->kernel->fng ? h->kernel->fng : (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, true>;
+        h->sws_launch = h->kernel->fng ? h->kernel->launchg : launch_dynamic<true>;
+        cudaDeviceGetAttribute(&h->sws_sms, cudaDevAttrMultiProcessorCount, device);
+        cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, 0);             // (no shared memory: all of the SRAM as L1)
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->sws_ctas_per_sm, fn, kWarpThreads, 0);
+        if (h->sws_ctas_per_sm < 1) h->sws_ctas_per_sm = 1;
+    }
     *out = h;
     return G1MPC_OK;
 }
@@ -665,6 +715,48 @@ int g1mpc_solve_batch_warm(g1mpc_handle *h, int64_t B, const double *x0, const d
 {
     return solve_batch_impl(h, B, B, x0, x_ref, contact, c_horizon, p_com, x_current, one_rollout, u_opt, x_opt, status, iters,
                             resid, y_opt, stream, u_warm, warm_shift);
+}
+
+// g1mpc_solve_batch for callers that cannot allocate (CUDA graph capture, tight serving loops): the global-workspace
+// variant of the solve kernel on the file-scope scratch array g_static_ws.  No cudaMalloc / cudaFree / allocating library call
+// here: the array's device address, the kernel and its occupancy were looked up in g1mpc_create.  Nothing in the scratch has
+// to start at zero -- a problem writes every word of its slot before it reads it (the cudaMalloc'ed workspace of the existing
+// path is never cleared either, and one warp reuses its slot for problem after problem) -- so the previous call's contents
+// are simply overwritten.  All calls on one GPU share the array: calls that overlap on the GPU race.
+int g1mpc_solve_batch_static_ws(g1mpc_handle *h, int64_t B, const double *x0, const double *x_ref, const double *contact,
+                                const double *c_horizon, const double *p_com, const double *x_current, int one_rollout,
+                                double *u_opt, double *x_opt, int32_t *status, int32_t *iters, double *resid, double *y_opt,
+                                void *stream)
+{
+    if (!h || B < 0 || (B > 0 && (!x0 || !x_ref || !contact || !c_horizon || !p_com || !u_opt || !x_opt))) {
+        g_last_error = "g1mpc_solve_batch_static_ws: null argument"; return G1MPC_ERR_INVALID_ARGUMENT;
+    }
+    if (B == 0) return G1MPC_OK;
+    if (B > 0x7fffffffLL) { g_last_error = "batch too large for one launch"; return G1MPC_ERR_INVALID_ARGUMENT; }
+    if (!h->sws_ptr) {
+        g_last_error = std::string("g1mpc_solve_batch_static_ws: cudaGetSymbolAddress of the static scratch array failed at set-up: ") +
+                       cudaGetErrorString(h->sws_err);
+        return G1MPC_ERR_CUDA;
+    }
+    // one working-set slot per SM at least must fit the array (below that the persistent grid would leave SMs idle: use
+    // g1mpc_solve_batch, which allocates what the shape needs)
+    const size_t slot = h->dlay.bytes, fit = (size_t)G1MPC_STATIC_WS_BYTES / slot;
+    if (fit < (size_t)h->sws_sms) {
+        g_last_error = "g1mpc_solve_batch_static_ws: (horizon, num_contacts) = (" + std::to_string(h->params.horizon) + ", " +
+                       std::to_string(h->params.num_contacts) + ") needs " + std::to_string(slot) + " B of scratch per problem in flight; the static " +
+                       std::to_string((size_t)G1MPC_STATIC_WS_BYTES) + " B array must hold one per SM (" + std::to_string(h->sws_sms) +
+                       "), i.e. at most " + std::to_string((size_t)G1MPC_STATIC_WS_BYTES / (size_t)h->sws_sms) +
+                       " B each: use g1mpc_solve_batch for this shape";
+        return G1MPC_ERR_UNSUPPORTED_SHAPE;
+    }
+    CUDA_TRY(cudaSetDevice(h->device));
+    long long warps = (long long)h->sws_sms * h->sws_ctas_per_sm;      // persistent grid: warp w takes problems w, w + W, ...
+    if (warps > (long long)fit) warps = (long long)fit;
+    if (warps > B) warps = B;
+    BatchPtrs io{x0, x_ref, contact, c_horizon, p_com, x_current, u_opt, x_opt, resid, y_opt, status, iters, one_rollout, nullptr, 0, h->sws_ptr};
+    h->sws_launch((unsigned)warps, kWarpThreads, 0, (cudaStream_t)stream, h->dev, io, (long long)B, h->dlay);
+    CUDA_TRY(cudaGetLastError());
+    return G1MPC_OK;
 }
 
 int g1mpc_rollout_batch(g1mpc_handle *h, int64_t B, const double *x_ref, const double *c_horizon, const double *p_com,

@@ -31,7 +31,7 @@ extern "C" {
 #endif
 
 #define G1MPC_NUM_STATES 13
-#define G1MPC_ABI_VERSION 6
+#define G1MPC_ABI_VERSION 7
 
 typedef enum g1mpc_error {
     G1MPC_OK = 0,
@@ -114,6 +114,26 @@ int g1mpc_solve_batch_warm(g1mpc_handle *h, int64_t B, const double *x0, const d
                            const double *x_current, int one_rollout, const double *u_warm, int warm_shift,
                            double *u_opt, double *x_opt, int32_t *status, int32_t *iters, double *resid,
                            double *y_opt, void *stream);
+
+/*
+ * g1mpc_solve_batch that ALLOCATES NOTHING.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, same results as g1mpc_solve_batch (cold start).  It runs the global-memory-workspace variant of the solve
+ * kernel (params.workspace = 2) with the workspace -- one working-set slot per resident warp -- in a file-scope
+ * `static __device__` array of G1MPC_STATIC_WS_BYTES that every GPU holding the library keeps until the process exits; the
+ * call itself makes no cudaMalloc, cudaFree or allocating library call (the array's device address and the kernel's occupancy
+ * are looked up once per device in g1mpc_create).  Limit: one slot per SM must fit, i.e. the working set of one problem may
+ * be at most G1MPC_STATIC_WS_BYTES / #SMs (226,719 B on a 148-SM B200: N = 10 / nc = 4 needs 28,096 B and runs at full
+ * residency, N = 40 / nc = 8 needs 160,096 B and runs on 209 warps; N = 60 / nc = 8, 240,096 B, is rejected) -- beyond it the call returns
+ * G1MPC_ERR_UNSUPPORTED_SHAPE with the sizes in g1mpc_last_error().  Any B runs (persistent grid).  All calls on one GPU share
+ * the one array, from whatever handle or stream: calls that OVERLAP on the GPU race -- order them on one stream or with
+ * events.  Nothing in it needs clearing between calls (a problem writes each word of its slot before reading it).
+ */
+#define G1MPC_STATIC_WS_BYTES (32u << 20)
+int g1mpc_solve_batch_static_ws(g1mpc_handle *h, int64_t B, const double *x0, const double *x_ref,
+                                const double *contact, const double *c_horizon, const double *p_com,
+                                const double *x_current, int one_rollout, double *u_opt, double *x_opt,
+                                int32_t *status, int32_t *iters, double *resid, double *y_opt, void *stream);
 
 /*
  * MPC::computeRollout (mpc.cpp:427-446 / mpc.py:379-391) of a GIVEN u_opt, device pointers: x_opt[0] = x_current if given,

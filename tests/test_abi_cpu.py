@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol():
     assert set(syms) == set(_lib.EXPORTS), (syms, _lib.EXPORTS)
     for s in syms:
         assert getattr(lib, s) is not None
-    assert lib.g1mpc_abi_version() == 6 == _lib.ABI_VERSION
+    assert lib.g1mpc_abi_version() == 7 == _lib.ABI_VERSION
 
 
 def test_params_struct_matches_header_layout():
