@@ -336,14 +336,14 @@ __global__ void fp64_peak_kernel(double *out, int iters)
 // shape-independent signature (the kernels take their layout object by value, so their own signatures differ).
 typedef void (*launch_fn)(unsigned grid, unsigned block, size_t smem, cudaStream_t st, const DevParams &, const BatchPtrs &, long long B,
                           const v2::DLay &);
-template <class LAY, int HL, bool WSG>
+template <class LAY, int HL, int WSG>
 void launch_static(unsigned grid, unsigned block, size_t smem, cudaStream_t st, const DevParams &P, const BatchPtrs &io, long long B,
                    const v2::DLay &)
 {
     v2::srbd_mpc_solve_warp_kernel<LAY, HL, WSG><<<grid, block, smem, st>>>(P, io, B, LAY());
 }
 // any other shape: the same kernel source with the layout in registers
-template <bool WSG>
+template <int WSG>
 void launch_dynamic(unsigned grid, unsigned block, size_t smem, cudaStream_t st, const DevParams &P, const BatchPtrs &io, long long B,
                     const v2::DLay &L)
 {
@@ -362,6 +362,7 @@ struct KernelEntry {
     const void *fng; launch_fn launchg;                 // workspace in global memory, persistent grid (or null)
     const void *fnl; launch_fn launchl;                 // partner-warp mode: one problem per two-warp CTA (or null)
     const void *fnl2; launch_fn launchl2;               // ... two problems per two-warp CTA (or null)
+    const void *fnh; launch_fn launchh;                 // hybrid workspace: per-stage region in shared, per-contact region in global memory (or null)
 };
 // the two-problems-per-warp layout is compiled for the shapes whose stages fit the 16 lanes of a half-warp in one round
 template <int N, int NC>
@@ -369,12 +370,15 @@ constexpr bool two_per_warp() { return N <= 16 && NC == 4 && 2 * v2::WLay<N, NC>
 // the global-workspace variant is compiled for the shapes of which fewer than four fit the shared memory of an SM
 template <int N, int NC>
 constexpr bool global_ws() { return 4 * v2::WLay<N, NC>::bytes > 227 * 1024; }
+// the hybrid variant (per-stage region in shared memory, per-contact region in global memory) is compiled for the same shapes
+template <int N, int NC>
+constexpr bool hybrid_ws() { return global_ws<N, NC>(); }
 template <int N, int NC>
 KernelEntry make_entry()
 {
     using LAY = v2::WLay<N, NC>;
     KernelEntry e{N, NC, (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 32, false>, launch_static<LAY, 32, false>, LAY::bytes,
-                  nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+                  nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     if constexpr (two_per_warp<N, NC>()) {
         e.fn2 = (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 16, false>;
         e.launch2 = launch_static<LAY, 16, false>;
@@ -386,8 +390,12 @@ KernelEntry make_entry()
         e.launchl2 = launch_lat<LAY, 16>;
     }
     if constexpr (global_ws<N, NC>()) {
-        e.fng = (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 32, true>;
-        e.launchg = launch_static<LAY, 32, true>;
+        e.fng = (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 32, 1>;
+        e.launchg = launch_static<LAY, 32, 1>;
+    }
+    if constexpr (hybrid_ws<N, NC>()) {
+        e.fnh = (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 32, 2>;
+        e.launchh = launch_static<LAY, 32, 2>;
     }
     return e;
 }
@@ -449,6 +457,11 @@ struct g1mpc_handle {
     long long global_above = 0;             // launches of more problems than this use the global workspace (auto mode)
     double *d_ws = nullptr;
     int ws_warps = 0, ws_ctas_per_sm = 0;
+    // hybrid workspace (stance list, per-stage region and scratch in shared memory, per-contact region in a slot of d_ws)
+    bool use_hybrid = false;
+    size_t hy_smem = 0;
+    int hy_warps = 0, hy_ctas_per_sm = 0;
+    long long hy_from = 0, hy_upto = 0, hy_also_from = 0;     // launches of hy_from < B <= hy_upto problems, or of B >= hy_also_from, use it
     cudaEvent_t ws_event = nullptr;
     int warps_per_block = 1;
     int ctas_per_sm = 0;
@@ -520,7 +533,7 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
     CUDA_TRY(cudaSetDevice(device));
     int max_smem = 0;
     CUDA_TRY(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
-    if (p->workspace < 0 || p->workspace > 2) { g_last_error = "workspace must be 0 (auto), 1 (shared) or 2 (global)"; return G1MPC_ERR_INVALID_ARGUMENT; }
+    if (p->workspace < 0 || p->workspace > 3) { g_last_error = "workspace must be 0 (auto), 1 (shared), 2 (global) or 3 (hybrid)"; return G1MPC_ERR_INVALID_ARGUMENT; }
     const bool fits_smem = dl.bytes <= (size_t)max_smem;
     if (!fits_smem && p->workspace == 1) {
         g_last_error = "shape exceeds shared memory: (horizon, num_contacts) = (" + std::to_string(p->horizon) + ", " + std::to_string(p->num_contacts) +
@@ -534,11 +547,11 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
         // no compile-time instantiation for this shape: the run-time-layout instantiation of the same kernel
         h->dyn_entry = KernelEntry{p->horizon, p->num_contacts, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, false>, launch_dynamic<false>,
                                    dl.bytes, nullptr, nullptr, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, true>, launch_dynamic<true>,
-                                   nullptr, nullptr, nullptr, nullptr};
+                                   nullptr, nullptr, nullptr, nullptr, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, 2>, launch_dynamic<2>};
         ke = &h->dyn_entry;
     }
     // workspace in global memory: forced, needed (does not fit shared memory), or -- auto -- where fewer than four problems fit an SM
-    h->use_global = ke->fng && (p->workspace == 2 || !fits_smem || (p->workspace == 0 && 4 * dl.bytes > (size_t)max_smem));
+    h->use_global = ke->fng && p->workspace != 3 && (p->workspace == 2 || !fits_smem || (p->workspace == 0 && 4 * dl.bytes > (size_t)max_smem));
     h->fits_smem = fits_smem;
     if (p->workspace == 2 && !ke->fng) { g_last_error = "no global-workspace kernel compiled for this shape"; delete h; return G1MPC_ERR_UNSUPPORTED_SHAPE; }
     h->kernel = ke;
@@ -571,6 +584,43 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
         e = cudaMalloc((void **)&h->d_ws, (size_t)h->ws_warps * dl.bytes);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ws_event, cudaEventDisableTiming);
         if (e != cudaSuccess) { g_last_error = std::string("global workspace: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
+    }
+    if (ke->fnh && (p->workspace == 3 || (p->workspace == 0 && h->use_global))) {
+        // hybrid: stance list + per-stage region + scratch (oSt .. oEnd) in shared memory, per-contact region (0 .. oSt) in a global slot
+        // per resident warp.  workspace = 3: always.  Auto, on the shapes that have the global-workspace variant (fewer than four problems
+        // fit the shared memory of an SM) -- measured, profiles/r2_g_hybrid_workspace.txt: a launch that the shared-memory kernel does NOT
+        // hold in one wave but this one does runs 20-40 % faster here than from the global workspace; beyond one wave it wins (10-15 %)
+        // only where it keeps at least five warps per SM, and from two waves on (a second wave of a few problems is a long tail).
+        const size_t stage_bytes = sizeof(double) * (size_t)(dl.oEnd - dl.oSt);
+        int sms = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        if (stage_bytes <= (size_t)max_smem) {
+            e = cudaFuncSetAttribute(ke->fnh, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stage_bytes);
+            if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->hy_ctas_per_sm, ke->fnh, kWarpThreads, stage_bytes);
+            if (h->hy_ctas_per_sm < 1) h->hy_ctas_per_sm = 1;
+            h->hy_warps = sms * h->hy_ctas_per_sm;
+            const size_t need = (size_t)h->hy_warps * sizeof(double) * (size_t)dl.oSt;
+            if (e == cudaSuccess && !h->d_ws) {         // (a handle with the global workspace has the larger block already)
+                e = cudaMalloc((void **)&h->d_ws, need);
+                if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ws_event, cudaEventDisableTiming);
+            }
+            if (e != cudaSuccess) { g_last_error = std::string("hybrid workspace: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
+            h->use_hybrid = true; h->hy_smem = stage_bytes;
+            if (p->workspace == 3) { h->hy_from = -1; h->hy_upto = 0x7fffffffffffLL; h->hy_also_from = 0; }
+            else {
+                int shared_ctas = 0;
+                if (fits_smem) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&shared_ctas, ke->fn, kWarpThreads, ke->smem);
+                h->hy_from = (long long)sms * shared_ctas;                       // (= global_above: up to there the shared-memory kernel runs)
+                h->hy_upto = h->hy_ctas_per_sm > shared_ctas ? (long long)h->hy_warps : h->hy_from;
+                h->hy_also_from = h->hy_ctas_per_sm >= 5 ? 2LL * h->hy_warps : 0x7fffffffffffLL;
+            }
+        } else if (p->workspace == 3) {
+            g_last_error = "hybrid workspace: the per-stage region of this shape exceeds shared memory";
+            g1mpc_destroy(h); return G1MPC_ERR_UNSUPPORTED_SHAPE;
+        }
+    } else if (p->workspace == 3) {
+        g_last_error = "no hybrid-workspace kernel compiled for this shape";
+        g1mpc_destroy(h); return G1MPC_ERR_UNSUPPORTED_SHAPE;
     }
     cudaFuncSetAttribute((const void *)srbd_mpc_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
     if (fits_smem) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->ctas_per_sm, ke->fn, kWarpThreads * h->warps_per_block, ke->smem * h->warps_per_block);
@@ -646,9 +696,9 @@ void g1mpc_destroy(g1mpc_handle *h)
 int g1mpc_kernel_info(const g1mpc_handle *h, int32_t *smem_bytes, int32_t *threads, int32_t *ctas_per_sm)
 {
     if (!h) return G1MPC_ERR_INVALID_ARGUMENT;
-    if (smem_bytes) *smem_bytes = h->use_global ? 0 : (int32_t)(h->kernel->smem * h->warps_per_block);
+    if (smem_bytes) *smem_bytes = (h->use_hybrid && h->hy_from < 0) ? (int32_t)h->hy_smem : h->use_global ? 0 : (int32_t)(h->kernel->smem * h->warps_per_block);
     if (threads) *threads = kWarpThreads * h->warps_per_block;
-    if (ctas_per_sm) *ctas_per_sm = h->use_global ? h->ws_ctas_per_sm : h->ctas_per_sm;
+    if (ctas_per_sm) *ctas_per_sm = (h->use_hybrid && h->hy_from < 0) ? h->hy_ctas_per_sm : h->use_global ? h->ws_ctas_per_sm : h->ctas_per_sm;
     return G1MPC_OK;
 }
 
@@ -667,6 +717,15 @@ static int solve_batch_impl(g1mpc_handle *h, int64_t B, int64_t load, const doub
     CUDA_TRY(cudaSetDevice(h->device));
     if (warm_shift < 0) { g_last_error = "warm_shift must be >= 0"; return G1MPC_ERR_INVALID_ARGUMENT; }
     BatchPtrs io{x0, x_ref, contact, c_horizon, p_com, x_current, u_opt, x_opt, resid, y_opt, status, iters, one_rollout, u_warm, warm_shift, h->d_ws};
+    if (h->use_hybrid && ((load > h->hy_from && load <= h->hy_upto) || load >= h->hy_also_from)) {
+        cudaStream_t st = (cudaStream_t)stream;
+        CUDA_TRY(cudaStreamWaitEvent(st, h->ws_event, 0));
+        const long long want = B < h->hy_warps ? B : h->hy_warps;
+        h->kernel->launchh((unsigned)want, kWarpThreads, h->hy_smem, st, h->dev, io, (long long)B, h->dlay);
+        CUDA_TRY(cudaGetLastError());
+        CUDA_TRY(cudaEventRecord(h->ws_event, st));
+        return G1MPC_OK;
+    }
     if (h->use_global && load > h->global_above) {
         // persistent grid over the handle's workspace; launches on different streams take turns on it
         cudaStream_t st = (cudaStream_t)stream;
@@ -818,6 +877,12 @@ int g1mpc_set_host_warm_start(g1mpc_handle *h, int enable, int shift)
 int g1mpc_layout_info(const g1mpc_handle *h, int64_t B, int32_t *problems_per_warp, int32_t *smem_bytes, int32_t *ctas_per_sm)
 {
     if (!h) return G1MPC_ERR_INVALID_ARGUMENT;
+    if (h->use_hybrid && ((B > h->hy_from && B <= h->hy_upto) || B >= h->hy_also_from)) {        // hybrid workspace: persistent grid, one problem per warp, the per-stage region in shared memory
+        if (problems_per_warp) *problems_per_warp = -2;
+        if (smem_bytes) *smem_bytes = (int32_t)h->hy_smem;
+        if (ctas_per_sm) *ctas_per_sm = h->hy_ctas_per_sm;
+        return G1MPC_OK;
+    }
     if (h->use_global && B > h->global_above) {        // workspace in global memory: persistent grid, one problem per warp, no dynamic shared memory
         if (problems_per_warp) *problems_per_warp = 1;
         if (smem_bytes) *smem_bytes = 0;

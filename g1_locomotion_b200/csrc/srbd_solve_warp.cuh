@@ -375,7 +375,7 @@ struct StageC {
 
 // t_k = Bm sum_c [r x tv_c ; tv_c]  (lane k), optionally also S_k = Bm (sum_c W~ Dinv W~') Bm'
 template <class LAY, int HL, bool WITH_S>
-__device__ __forceinline__ void assemble_stage(const LAY &L, double *sm, const DevParams &P, const StageC &C, int lane)
+__device__ __forceinline__ void assemble_stage(const LAY &L, double *sm, double *smc, const DevParams &P, const StageC &C, int lane)
 {
     const int N = L.N, NC = L.NC;
     for (int k = lane; k < N; k += HL) {
@@ -383,15 +383,15 @@ __device__ __forceinline__ void assemble_stage(const LAY &L, double *sm, const D
         double Stt[6] = {0, 0, 0, 0, 0, 0}, Sff[6] = {0, 0, 0, 0, 0, 0}, Stf[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};   // tau-tau, F-F (sym), tau-F (full)
         for (int j = 0; j < NC; j++) {
             const int c = k * NC + j;
-            const double cf = sm[L.oCf + c];
+            const double cf = smc[L.oCf + c];
             if (!(P.fz_max * cf > P.fz_min * cf)) continue;          // swing / eliminated
-            const double *r = sm + L.oR + 3 * c, *tv = sm + L.oTv + 3 * c;
+            const double *r = smc + L.oR + 3 * c, *tv = (L.kTvInScratch ? sm : smc) + L.oTv + 3 * c;
             const double r0 = r[0], r1 = r[1], r2 = r[2];
             tt[0] += r1 * tv[2] - r2 * tv[1]; tt[1] += r2 * tv[0] - r0 * tv[2]; tt[2] += r0 * tv[1] - r1 * tv[0];
             tf[0] += tv[0]; tf[1] += tv[1]; tf[2] += tv[2];
             if (WITH_S) {
                 double Di[6];
-                ld6(sm + L.oProd + 6 * c, Di);        // Dblk^-1 of this iteration, left there by the per-contact pass (2)
+                ld6(smc + L.oProd + 6 * c, Di);        // Dblk^-1 of this iteration, left there by the per-contact pass (2)
                 const double D00 = Di[0], D01 = Di[1], D02 = Di[2], D11 = Di[3], D12 = Di[4], D22 = Di[5];
                 // RD = skew(r) Dinv
                 const double a00 = -r2 * D01 + r1 * D02, a01 = -r2 * D11 + r1 * D12, a02 = -r2 * D12 + r1 * D22;
@@ -825,7 +825,7 @@ __device__ __forceinline__ void lat_helper(const LAY &L, double *sm, double *lat
 // grad f(u) = s r u + W^T (M W u + h): per-stage wrench, state rollout, adjoint sweep (all O(N)), then the
 // per-stage co-state wrench in physical units (Bm^T v) is left in V for the per-contact pass.
 template <class LAY, int HL>
-__device__ __forceinline__ void gradient_sweeps(const LAY &L, double *sm, const DevParams &P, const StageC &C, int lane)
+__device__ __forceinline__ void gradient_sweeps(const LAY &L, double *sm, double *smc, const DevParams &P, const StageC &C, int lane)
 {
     const int N = L.N, NC = L.NC;
     double *w = sm + L.oW, *X = sm + L.oXs, *L1 = sm + L.oL1, *V = sm + L.oV;
@@ -836,7 +836,7 @@ __device__ __forceinline__ void gradient_sweeps(const LAY &L, double *sm, const 
         double tt[3] = {0, 0, 0}, tf[3] = {0, 0, 0};
         for (int j = 0; j < NC; j++) {
             const int c = k * NC + j;
-            const double *r = sm + L.oR + 3 * c, *f = sm + L.oU + 3 * c;
+            const double *r = smc + L.oR + 3 * c, *f = smc + L.oU + 3 * c;
             tt[0] += r[1] * f[2] - r[2] * f[1]; tt[1] += r[2] * f[0] - r[0] * f[2]; tt[2] += r[0] * f[1] - r[1] * f[0];
             tf[0] += f[0]; tf[1] += f[1]; tf[2] += f[2];
         }
@@ -937,10 +937,10 @@ __device__ __noinline__ void rollout_rows(double *gx, const double *x_current, i
 // the shifted solution gets the cold value.  lambda = mu0 / s is set at the first pass (2).  tests/ipm_model.py:warm_point
 // is the numpy twin.  `active` = this half-warp's problem takes part (control flow stays warp-uniform).
 template <class LAY, int HL>
-__device__ __forceinline__ void start_point(const LAY &L, double *sm, const DevParams &P, int lane, bool active, const double *gw, int shift)
+__device__ __forceinline__ void start_point(const LAY &L, double *smc, const DevParams &P, int lane, bool active, const double *gw, int shift)
 {
     const int N = L.N, NC = L.NC, NCN = L.NCN;
-    double *cfl = sm + L.oCf, *u = sm + L.oU, *sl = sm + L.oSl, *lam = sm + L.oLam;
+    double *cfl = smc + L.oCf, *u = smc + L.oU, *sl = smc + L.oSl, *lam = smc + L.oLam;
     const double mu = P.mu;
     for (int c = lane; c < (active ? NCN : 0); c += HL) {
         const int k = c / NC;
@@ -987,7 +987,7 @@ __device__ __forceinline__ void start_point(const LAY &L, double *sm, const DevP
 // L1/L2 caches keep close: the code is the same, `__syncwarp()` orders both.
 template <class LAY, int HL, bool LAT = false>
 __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtrs &io, long long B, const LAY &L, long long b, double *sm,
-                                              int lane, int half, double *lat = nullptr)
+                                              double *smc, int lane, int half, double *lat = nullptr)
 {
     const int N = L.N, NC = L.NC, NU = 3 * NC, NV = NU * N, NCN = NC * N;
 #ifdef G1MPC_PHASE_CLOCKS
@@ -996,10 +996,12 @@ __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtr
     if (b - half >= B) return;                     // whole warp out of range
     const bool valid = b < B;                      // odd batch: the last half-warp repeats the last problem and writes nothing
     if (!valid) b = B - 1;
-    double *rr = sm + L.oR, *cfl = sm + L.oCf, *u = sm + L.oU, *sl = sm + L.oSl, *lam = sm + L.oLam;
-    double *gf = sm + L.oGf, *Dst = sm + L.oDst, *prod = sm + L.oProd, *tv = sm + L.oTv, *E = sm + L.oE;
+    // (smc = base of the per-contact region, offsets below L.oSt; sm = base of the stance list, the per-stage region and the scratch.  They are the
+    //  same pointer except in the hybrid workspace variant of the kernel.)
+    double *rr = smc + L.oR, *cfl = smc + L.oCf, *u = smc + L.oU, *sl = smc + L.oSl, *lam = smc + L.oLam;
+    double *gf = smc + L.oGf, *Dst = smc + L.oDst, *prod = smc + L.oProd, *tv = (L.kTvInScratch ? sm : smc) + L.oTv, *E = sm + L.oE;
     double *dsv = sm + L.oRic, *dlv = sm + L.oRic + 6 * NCN;     // alias: valid only after the corrector solve
-    int *stIdx = reinterpret_cast<int *>(sm + L.oSt);
+    int *stIdx = reinterpret_cast<int *>(sm + L.oSt);      // (the list of stance contacts belongs to the on-chip part: every per-contact pass starts from it)
     const double *gx0 = io.x0 + b * NS, *gxr = io.x_ref + b * (N * NS), *gct = io.contact + b * NCN;
     const double *gch = io.c_hor + b * (NCN * 3), *gpc = io.p_com + b * (N * 3);
     const double sr = P.sr, mu = P.mu;
@@ -1056,7 +1058,7 @@ __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtr
     __syncwarp();
     // start point (cold, or from a previous solution)
     bool warm = io.u_warm != nullptr;
-    start_point<LAY, HL>(L, sm, P, lane, true, warm ? io.u_warm + b * NV : nullptr, io.warm_shift);
+    start_point<LAY, HL>(L, smc, P, lane, true, warm ? io.u_warm + b * NV : nullptr, io.warm_shift);
     const double m_ineq = 6.0 * (double)(n_stance > 0 ? n_stance : 1);
     __syncwarp();
 
@@ -1087,7 +1089,7 @@ __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtr
         double p_gf = 0.0;
         if (HL == 32 ? exact : __any_sync(kFullMask, exact && !frozen)) {
             // (1) gradient: V <- Bm^T (M W u + h)
-            gradient_sweeps<LAY, HL>(L, sm, P, C, lane);
+            gradient_sweeps<LAY, HL>(L, sm, smc, P, C, lane);
             PH(0)
             const double *Vt = sm + L.oV;
             for (int i = lane; i < (exact ? n_act : 0); i += HL) {
@@ -1162,7 +1164,7 @@ __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtr
             const bool fall = warm && !frozen && it == kWarmCheckIt && gap > 0.5 * gap_start;
             if (HL == 32 ? fall : __any_sync(kFullMask, fall)) {
                 __syncwarp();
-                start_point<LAY, HL>(L, sm, P, lane, fall, nullptr, 0);
+                start_point<LAY, HL>(L, smc, P, lane, fall, nullptr, 0);
                 if (fall) { warm = false; lam_init = false; exact = true; }
                 __syncwarp();
                 goto again;
@@ -1191,7 +1193,7 @@ __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtr
 
         PH(1)
         // (3) S_k, t_k, then the backward Riccati sweep (shared by predictor and corrector)
-        assemble_stage<LAY, HL, true>(L, sm, P, C, lane);
+        assemble_stage<LAY, HL, true>(L, sm, smc, P, C, lane);
         __syncwarp();
         PH(2)
         if (LAT) { if (lane == 0) { lat[36] = C.F.dc; lat[37] = C.F.dsn; lat[38] = C.F.dt; } }      // (published with the first stage barrier)
@@ -1261,7 +1263,7 @@ __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtr
             for (int j = 0; j < 6; j++) prod[6 * c + j] = q6[j];
         }
         __syncwarp();
-        assemble_stage<LAY, HL, false>(L, sm, P, C, lane);
+        assemble_stage<LAY, HL, false>(L, sm, smc, P, C, lane);
         __syncwarp();
         PH(5)
         solve_stages<LAY, HL>(L, sm, C, lane PH_ARGS);
@@ -1327,7 +1329,7 @@ __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtr
     // first has had its stage storage reused by the other's later iterations: evaluate w, X, V again from the returned u.
     if (HL == 16 || status == G1MPC_NUMERICAL) {
         __syncwarp();
-        gradient_sweeps<LAY, HL>(L, sm, P, C, lane);
+        gradient_sweeps<LAY, HL>(L, sm, smc, P, C, lane);
     }
     __syncwarp();
     // here w = W u, X = state response, gf = grad f(u) are consistent with the returned u
@@ -1417,23 +1419,34 @@ __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtr
 // of a problem on chip).  WSG = true: the workspace of a problem lives in GLOBAL memory (io.workspace, one slot per resident
 // warp) and the grid is persistent -- warp w takes problems w, w + W, w + 2W, ... .  For the long-horizon shapes (n = 480-960,
 // 80-160 KB per problem) shared memory held one or two warps per SM; this way the register file is the only limit
-// (8 warps per SM) and the caches carry the working set.
+// (8 warps per SM) and the caches carry the working set.  WSG = 2 (hybrid): see the branch below.
 // ------------------------------------------------------------------------------------------------
-template <class LAY, int HL, bool WSG>
+template <class LAY, int HL, int WSG>
 __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParams P, const BatchPtrs io, long long B, const LAY L)
 {
     constexpr int PPW = 32 / HL;
     extern __shared__ __align__(16) double sm_all[];
     const int lane = threadIdx.x & (HL - 1), half = (threadIdx.x & 31) / HL, warp = threadIdx.x >> 5;
-    if (!WSG) {
+    if (WSG == 0) {
         double *sm = sm_all + (size_t)(warp * PPW + half) * L.oEnd;
         const long long b = ((long long)blockIdx.x * (blockDim.x >> 5) + warp) * PPW + half;
-        solve_problem<LAY, HL>(P, io, B, L, b, sm, lane, half);
-    } else {
+        solve_problem<LAY, HL>(P, io, B, L, b, sm, sm, lane, half);
+    } else if (WSG == 1) {
         const long long w = (long long)blockIdx.x * (blockDim.x >> 5) + warp, nW = (long long)gridDim.x * (blockDim.x >> 5);
         double *sm = io.workspace + (size_t)(w * PPW + half) * L.oEnd;
         for (long long b0 = w * PPW; b0 < B; b0 += nW * PPW) {
-            solve_problem<LAY, HL>(P, io, B, L, b0 + half, sm, lane, half);
+            solve_problem<LAY, HL>(P, io, B, L, b0 + half, sm, sm, lane, half);
+            __syncwarp();
+        }
+    } else {
+        // hybrid: the stance list, the per-stage region and the scratch (offsets >= oSt: the dependent chains of the factorisation and
+        // of the sweeps) in shared memory, the per-contact region (offsets < oSt: streamed by independent per-contact passes) in a
+        // global-memory slot per resident warp, persistent grid
+        const long long w = (long long)blockIdx.x * (blockDim.x >> 5) + warp, nW = (long long)gridDim.x * (blockDim.x >> 5);
+        double *sm = sm_all + (size_t)(warp * PPW + half) * (L.oEnd - L.oSt) - L.oSt;
+        double *smc = io.workspace + (size_t)(w * PPW + half) * L.oSt;
+        for (long long b0 = w * PPW; b0 < B; b0 += nW * PPW) {
+            solve_problem<LAY, HL>(P, io, B, L, b0 + half, sm, smc, lane, half);
             __syncwarp();
         }
     }
@@ -1469,7 +1482,7 @@ __global__ void __launch_bounds__(64) srbd_mpc_solve_lat_kernel(const DevParams 
     const unsigned s_lo = slot[0] < slot[1] ? slot[0] : slot[1];
     const int main_warp = (((s_lo >> 2) & 1) == 0) == (slot[0] <= slot[1]) ? 0 : 1;
     if (warp == main_warp) {
-        solve_problem<LAY, HL, true>(P, io, B, L, (long long)blockIdx.x * PPW + half, sm, lane, half, lat);
+        solve_problem<LAY, HL, true>(P, io, B, L, (long long)blockIdx.x * PPW + half, sm, sm, lane, half, lat);
         // release the partner, which waits for a stage that will not come
         __syncwarp();
         if ((threadIdx.x & 31) == 0) cta_done = 1;

@@ -40,7 +40,7 @@ class BatchedMPC:
     def __init__(self, preset="cpp_node", device=None, gap_tol=0.0, max_iter=0, layout=0, dual_tol=0.0, warm_margin=0.0,
                  warm_mu0=0.0, workspace=0, nvtx=False, **overrides):
         """layout: 0 = lane layout chosen per launch, 1 / 2 = one / two problems per warp (bit-identical results);
-        workspace: 0 = auto, 1 = shared memory, 2 = global memory behind the caches (long horizons; bit-identical results);
+        workspace: 0 = auto, 1 = shared memory, 2 = global memory behind the caches, 3 = hybrid (long horizons; bit-identical results);
         nvtx: wrap every entry point in an NVTX range "g1mpc.<call>" (what the reference's chrono / ros::WallTime timers around
         updateMPC become on a GPU timeline, mpc.cpp:382,404-412, mpc_to_wbid_node.cpp:476,496);
         dual_tol, warm_margin, warm_mu0: see include/g1mpc_b200.h (0 = defaults)."""
@@ -91,10 +91,12 @@ class BatchedMPC:
             return dict(smem_bytes=a.value, threads=b.value, ctas_per_sm=c.value)
         ppw = C.c_int32()
         _lib.check(self._lib.g1mpc_layout_info(self._h, int(B), C.byref(ppw), C.byref(a), C.byref(c)), "g1mpc_layout_info")
-        mode = ("latency: one problem per two-warp CTA" if ppw.value < 0 else "global-memory workspace, persistent grid" if a.value == 0
-                else "two problems per warp" if ppw.value == 2 else "one problem per warp")
-        return dict(smem_bytes=a.value, threads=64 if ppw.value < 0 else b.value, ctas_per_sm=c.value, problems_per_warp=ppw.value,
-                    mode=mode)
+        mode = ("latency: one problem per two-warp CTA" if ppw.value == -1 else
+                "hybrid workspace (stage factors in shared, per-contact state in global memory), persistent grid" if ppw.value == -2 else
+                "global-memory workspace, persistent grid" if a.value == 0 else
+                "two problems per warp" if ppw.value == 2 else "one problem per warp")
+        return dict(smem_bytes=a.value, threads=64 if ppw.value == -1 else b.value, ctas_per_sm=c.value,
+                    problems_per_warp=1 if ppw.value == -2 else ppw.value, mode=mode)
 
     # -- device API ------------------------------------------------------------------------------
     def update_batch(self, x0, x_ref, contact, c_horizon, p_com, x_current=None, *, one_rollout=False,

@@ -76,8 +76,10 @@ typedef struct g1mpc_params {
     double warm_mu0;          /* warm start: initial complementarity s*lambda (<=0: default 0.1)    */
     int32_t workspace;        /* where a problem's working set (stage factors, per-contact state) lives during the solve:
                                  1 = shared memory (everything on chip; needs it to fit 227 KB), 2 = global memory behind
-                                 L1/L2 with a persistent grid (any horizon), 0 = shared where at least four problems fit an SM,
-                                 else global.  Same arithmetic, same bits.                                             */
+                                 L1/L2 with a persistent grid (any horizon), 3 = hybrid (stage factors and scratch in shared
+                                 memory, per-contact state in global memory, persistent grid), 0 = shared where at least four
+                                 problems fit an SM, else chosen per launch among the three by batch size (g1mpc_layout_info).
+                                 Same arithmetic, same bits.                                                           */
     int32_t reserved;
 } g1mpc_params;
 
@@ -279,8 +281,9 @@ int g1mpc_kernel_info(const g1mpc_handle *h, int32_t *smem_bytes, int32_t *threa
  * Lane layout a launch of B problems uses: problems_per_warp = 1, or -- for the shapes it is compiled for and above 4
  * problems per SM -- 2 (a half-warp each: the per-stage 6x6 factorisations, identical in every lane, are then issued
  * once for two problems), or -1 for the latency mode (up to 2 problems per SM: one problem per CTA of TWO warps, the
- * second sweeping behind the first's factorisation).  Results do not depend on the layout (bit-identical).
- * smem_bytes / ctas_per_sm are per CTA of that layout.
+ * second sweeping behind the first's factorisation), or -2 for the hybrid workspace (one problem per warp, persistent grid;
+ * smem_bytes = its on-chip part).  smem_bytes = 0: the global-memory workspace.  Results do not depend on the layout
+ * (bit-identical).  smem_bytes / ctas_per_sm are per CTA of that layout.
  */
 int g1mpc_layout_info(const g1mpc_handle *h, int64_t B, int32_t *problems_per_warp, int32_t *smem_bytes, int32_t *ctas_per_sm);
 

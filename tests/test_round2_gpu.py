@@ -260,7 +260,10 @@ def test_shape_beyond_shared_memory_runs_from_the_global_workspace(orc):
     with pytest.raises(RuntimeError):
         BatchedMPC(presets.get_preset("cpp_node", horizon=1), device=0)
     s = BatchedMPC(preset, device=0)
-    assert s.kernel_info(24)["smem_bytes"] == 0
+    # 24 problems fit one wave of the hybrid workspace (stage factors in shared memory, per-contact state in global memory);
+    # a batch of several waves runs from the global-memory workspace
+    assert "hybrid" in s.kernel_info(24)["mode"] and 0 < s.kernel_info(24)["smem_bytes"] < 240096
+    assert s.kernel_info(4096)["smem_bytes"] == 0
     ins = list(inputs.random_batch(preset, 24, seed=3, device="cuda"))
     u, x, info = s.update_batch(*ins, x_current=ins[0], want_multipliers=True)
     st = info["status"].tolist()
@@ -321,6 +324,23 @@ def test_global_workspace_gives_the_same_bits_as_shared_memory(N, nc, B):
     host = [t.cpu().numpy() for t in ins]
     uh, xh, ih = sg.update_host(*host, x_current=host[0])
     assert np.array_equal(uh, a[0].cpu().numpy()) and np.array_equal(ih["iters"], a[2]["iters"].cpu().numpy())
+    # the hybrid workspace (stance list, stage factors and scratch in shared memory, per-contact state in a global-memory slot per
+    # resident warp): same code again, same bits, forced and as the automatic choice picks it
+    sh = BatchedMPC(preset, device=0, workspace=3)
+    ki = sh.kernel_info(B)
+    assert "hybrid" in ki["mode"] and 0 < ki["smem_bytes"] < BatchedMPC(preset, device=0, workspace=1).kernel_info(B)["smem_bytes"]
+    for r in (sh.update_batch(*ins, x_current=ins[0], want_multipliers=True), sh.update_batch(*ins, x_current=ins[0], want_multipliers=True)):
+        assert torch.equal(a[0], r[0]) and torch.equal(a[1], r[1])
+        for k in ("status", "iters", "resid", "y"):
+            assert torch.equal(a[2][k], r[2][k]), k
+    auto = BatchedMPC(preset, device=0)
+    modes = set()
+    for Bsub in (100, ki["ctas_per_sm"] * 148, B):
+        sub = [t[:Bsub].contiguous() for t in ins]
+        r = auto.update_batch(*sub, x_current=sub[0])
+        modes.add(auto.kernel_info(Bsub)["mode"].split()[0])
+        assert torch.equal(a[0][:Bsub], r[0]) and torch.equal(a[2]["iters"][:Bsub], r[2]["iters"]), Bsub
+    assert {"one", "hybrid"} <= modes, modes          # shared memory for one wave of it, the hybrid for one wave of the hybrid
 
 
 # --------------------------------------------------------------------------------------------------------------------
