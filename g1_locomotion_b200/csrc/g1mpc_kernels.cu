@@ -363,6 +363,7 @@ struct KernelEntry {
     const void *fnl; launch_fn launchl;                 // partner-warp mode: one problem per two-warp CTA (or null)
     const void *fnl2; launch_fn launchl2;               // ... two problems per two-warp CTA (or null)
     const void *fnh; launch_fn launchh;                 // hybrid workspace: per-stage region in shared, per-contact region in global memory (or null)
+    const void *fnh2; launch_fn launchh2;               // ... two problems per warp (or null)
 };
 // the two-problems-per-warp layout is compiled for the shapes whose stages fit the 16 lanes of a half-warp in one round
 template <int N, int NC>
@@ -373,12 +374,15 @@ constexpr bool global_ws() { return 4 * v2::WLay<N, NC>::bytes > 227 * 1024; }
 // the hybrid variant (per-stage region in shared memory, per-contact region in global memory) is compiled for the same shapes
 template <int N, int NC>
 constexpr bool hybrid_ws() { return global_ws<N, NC>(); }
+// ... and with two problems per warp (the stages of a problem must fit the 16 lanes of a half-warp in one round)
+template <int N, int NC>
+constexpr bool hybrid2() { return N >= 10 && N <= 16; }
 template <int N, int NC>
 KernelEntry make_entry()
 {
     using LAY = v2::WLay<N, NC>;
     KernelEntry e{N, NC, (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 32, false>, launch_static<LAY, 32, false>, LAY::bytes,
-                  nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+                  nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     if constexpr (two_per_warp<N, NC>()) {
         e.fn2 = (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 16, false>;
         e.launch2 = launch_static<LAY, 16, false>;
@@ -396,6 +400,10 @@ KernelEntry make_entry()
     if constexpr (hybrid_ws<N, NC>()) {
         e.fnh = (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 32, 2>;
         e.launchh = launch_static<LAY, 32, 2>;
+    }
+    if constexpr (hybrid2<N, NC>()) {
+        e.fnh2 = (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 16, 2>;
+        e.launchh2 = launch_static<LAY, 16, 2>;
     }
     return e;
 }
@@ -460,7 +468,9 @@ struct g1mpc_handle {
     // hybrid workspace (stance list, per-stage region and scratch in shared memory, per-contact region in a slot of d_ws)
     bool use_hybrid = false;
     size_t hy_smem = 0;
-    int hy_warps = 0, hy_ctas_per_sm = 0;
+    int hy_warps = 0, hy_ctas_per_sm = 0, hy_ppw = 1;
+    const void *hy_fn = nullptr; launch_fn hy_launch = nullptr;
+    bool hy_whole_only = false;             // not for the chunks of a host-API batch (they would take turns on the one workspace)
     long long hy_from = 0, hy_upto = 0, hy_also_from = 0;     // launches of hy_from < B <= hy_upto problems, or of B >= hy_also_from, use it
     cudaEvent_t ws_event = nullptr;
     int warps_per_block = 1;
@@ -547,7 +557,7 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
         // no compile-time instantiation for this shape: the run-time-layout instantiation of the same kernel
         h->dyn_entry = KernelEntry{p->horizon, p->num_contacts, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, false>, launch_dynamic<false>,
                                    dl.bytes, nullptr, nullptr, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, true>, launch_dynamic<true>,
-                                   nullptr, nullptr, nullptr, nullptr, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, 2>, launch_dynamic<2>};
+                                   nullptr, nullptr, nullptr, nullptr, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, 2>, launch_dynamic<2>, nullptr, nullptr};
         ke = &h->dyn_entry;
     }
     // workspace in global memory: forced, needed (does not fit shared memory), or -- auto -- where fewer than four problems fit an SM
@@ -585,43 +595,6 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ws_event, cudaEventDisableTiming);
         if (e != cudaSuccess) { g_last_error = std::string("global workspace: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
     }
-    if (ke->fnh && (p->workspace == 3 || (p->workspace == 0 && h->use_global))) {
-        // hybrid: stance list + per-stage region + scratch (oSt .. oEnd) in shared memory, per-contact region (0 .. oSt) in a global slot
-        // per resident warp.  workspace = 3: always.  Auto, on the shapes that have the global-workspace variant (fewer than four problems
-        // fit the shared memory of an SM) -- measured, profiles/r2_g_hybrid_workspace.txt: a launch that the shared-memory kernel does NOT
-        // hold in one wave but this one does runs 20-40 % faster here than from the global workspace; beyond one wave it wins (10-15 %)
-        // only where it keeps at least five warps per SM, and from two waves on (a second wave of a few problems is a long tail).
-        const size_t stage_bytes = sizeof(double) * (size_t)(dl.oEnd - dl.oSt);
-        int sms = 0;
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-        if (stage_bytes <= (size_t)max_smem) {
-            e = cudaFuncSetAttribute(ke->fnh, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stage_bytes);
-            if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->hy_ctas_per_sm, ke->fnh, kWarpThreads, stage_bytes);
-            if (h->hy_ctas_per_sm < 1) h->hy_ctas_per_sm = 1;
-            h->hy_warps = sms * h->hy_ctas_per_sm;
-            const size_t need = (size_t)h->hy_warps * sizeof(double) * (size_t)dl.oSt;
-            if (e == cudaSuccess && !h->d_ws) {         // (a handle with the global workspace has the larger block already)
-                e = cudaMalloc((void **)&h->d_ws, need);
-                if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ws_event, cudaEventDisableTiming);
-            }
-            if (e != cudaSuccess) { g_last_error = std::string("hybrid workspace: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
-            h->use_hybrid = true; h->hy_smem = stage_bytes;
-            if (p->workspace == 3) { h->hy_from = -1; h->hy_upto = 0x7fffffffffffLL; h->hy_also_from = 0; }
-            else {
-                int shared_ctas = 0;
-                if (fits_smem) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&shared_ctas, ke->fn, kWarpThreads, ke->smem);
-                h->hy_from = (long long)sms * shared_ctas;                       // (= global_above: up to there the shared-memory kernel runs)
-                h->hy_upto = h->hy_ctas_per_sm > shared_ctas ? (long long)h->hy_warps : h->hy_from;
-                h->hy_also_from = h->hy_ctas_per_sm >= 5 ? 2LL * h->hy_warps : 0x7fffffffffffLL;
-            }
-        } else if (p->workspace == 3) {
-            g_last_error = "hybrid workspace: the per-stage region of this shape exceeds shared memory";
-            g1mpc_destroy(h); return G1MPC_ERR_UNSUPPORTED_SHAPE;
-        }
-    } else if (p->workspace == 3) {
-        g_last_error = "no hybrid-workspace kernel compiled for this shape";
-        g1mpc_destroy(h); return G1MPC_ERR_UNSUPPORTED_SHAPE;
-    }
     cudaFuncSetAttribute((const void *)srbd_mpc_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
     if (fits_smem) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->ctas_per_sm, ke->fn, kWarpThreads * h->warps_per_block, ke->smem * h->warps_per_block);
     if (h->use_global && fits_smem && p->workspace == 0) {
@@ -656,6 +629,53 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
             if (e != cudaSuccess) { g_last_error = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
             h->lat_upto = p->layout == 3 ? 0x7fffffffLL : 2LL * sms;
         }
+    }
+    // Two problems per warp from the hybrid workspace: forced by workspace = 3 with layout = 2; automatic on the short-horizon shapes
+    // for which two problems per warp do NOT pay from shared memory alone, because two working sets per CTA leave half the
+    // schedulers without a warp (N = 15 / nc = 4: 2 x 42 KB; nc = 8: 2 x 40-48 KB) -- with only the stage factors on chip four to
+    // six such CTAs fit (profiles/r2_g_hybrid_workspace.txt: +10 to +20 % from 1,024 problems on; on the bench shape, where the
+    // shared-memory two-per-warp layout holds eight problems per SM, it loses 25 % and is not used).
+    const bool smem_two = ke->fn2 && h->two_above < 0x7fffffffffffLL;
+    const bool hy2_auto = p->workspace == 0 && p->layout == 0 && ke->fnh2 && !h->use_global && !smem_two;
+    const bool hy2 = (p->workspace == 3 && p->layout == 2 && ke->fnh2) || hy2_auto;
+    h->hy_fn = hy2 ? ke->fnh2 : ke->fnh; h->hy_launch = hy2 ? ke->launchh2 : ke->launchh; h->hy_ppw = hy2 ? 2 : 1;
+    if (h->hy_fn && (p->workspace == 3 || hy2_auto || (p->workspace == 0 && h->use_global))) {
+        // hybrid: stance list + per-stage region + scratch (oSt .. oEnd) in shared memory, per-contact region (0 .. oSt) in a global slot
+        // per resident warp.  workspace = 3: always.  Auto, on the shapes that have the global-workspace variant (fewer than four problems
+        // fit the shared memory of an SM) -- measured, profiles/r2_g_hybrid_workspace.txt: a launch that the shared-memory kernel does NOT
+        // hold in one wave but this one does runs 20-40 % faster here than from the global workspace; beyond one wave it wins (10-15 %)
+        // only where it keeps at least five warps per SM, and from two waves on (a second wave of a few problems is a long tail).
+        const size_t stage_bytes = sizeof(double) * (size_t)(dl.oEnd - dl.oSt) * h->hy_ppw;
+        int sms = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        if (stage_bytes <= (size_t)max_smem) {
+            e = cudaFuncSetAttribute(h->hy_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stage_bytes);
+            if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&h->hy_ctas_per_sm, h->hy_fn, kWarpThreads, stage_bytes);
+            if (h->hy_ctas_per_sm < 1) h->hy_ctas_per_sm = 1;
+            h->hy_warps = sms * h->hy_ctas_per_sm;
+            const size_t need = (size_t)h->hy_warps * h->hy_ppw * sizeof(double) * (size_t)dl.oSt;
+            if (e == cudaSuccess && !h->d_ws) {         // (a handle with the global workspace has the larger block already)
+                e = cudaMalloc((void **)&h->d_ws, need);
+                if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ws_event, cudaEventDisableTiming);
+            }
+            if (e != cudaSuccess) { g_last_error = std::string("hybrid workspace: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
+            h->use_hybrid = true; h->hy_smem = stage_bytes;
+            if (p->workspace == 3) { h->hy_from = -1; h->hy_upto = 0x7fffffffffffLL; h->hy_also_from = 0; }
+            else if (hy2_auto) { h->hy_from = 4LL * sms; h->hy_upto = 0x7fffffffffffLL; h->hy_also_from = 0x7fffffffffffLL; h->hy_whole_only = true; }
+            else {
+                int shared_ctas = 0;
+                if (fits_smem) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&shared_ctas, ke->fn, kWarpThreads, ke->smem);
+                h->hy_from = (long long)sms * shared_ctas;                       // (= global_above: up to there the shared-memory kernel runs)
+                h->hy_upto = h->hy_ctas_per_sm > shared_ctas ? (long long)h->hy_warps : h->hy_from;
+                h->hy_also_from = h->hy_ctas_per_sm >= 5 ? 2LL * h->hy_warps : 0x7fffffffffffLL;
+            }
+        } else if (p->workspace == 3) {
+            g_last_error = "hybrid workspace: the per-stage region of this shape exceeds shared memory";
+            g1mpc_destroy(h); return G1MPC_ERR_UNSUPPORTED_SHAPE;
+        }
+    } else if (p->workspace == 3) {
+        g_last_error = "no hybrid-workspace kernel compiled for this shape";
+        g1mpc_destroy(h); return G1MPC_ERR_UNSUPPORTED_SHAPE;
     }
     for (int sl = 0; sl < g1mpc_handle::kSlots; sl++)
         for (int i = 0; i < g1mpc_handle::kPipe; i++) {
@@ -717,11 +737,11 @@ static int solve_batch_impl(g1mpc_handle *h, int64_t B, int64_t load, const doub
     CUDA_TRY(cudaSetDevice(h->device));
     if (warm_shift < 0) { g_last_error = "warm_shift must be >= 0"; return G1MPC_ERR_INVALID_ARGUMENT; }
     BatchPtrs io{x0, x_ref, contact, c_horizon, p_com, x_current, u_opt, x_opt, resid, y_opt, status, iters, one_rollout, u_warm, warm_shift, h->d_ws};
-    if (h->use_hybrid && ((load > h->hy_from && load <= h->hy_upto) || load >= h->hy_also_from)) {
+    if (h->use_hybrid && ((load > h->hy_from && load <= h->hy_upto) || load >= h->hy_also_from) && (!h->hy_whole_only || B == load)) {
         cudaStream_t st = (cudaStream_t)stream;
         CUDA_TRY(cudaStreamWaitEvent(st, h->ws_event, 0));
-        const long long want = B < h->hy_warps ? B : h->hy_warps;
-        h->kernel->launchh((unsigned)want, kWarpThreads, h->hy_smem, st, h->dev, io, (long long)B, h->dlay);
+        const long long nw = (B + h->hy_ppw - 1) / h->hy_ppw, want = nw < h->hy_warps ? nw : h->hy_warps;
+        h->hy_launch((unsigned)want, kWarpThreads, h->hy_smem, st, h->dev, io, (long long)B, h->dlay);
         CUDA_TRY(cudaGetLastError());
         CUDA_TRY(cudaEventRecord(h->ws_event, st));
         return G1MPC_OK;
@@ -878,7 +898,7 @@ int g1mpc_layout_info(const g1mpc_handle *h, int64_t B, int32_t *problems_per_wa
 {
     if (!h) return G1MPC_ERR_INVALID_ARGUMENT;
     if (h->use_hybrid && ((B > h->hy_from && B <= h->hy_upto) || B >= h->hy_also_from)) {        // hybrid workspace: persistent grid, one problem per warp, the per-stage region in shared memory
-        if (problems_per_warp) *problems_per_warp = -2;
+        if (problems_per_warp) *problems_per_warp = h->hy_ppw == 2 ? -3 : -2;
         if (smem_bytes) *smem_bytes = (int32_t)h->hy_smem;
         if (ctas_per_sm) *ctas_per_sm = h->hy_ctas_per_sm;
         return G1MPC_OK;

@@ -93,10 +93,11 @@ class BatchedMPC:
         _lib.check(self._lib.g1mpc_layout_info(self._h, int(B), C.byref(ppw), C.byref(a), C.byref(c)), "g1mpc_layout_info")
         mode = ("latency: one problem per two-warp CTA" if ppw.value == -1 else
                 "hybrid workspace (stage factors in shared, per-contact state in global memory), persistent grid" if ppw.value == -2 else
+                "hybrid workspace, two problems per warp, persistent grid" if ppw.value == -3 else
                 "global-memory workspace, persistent grid" if a.value == 0 else
                 "two problems per warp" if ppw.value == 2 else "one problem per warp")
         return dict(smem_bytes=a.value, threads=64 if ppw.value == -1 else b.value, ctas_per_sm=c.value,
-                    problems_per_warp=1 if ppw.value == -2 else ppw.value, mode=mode)
+                    problems_per_warp={-2: 1, -3: 2}.get(ppw.value, ppw.value), mode=mode)
 
     # -- device API ------------------------------------------------------------------------------
     def update_batch(self, x0, x_ref, contact, c_horizon, p_com, x_current=None, *, one_rollout=False,

@@ -281,8 +281,8 @@ int g1mpc_kernel_info(const g1mpc_handle *h, int32_t *smem_bytes, int32_t *threa
  * Lane layout a launch of B problems uses: problems_per_warp = 1, or -- for the shapes it is compiled for and above 4
  * problems per SM -- 2 (a half-warp each: the per-stage 6x6 factorisations, identical in every lane, are then issued
  * once for two problems), or -1 for the latency mode (up to 2 problems per SM: one problem per CTA of TWO warps, the
- * second sweeping behind the first's factorisation), or -2 for the hybrid workspace (one problem per warp, persistent grid;
- * smem_bytes = its on-chip part).  smem_bytes = 0: the global-memory workspace.  Results do not depend on the layout
+ * second sweeping behind the first's factorisation), or -2 / -3 for the hybrid workspace with one / two problems per warp
+ * (persistent grid; smem_bytes = its on-chip part).  smem_bytes = 0: the global-memory workspace.  Results do not depend on the layout
  * (bit-identical).  smem_bytes / ctas_per_sm are per CTA of that layout.
  */
 int g1mpc_layout_info(const g1mpc_handle *h, int64_t B, int32_t *problems_per_warp, int32_t *smem_bytes, int32_t *ctas_per_sm);

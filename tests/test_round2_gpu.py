@@ -343,6 +343,34 @@ def test_global_workspace_gives_the_same_bits_as_shared_memory(N, nc, B):
     assert {"one", "hybrid"} <= modes, modes          # shared memory for one wave of it, the hybrid for one wave of the hybrid
 
 
+@pytest.mark.parametrize("pname,N,nc,B", [("python_default", 15, 4, 4001), ("cpp_node", 10, 8, 4001), ("cpp_node", 12, 8, 3333)])
+def test_two_problems_per_warp_from_the_hybrid_workspace_give_the_same_bits(pname, N, nc, B):
+    """Short horizons whose two-problem CTAs would leave schedulers empty if both working sets lay in shared memory (N = 15, or
+    eight contacts per stage) run two problems per warp with only the stage factors on chip and the per-contact state in a
+    global-memory slot per half-warp (persistent grid; above 4 problems per SM, whole-batch launches).  Same code, same bits as
+    one problem per warp from shared memory -- odd batch (the last half-warp idles) and more than two waves of the grid."""
+    preset = presets.get_preset(pname, horizon=N, num_contacts=nc)
+    ins = list(inputs.random_batch(preset, B, seed=31, device="cuda"))
+    one = BatchedMPC(preset, device=0, layout=1, workspace=1)
+    a = one.update_batch(*ins, x_current=ins[0], want_multipliers=True)
+    assert one.kernel_info(B)["mode"] == "one problem per warp"
+    auto = BatchedMPC(preset, device=0)
+    ki = auto.kernel_info(B)
+    assert ki["mode"].startswith("hybrid workspace, two problems per warp") and ki["problems_per_warp"] == 2, ki
+    assert B > 2 * 2 * 148 * ki["ctas_per_sm"]                               # more than two waves of the persistent grid
+    assert "hybrid" not in auto.kernel_info(500)["mode"]
+    forced = BatchedMPC(preset, device=0, workspace=3, layout=2)
+    for s in (auto, forced, auto):
+        r = s.update_batch(*ins, x_current=ins[0], want_multipliers=True)
+        assert torch.equal(a[0], r[0]) and torch.equal(a[1], r[1])
+        for k in ("status", "iters", "resid", "y"):
+            assert torch.equal(a[2][k], r[2][k]), k
+    # the host API cuts a batch into chunks on several streams: those keep the shared-memory kernel (no shared workspace to queue on)
+    host = [t.cpu().numpy() for t in ins]
+    uh, xh, ih = auto.update_host(*host, x_current=host[0])
+    assert np.array_equal(uh, a[0].cpu().numpy()) and np.array_equal(ih["iters"], a[2]["iters"].cpu().numpy())
+
+
 # --------------------------------------------------------------------------------------------------------------------
 # 8a a18: the drop-in class keeps every intermediate current after update(), like the reference object
 # --------------------------------------------------------------------------------------------------------------------
