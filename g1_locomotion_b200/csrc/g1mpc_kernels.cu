@@ -343,11 +343,11 @@ void launch_static(unsigned grid, unsigned block, size_t smem, cudaStream_t st, 
     v2::srbd_mpc_solve_warp_kernel<LAY, HL, WSG><<<grid, block, smem, st>>>(P, io, B, LAY());
 }
 // any other shape: the same kernel source with the layout in registers
-template <int WSG>
+template <int WSG, int HL = 32>
 void launch_dynamic(unsigned grid, unsigned block, size_t smem, cudaStream_t st, const DevParams &P, const BatchPtrs &io, long long B,
                     const v2::DLay &L)
 {
-    v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, WSG><<<grid, block, smem, st>>>(P, io, B, L);
+    v2::srbd_mpc_solve_warp_kernel<v2::DLay, HL, WSG><<<grid, block, smem, st>>>(P, io, B, L);
 }
 template <class LAY, int HL>
 void launch_lat(unsigned grid, unsigned block, size_t smem, cudaStream_t st, const DevParams &P, const BatchPtrs &io, long long B,
@@ -558,6 +558,11 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
         h->dyn_entry = KernelEntry{p->horizon, p->num_contacts, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, false>, launch_dynamic<false>,
                                    dl.bytes, nullptr, nullptr, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, true>, launch_dynamic<true>,
                                    nullptr, nullptr, nullptr, nullptr, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, 2>, launch_dynamic<2>, nullptr, nullptr};
+        // two problems per warp where the stages of a problem fit the 16 lanes of a half-warp in one round (as for the compiled shapes)
+        if (p->horizon <= 16 && p->num_contacts == 4 && 2 * dl.bytes <= (size_t)max_smem) {
+            h->dyn_entry.fn2 = (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 16, 0>;
+            h->dyn_entry.launch2 = launch_dynamic<0, 16>;
+        }
         ke = &h->dyn_entry;
     }
     // workspace in global memory: forced, needed (does not fit shared memory), or -- auto -- where fewer than four problems fit an SM

@@ -466,6 +466,27 @@ def test_two_problems_per_warp_layout_gives_the_same_bits():
     assert int((b[2]["status"] != 0).sum()) == 0
 
 
+@pytest.mark.parametrize("pname,N,auto_ppw", [("cpp_node", 12, 2), ("python_default", 7, 2), ("cpp_node", 16, 1)])
+def test_two_problems_per_warp_layout_on_run_time_shapes(pname, N, auto_ppw):
+    """Horizons without a compile-time instantiation (the reference takes HORIZON_LENGTH at run time, mpc.py:12) get the two-per-warp
+    layout as well, from the run-time-layout instantiation of the same kernel, for N <= 16 and four contacts: same bits as one
+    problem per warp, and the automatic choice uses it above 4 problems per SM -- unless two-problem CTAs would hold fewer
+    problems per SM than one-problem CTAs do (N = 16: 2 x 2 against 5), the rule of the compiled shapes."""
+    preset = presets.get_preset(pname, horizon=N)
+    s1, s2, auto = (BatchedMPC(preset, device=0, layout=l) for l in (1, 2, 0))
+    B = 1501
+    assert s1.kernel_info(B)["problems_per_warp"] == 1 and s2.kernel_info(3)["problems_per_warp"] == 2
+    assert auto.kernel_info(B)["problems_per_warp"] == auto_ppw and auto.kernel_info(500)["problems_per_warp"] == 1
+    ins = list(inputs.random_batch(preset, B, seed=5 + N, device="cuda"))
+    a = s1.update_batch(*ins, x_current=ins[0], want_multipliers=True)
+    assert int((a[2]["status"] != 0).sum()) == 0
+    for s in (s2, auto):
+        b = s.update_batch(*ins, x_current=ins[0], want_multipliers=True)
+        assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+        for k in ("status", "iters", "resid", "y"):
+            assert torch.equal(a[2][k], b[2][k]), k
+
+
 def test_bench_config5_line():
     """`bench.py --config5` on one GPU: the full 2^20-problem batch of BASELINE.json configs[4] as a single shard; one JSON
     line, nothing unsolved, above north_star's 1e6 problems/s."""
