@@ -15,7 +15,9 @@ Follows, field by field:
 Messages are plain dicts with the .msg field names (what `rospy` message objects expose as attributes).
 `serialize` / `deserialize` implement the ROS 1 wire encoding of `SRBD_state` (little-endian; `string` and arrays with a
 uint32 length prefix; `Header` = uint32 seq, uint32 secs, uint32 nsecs, string frame_id; `bool` one byte).
-Parity unpinned: there is no ROS on this box, the encoding is restated from the ROS 1 serialization rules.
+The simulator's halves (pack_srbd_current, unpack_mpc_solution) are pinned to ros_run_simulation.py's own functions run on stand-in
+message objects (tests/test_reference_callers_cpu.py); there is no ROS on this box, so the node's halves (C++) and the byte encoding
+are restated from the sources / the ROS 1 serialization rules: that part stays parity unpinned.
 
 Host-side glue only: nothing here touches the device; the arrays go to `BatchedMPC.walk_inputs` / `update_*`.
 """

@@ -110,6 +110,57 @@ def gait_golden():
     print("gait_plan", len(rows), "cases")
 
 
+def callers_golden():
+    """Two CALLERS of the path run from the reference's own sources (oracle/ref_loader.py says how):
+    wbid_refs.npz    -- WholeBodyID.setReference (g1_mujoco_sim/src/wbid.py:231-297) on 96 random (x_opt[1], u_opt[0], foot positions),
+                        what it hands its OpenSoT tasks in the order of g1mpc_wbid_refs_batch (SURVEY 8f-2);
+    ref_main_loop.npz -- g1_mpc/scripts/main.py main() as shipped (python defaults, planner (1000, 0.25, 0.1, 0.2, 100), 4 s), first 40
+                        ticks: per tick the inputs main() handed the class and the u_opt / x_opt it got back through the OSQP shim, plus
+                        the x_opt[0] / u_opt[0] history main() records."""
+    from oracle import node_oracle
+    W = ref_loader.load_wbid()
+    rng = np.random.default_rng(20251105)
+    B = 96
+    x1 = np.concatenate([rng.uniform(-0.4, 0.4, (B, 3)), rng.uniform(-2, 2, (B, 3)), rng.uniform(-1.5, 1.5, (B, 6)), np.full((B, 1), -9.80665)], 1)
+    u0 = np.stack([rng.uniform(-80, 80, (B, 4)), rng.uniform(-80, 80, (B, 4)), rng.uniform(0, 400, (B, 4))], 2).reshape(B, 12)
+    feet = x1[:, None, 3:6] + rng.uniform(-0.3, 0.3, (B, 4, 3))
+    mass = 35.112
+    refs = np.stack([ref_loader.reference_wbid_set_reference(W, x1[b], u0[b], feet[b], mass) for b in range(B)])
+    mine = np.stack([node_oracle.wbid_refs_flat(x1[b], u0[b], feet[b], mass) for b in range(B)])
+    assert np.array_equal(refs, mine), np.abs(refs - mine).max()        # the restatement IS the reference code, bit for bit
+    np.savez_compressed(os.path.join(OUT, "wbid_refs.npz"), x_opt1=x1, u_opt0=u0, feet=feet, mass=mass, refs=refs)
+    print("wbid_refs", refs.shape)
+    tx, tu, ticks = ref_loader.run_reference_main(max_ticks=40, per_tick=True)
+    np.savez_compressed(os.path.join(OUT, "ref_main_loop.npz"), planner=np.array([1000., 0.25, 0.1, 0.2, 100.]), total_duration=4.0,
+                        foot_offset=0.08, traj_x=tx, traj_u=tu, **{k: np.stack([t[k] for t in ticks]) for k in ticks[0]})
+    print("ref_main_loop", tx.shape, {k: np.stack([t[k] for t in ticks]).shape for k in ticks[0]})
+    # SURVEY 8f-4, the simulator's (Python) halves of the message exchange, from g1_mujoco_sim/src/ros_run_simulation.py itself:
+    # publish_current_state (:22-78) and G1MujocoSimulation.callback_mpc_solution (:188-218) on stand-in message objects
+    from g1_locomotion_b200 import wire
+    sim = ref_loader.load_ros_simulation()
+    K, N = 24, 10
+    x0 = rng.normal(size=(K, 13)); x0[:, 12] = -9.80665
+    fpos = rng.normal(size=(K, 4, 3)); qf = rng.normal(0, 100, (K, 12))
+    pub = [ref_loader.reference_publish_current_state(sim, x0[k, 0:3], x0[k, 3:6], x0[k, 6:9], x0[k, 9:12], fpos[k], qf[k], 0.05 * k) for k in range(K)]
+    assert all(p["n_states"] == 1 and p["trajectory_index"] == 0 and p["frame_id"] == "SRBD" for p in pub)
+    x_opt = rng.normal(size=(K, N, 13)); u_opt = rng.normal(0, 100, (K, N, 12)); c_hor = rng.normal(size=(K, N, 12))
+    contact = (rng.uniform(size=(K, N, 4)) > 0.4).astype(float); landing = rng.normal(size=(K, 2))
+    cb = [ref_loader.reference_callback_mpc_solution(sim, ref_loader.msg_from_dict(
+        wire.pack_mpc_solution(x_opt[k], u_opt[k], c_hor[k], contact[k], landing[k], sim_time=0.05 * k))) for k in range(K)]
+    np.savez_compressed(os.path.join(OUT, "wire_simulator.npz"), x0=x0, foot_positions=fpos, qp_forces=qf,
+                        pub_state=np.stack([p["state"] for p in pub]), pub_positions=np.stack([p["positions"] for p in pub]),
+                        pub_forces=np.stack([p["forces"] for p in pub]), pub_names=np.array(pub[0]["names"]),
+                        x_opt=x_opt, u_opt=u_opt, c_horizon=c_hor, contact=contact, landing=landing,
+                        cb_x_opt=np.stack([c[0] for c in cb]), cb_u_opt0=np.stack([c[1] for c in cb]),
+                        cb_contact_states=np.array([c[2] for c in cb]), cb_landing=np.stack([c[3] for c in cb]))
+    print("wire_simulator", K, "cases")
+
+
 if __name__ == "__main__":
-    main()
-    gait_golden()
+    import sys
+    if len(sys.argv) > 1 and sys.argv[1] == "callers":
+        callers_golden()
+    else:
+        main()
+        gait_golden()
+        callers_golden()

@@ -127,10 +127,12 @@ def double_support_reference(x_ref, current_time, total_duration, dt):
     return x_ref
 
 
-def main_loop(orc, preset, planner, ticks, total_duration=4.0, foot_offset=0.08):
+def main_loop(orc, preset, planner, ticks, total_duration=4.0, foot_offset=0.08, solve=None, on_tick=None):
     """The SRBD-only loop of g1_mpc/scripts/main.py:200-326 for ONE walker on the CPU: planner phases -> mapping ->
     reference build (oracle.build) -> exact QP minimiser -> x_opt[0] carry and rollout without x_current (main.py:306-311);
-    the next solve starts from x_opt[2] (main.py:228).  Returns traj_x[ticks,13] (x_opt[0] after each rollout), traj_u[ticks,12]."""
+    the next solve starts from x_opt[2] (main.py:228).  Returns traj_x[ticks,13] (x_opt[0] after each rollout), traj_u[ticks,12].
+    solve(k, m, contact) -> u[N,12] replaces the exact minimiser (the pinning test feeds the reference run's own u_opt back, so that
+    the LOOP LOGIC is compared tick by tick without a solver in between); on_tick(k, dict of this tick's inputs and x_opt) observes."""
     N, dt, g = preset["horizon"], preset["dt"], preset.get("gravity", -9.80665)
     p = orc.params_from_dict(preset)
     phases = plan_gait(*planner)
@@ -147,12 +149,17 @@ def main_loop(orc, preset, planner, ticks, total_duration=4.0, foot_offset=0.08)
         contact, c_hor = map_gait_phases(phases, t, N, dt, foot_offset)
         p_com = x_ref[:, 3:6].copy()                                      # main.py:286
         m = orc.build(p, x0, x_ref, contact, c_hor, p_com)
-        xs, _, cert = orc.qp_exact(p, m["H"], m["g"], contact)
-        assert cert["rc"] == 0, cert
-        u = xs.reshape(N, 12)
+        if solve is None:
+            xs, _, cert = orc.qp_exact(p, m["H"], m["g"], contact)
+            assert cert["rc"] == 0, cert
+            u = xs.reshape(N, 12)
+        else:
+            u = np.asarray(solve(k, m, contact), float).reshape(N, 12)
         x_opt[0] = x0 if k == 0 else x_opt[1].copy()                      # main.py:306-310
         x_opt = orc.rollout(p, m["A"], m["Bd"], u, None, False, x_opt=x_opt)
         tx[k], tu[k] = x_opt[0], u[0]
+        if on_tick is not None:
+            on_tick(k, dict(x0=x0.copy(), x_ref=x_ref.copy(), contact=contact.copy(), c_horizon=c_hor.copy(), p_com=p_com, x_opt=x_opt.copy()))
         t += dt                                                           # main.py:326
     return tx, tu
 

@@ -80,6 +80,24 @@ def test_wbid_refs_match_restatement():
         assert np.array_equal(refs[b, 9:], want[9:]), (b, np.abs(refs[b, 9:] - want[9:]).max())
 
 
+def test_wbid_refs_match_the_reference_set_reference_golden():
+    """g1mpc_wbid_refs_batch against what the reference's OWN WholeBodyID.setReference (g1_mujoco_sim/src/wbid.py:231-297) handed its
+    OpenSoT tasks on the same inputs (tests/golden/wbid_refs.npz, written by `python -m oracle.gen_golden callers` from the unmodified
+    file with recording stand-ins for the tasks): bit for bit, except the rotation (device sin/cos, <= 4e-16)."""
+    import os
+    from conftest import ROOT
+    from g1_locomotion_b200 import BatchedMPC
+    z = np.load(os.path.join(ROOT, "tests", "golden", "wbid_refs.npz"))
+    B, N = len(z["refs"]), 10
+    s = BatchedMPC(presets.get_preset("cpp_node"))
+    rng = np.random.default_rng(9)
+    u = rng.normal(0, 100, (B, N, 12)); x = rng.normal(0, 0.4, (B, N, 13))
+    u[:, 0], x[:, 1] = z["u_opt0"], z["x_opt1"]                    # the adaptor reads row 0 of u_opt and row 1 of x_opt (ros_run_simulation.py:409)
+    refs = s.wbid_refs(_dev(u), _dev(x), _dev(z["feet"]), float(z["mass"])).cpu().numpy()
+    assert np.abs(refs[:, :9] - z["refs"][:, :9]).max() <= 4e-16
+    assert np.array_equal(refs[:, 9:], z["refs"][:, 9:]), np.abs(refs[:, 9:] - z["refs"][:, 9:]).max()
+
+
 def test_adaptors_reject_unsupported_shapes():
     from g1_locomotion_b200 import BatchedMPC
     s = BatchedMPC(presets.get_preset("cpp_node", num_contacts=8))

@@ -506,6 +506,27 @@ def test_main_loop_matches_cpu_composition(orc):
     assert int(warm["iters_sum"].sum()) <= int(out["iters_sum"].sum()) + 5 * T * len(planners)
 
 
+def test_main_loop_on_the_scenario_main_py_ships(orc):
+    """g1mpc_main_loop_batch on main.py's own scenario (mpc.MPC() defaults, GaitPlanner(1000, 0.25, 0.1, 0.2, 100), total_duration 4 s):
+    (i) against the restated loop closed on the exact minimiser -- the loop whose logic tests/test_reference_callers_cpu.py holds to
+    the reference's main() tick by tick; (ii) against the trajectory the reference's own main() produced through the OSQP shim
+    (tests/golden/ref_main_loop.npz): that run stops every solve at eps 1e-3, so the two closed loops agree to millimetres in the
+    CoM and centimetres per second in the velocities, not better."""
+    z = np.load(os.path.join(ROOT, "tests", "golden", "ref_main_loop.npz"))
+    preset = presets.get_preset("python_default")
+    s = BatchedMPC(preset, device=0)
+    T = 32
+    out = s.main_loop(_dev(z["planner"][None]), T, total_duration=float(z["total_duration"]), foot_offset=float(z["foot_offset"]))
+    torch.cuda.synchronize()
+    assert int(out["status_any"].abs().sum()) == 0
+    tx, tu = out["traj_x"][0].cpu().numpy(), out["traj_u"][0].cpu().numpy()
+    ex, eu = node_oracle.main_loop(orc, preset, tuple(z["planner"]), T, total_duration=float(z["total_duration"]))
+    assert np.abs(tx - ex).max() <= 1e-5 and np.abs(tu - eu).max() <= 5e-3, (np.abs(tx - ex).max(), np.abs(tu - eu).max())
+    d = np.abs(tx - z["traj_x"][:T]).max(0)
+    assert d[:6].max() <= 5e-3 and d[6:12].max() <= 5e-2, d
+    assert np.abs(tu - z["traj_u"][:T]).max() <= 40.0                  # (forces of an eps = 1e-3 OSQP iterate: tens of newtons off)
+
+
 # --------------------------------------------------------------------------------------------------------------------
 # C++ adapter (include/g1mpc_mpc.hpp) -- compiled by __graft_entry__.build(), run here against the Python path
 # --------------------------------------------------------------------------------------------------------------------
