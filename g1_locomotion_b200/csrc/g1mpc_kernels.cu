@@ -355,6 +355,13 @@ void launch_lat(unsigned grid, unsigned block, size_t smem, cudaStream_t st, con
 {
     v2::srbd_mpc_solve_lat_kernel<LAY, HL><<<grid, block, smem, st>>>(P, io, B, LAY());
 }
+typedef void (*launch_refill_fn)(unsigned grid, size_t smem, cudaStream_t st, const DevParams &, const BatchPtrs &, long long B,
+                                 unsigned long long *next);
+template <class LAY>
+void launch_refill(unsigned grid, size_t smem, cudaStream_t st, const DevParams &P, const BatchPtrs &io, long long B, unsigned long long *next)
+{
+    v2::srbd_mpc_solve_refill_kernel<LAY, 16><<<grid, 32, smem, st>>>(P, io, B, LAY(), next);
+}
 struct KernelEntry {
     int N, NC;
     const void *fn; launch_fn launch; size_t smem;      // workspace in shared memory; smem = bytes per problem
@@ -364,6 +371,7 @@ struct KernelEntry {
     const void *fnl2; launch_fn launchl2;               // ... two problems per two-warp CTA (or null)
     const void *fnh; launch_fn launchh;                 // hybrid workspace: per-stage region in shared, per-contact region in global memory (or null)
     const void *fnh2; launch_fn launchh2;               // ... two problems per warp (or null)
+    const void *fnr; launch_refill_fn launchr;          // two problems per warp with refill, persistent grid (or null)
 };
 // the two-problems-per-warp layout is compiled for the shapes whose stages fit the 16 lanes of a half-warp in one round
 template <int N, int NC>
@@ -382,10 +390,14 @@ KernelEntry make_entry()
 {
     using LAY = v2::WLay<N, NC>;
     KernelEntry e{N, NC, (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 32, false>, launch_static<LAY, 32, false>, LAY::bytes,
-                  nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+                  nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     if constexpr (two_per_warp<N, NC>()) {
         e.fn2 = (const void *)v2::srbd_mpc_solve_warp_kernel<LAY, 16, false>;
         e.launch2 = launch_static<LAY, 16, false>;
+        if constexpr (N == 10) {         // (the bench shape)
+            e.fnr = (const void *)v2::srbd_mpc_solve_refill_kernel<LAY, 16>;
+            e.launchr = launch_refill<LAY>;
+        }
     }
     if constexpr (two_per_warp<N, NC>() && N <= 15) {                   // (one named barrier per stage: N <= 15)
         e.fnl = (const void *)v2::srbd_mpc_solve_lat_kernel<LAY, 32>;   // the short-horizon shapes: where latency is the metric
@@ -480,6 +492,11 @@ struct g1mpc_handle {
     long long two_above = 0, lat_upto = 0;      // launches of at most lat_upto problems run the latency-mode kernel
     int lat2 = 0;                               // partner-warp kernel with two problems per warp: 0 off, 1 in place of the plain one, 2 always
     int force_ppw = 0;
+    // two problems per warp with refill: a counter per launch in flight (round robin), persistent grid of refill_ctas CTAs
+    static constexpr int kRefillCounters = 64;
+    unsigned long long *d_refill = nullptr;
+    int refill_k = 0, refill_ctas = 0;
+    long long refill_above = 0x7fffffffffffLL;
     int host_warm = 0, host_warm_shift = 1;     // g1mpc_set_host_warm_start
     // host-API staging: kSlots batches in flight, each cut into up to kPipe chunks with a stream of their own
     static constexpr int kPipe = 4, kSlots = G1MPC_HOST_SLOTS;
@@ -532,7 +549,7 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
         g_last_error = "q_weights[12] (gravity state) must be 0: the state is constant and is not part of the tracked cost";
         return G1MPC_ERR_INVALID_ARGUMENT;
     }
-    if (p->layout < 0 || p->layout > 4) { g_last_error = "layout must be 0 (auto), 1, 2, 3 or 4"; return G1MPC_ERR_INVALID_ARGUMENT; }
+    if (p->layout < 0 || p->layout > 5) { g_last_error = "layout must be 0 (auto), 1, 2, 3, 4 or 5"; return G1MPC_ERR_INVALID_ARGUMENT; }
     const KernelEntry *ke = nullptr;
     for (const auto &k : kKernels) if (k.N == p->horizon && k.NC == p->num_contacts) ke = &k;
     const v2::DLay dl(p->horizon, p->num_contacts);
@@ -557,7 +574,7 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
         // no compile-time instantiation for this shape: the run-time-layout instantiation of the same kernel
         h->dyn_entry = KernelEntry{p->horizon, p->num_contacts, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, false>, launch_dynamic<false>,
                                    dl.bytes, nullptr, nullptr, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, true>, launch_dynamic<true>,
-                                   nullptr, nullptr, nullptr, nullptr, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, 2>, launch_dynamic<2>, nullptr, nullptr};
+                                   nullptr, nullptr, nullptr, nullptr, (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 32, 2>, launch_dynamic<2>, nullptr, nullptr, nullptr, nullptr};
         // two problems per warp where the stages of a problem fit the 16 lanes of a half-warp in one round (as for the compiled shapes)
         if (p->horizon <= 16 && p->num_contacts == 4 && 2 * dl.bytes <= (size_t)max_smem) {
             h->dyn_entry.fn2 = (const void *)v2::srbd_mpc_solve_warp_kernel<v2::DLay, 16, 0>;
@@ -612,6 +629,16 @@ int g1mpc_create(const g1mpc_params *p, int device, g1mpc_handle **out)
     if (ke->fn2) {
         e = cudaFuncSetAttribute(ke->fn2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * ke->smem * h->warps_per_block));
         if (e != cudaSuccess) { g_last_error = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
+    }
+    if (ke->fnr && (p->layout == 0 || p->layout == 5)) {
+        int sms = 0, n = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        e = cudaFuncSetAttribute(ke->fnr, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * ke->smem));
+        if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, ke->fnr, kWarpThreads, 2 * ke->smem);
+        if (e == cudaSuccess) e = cudaMalloc((void **)&h->d_refill, sizeof(unsigned long long) * g1mpc_handle::kRefillCounters);
+        if (e != cudaSuccess) { g_last_error = std::string("refill kernel: ") + cudaGetErrorString(e); g1mpc_destroy(h); return G1MPC_ERR_CUDA; }
+        h->refill_ctas = sms * (n > 0 ? n : 1);
+        h->refill_above = p->layout == 5 ? -1 : 0x7fffffffffffLL;
     }
     {
         int sms = 0, ctas2 = 0;
@@ -714,6 +741,7 @@ void g1mpc_destroy(g1mpc_handle *h)
     }
     if (h->d_loop) cudaFree(h->d_loop);
     if (h->d_ws) cudaFree(h->d_ws);
+    if (h->d_refill) cudaFree(h->d_refill);
     if (h->ws_event) cudaEventDestroy(h->ws_event);
     delete h;
 }
@@ -764,6 +792,15 @@ static int solve_batch_impl(g1mpc_handle *h, int64_t B, int64_t load, const doub
     if (h->kernel->launchl && load <= h->lat_upto) {
         h->kernel->launchl((unsigned)B, 2 * kWarpThreads, h->kernel->smem, (cudaStream_t)stream, h->dev, io,
                            (long long)B, h->dlay);
+        CUDA_TRY(cudaGetLastError());
+        return G1MPC_OK;
+    }
+    if (h->kernel->launchr && load > h->refill_above && !u_warm) {
+        cudaStream_t st = (cudaStream_t)stream;
+        unsigned long long *cnt = h->d_refill + (h->refill_k++ % g1mpc_handle::kRefillCounters);
+        CUDA_TRY(cudaMemsetAsync(cnt, 0, sizeof(unsigned long long), st));
+        const long long nw = (B + 1) / 2, grid = nw < h->refill_ctas ? nw : h->refill_ctas;
+        h->kernel->launchr((unsigned)grid, 2 * h->kernel->smem, st, h->dev, io, (long long)B, cnt);
         CUDA_TRY(cudaGetLastError());
         return G1MPC_OK;
     }

@@ -985,16 +985,21 @@ __device__ __forceinline__ void start_point(const LAY &L, double *smc, const Dev
 // ------------------------------------------------------------------------------------------------
 // One problem (per HL lanes), `sm` = its workspace of L.oEnd doubles -- shared memory, or (long horizons) global memory that the
 // L1/L2 caches keep close: the code is the same, `__syncwarp()` orders both.
-template <class LAY, int HL, bool LAT = false>
+// REFILL (two problems per warp, persistent grid): a half-warp whose problem has stopped writes its results and takes the next
+// problem from the launch's counter `next` while the other half goes on -- the outputs / prologue of the one run at an iteration
+// boundary of the other, whose per-iteration quantities are then recomputed from its (untouched) iterate: same bits as ever.
+template <class LAY, int HL, bool LAT = false, bool REFILL = false>
 __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtrs &io, long long B, const LAY &L, long long b, double *sm,
-                                              double *smc, int lane, int half, double *lat = nullptr)
+                                              double *smc, int lane, int half, double *lat = nullptr, unsigned long long *next = nullptr,
+                                              unsigned long long next_base = 0)
 {
     const int N = L.N, NC = L.NC, NU = 3 * NC, NV = NU * N, NCN = NC * N;
 #ifdef G1MPC_PHASE_CLOCKS
     const long long ph_k0 = clock64();
 #endif
-    if (b - half >= B) return;                     // whole warp out of range
-    const bool valid = b < B;                      // odd batch: the last half-warp repeats the last problem and writes nothing
+    if (!REFILL && b - half >= B) return;          // whole warp out of range
+    bool valid = b < B;                            // odd batch: the last half-warp repeats the last problem and writes nothing
+    bool have = valid;                             // (REFILL) this half-warp holds a problem
     if (!valid) b = B - 1;
     // (smc = base of the per-contact region, offsets below L.oSt; sm = base of the stance list, the per-stage region and the scratch.  They are the
     //  same pointer except in the hybrid workspace variant of the kernel.)
@@ -1002,87 +1007,191 @@ __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtr
     double *gf = smc + L.oGf, *Dst = smc + L.oDst, *prod = smc + L.oProd, *tv = (L.kTvInScratch ? sm : smc) + L.oTv, *E = sm + L.oE;
     double *dsv = sm + L.oRic, *dlv = sm + L.oRic + 6 * NCN;     // alias: valid only after the corrector solve
     int *stIdx = reinterpret_cast<int *>(sm + L.oSt);      // (the list of stance contacts belongs to the on-chip part: every per-contact pass starts from it)
-    const double *gx0 = io.x0 + b * NS, *gxr = io.x_ref + b * (N * NS), *gct = io.contact + b * NCN;
-    const double *gch = io.c_hor + b * (NCN * 3), *gpc = io.p_com + b * (N * 3);
     const double sr = P.sr, mu = P.mu;
 
-    // ---- linearise (mpc.cpp:153-221) and stage the inputs ----------------------------------------
-    Lin lin;
-    linearise(P, gxr, N, lin);
+    // per-problem state of this half-warp (set by `prologue`)
     StageC C;
-#pragma unroll
-    for (int i = 0; i < 9; i++) C.J[i] = lin.Iwi[i] * P.dt;
-    C.bv = P.bv;
-    C.F.dc = P.dt * lin.c; C.F.dsn = P.dt * lin.s; C.F.dt = P.dt;
     int fcount = 0;
-    const double cz = lin.c, sz = lin.s;
+    double cz = 0.0, sz = 0.0, m_ineq = 6.0;
     int bad_bounds = 0, n_stance = 0;
-    for (int c0 = 0; c0 < NCN; c0 += HL) {
-        const int c = c0 + lane;
-        bool st = false;
-        if (c < NCN) {
-        const int k = c / NC;
-        rr[3 * c] = gch[3 * c] - gpc[3 * k]; rr[3 * c + 1] = gch[3 * c + 1] - gpc[3 * k + 1]; rr[3 * c + 2] = gch[3 * c + 2] - gpc[3 * k + 2];
-        const double cf = gct[c];
-        const double lo = P.fz_min * cf, hi = P.fz_max * cf;         // mpc.cpp:344,350
-        if (hi < lo) bad_bounds = 1;
-        cfl[c] = cf;
-        st = hi > lo;
-        }
-        // compacted list of stance contacts (order preserved)
-        const unsigned mw = __ballot_sync(kFullMask, st);
-        const unsigned m = HL == 32 ? mw : ((mw >> (half * HL)) & ((1u << (HL & 31)) - 1u));      // the bits of this problem's lanes
-        if (st) stIdx[n_stance + __popc(m & ((1u << lane) - 1u))] = c;
-        n_stance += __popc(m);
-    }
-    // free-response error e_k = A^(k+1) x0 - xref_k on the 12 weighted states (mpc.cpp:256-270,369-375)
-    {
-        double x0r[13];
-#pragma unroll
-        for (int i = 0; i < 13; i++) x0r[i] = gx0[i];
-        const double g0 = x0r[12], dt = P.dt;
-        for (int k = lane; k < N; k += HL) {
-            const double kk = (double)(k + 1);
-            const double *xr = gxr + k * NS;
-            double *Ek = E + 12 * k;
-            Ek[0] = x0r[0] + kk * dt * (cz * x0r[6] - sz * x0r[7]) - xr[0];
-            Ek[1] = x0r[1] + kk * dt * (sz * x0r[6] + cz * x0r[7]) - xr[1];
-            Ek[2] = x0r[2] + kk * dt * x0r[8] - xr[2];
-            Ek[3] = x0r[3] + kk * dt * x0r[9] - xr[3];
-            Ek[4] = x0r[4] + kk * dt * x0r[10] - xr[4];
-            Ek[5] = x0r[5] + kk * dt * x0r[11] + (0.5 * kk * (kk - 1.0)) * dt * dt * g0 - xr[5];
-            Ek[6] = x0r[6] - xr[6]; Ek[7] = x0r[7] - xr[7]; Ek[8] = x0r[8] - xr[8];
-            Ek[9] = x0r[9] - xr[9]; Ek[10] = x0r[10] - xr[10]; Ek[11] = x0r[11] + kk * dt * g0 - xr[11];
-        }
-    }
-    __syncwarp();
-    // start point (cold, or from a previous solution)
-    bool warm = io.u_warm != nullptr;
-    start_point<LAY, HL>(L, smc, P, lane, true, warm ? io.u_warm + b * NV : nullptr, io.warm_shift);
-    const double m_ineq = 6.0 * (double)(n_stance > 0 ? n_stance : 1);
-    __syncwarp();
-
-    PH_DECL
-#ifdef G1MPC_PHASE_CLOCKS
-    ph_t[13] = ph_last - ph_k0;                     // prologue: linearise, stage the inputs, start point
-#endif
+    bool warm = false;
     int status = G1MPC_MAX_ITER, it = 0;
     double gap = 0.0, rdmax = 0.0, gscale = 1.0, gap_start = 0.0;
     bool lam_init = false;
-
     // grad f is recomputed from u (two O(N) sweeps) only near the end; while the gap is large it is carried along with
     // the step, grad f += alpha (s r du + W^T y), because the multiplier wrench of the corrector solve IS M W du.  The
     // carried gradient drifts by ~1e-7 relative (the residual of the stage-wise solve), which the exact evaluations of
     // the last iterations remove; the iteration that stops always runs on an exact one (tests/test_ipm_model_cpu.py).
     bool exact = true;
-    const double exact_gap = 1e7 * P.gap_tol;
     // `frozen`: this problem has stopped.  With one problem per warp that ends the loop; with two, the warp goes on until
     // both have stopped, the per-contact passes of the frozen one run over zero contacts (n_act) and nothing of its
     // state changes any more.
     bool frozen = false;
+
+    // ---- linearise (mpc.cpp:153-221), stage the inputs, start point: for the half-warps with `act` (all of them unless REFILL).
+    //      What a half-warp WITHOUT act writes here it writes again with the values its own problem gave before (inputs and lists
+    //      only), its iterate (u, s, lambda, grad f) is not touched.
+    auto prologue = [&](const bool act) {
+        const double *gx0 = io.x0 + b * NS, *gxr = io.x_ref + b * (N * NS), *gct = io.contact + b * NCN;
+        const double *gch = io.c_hor + b * (NCN * 3), *gpc = io.p_com + b * (N * 3);
+        Lin lin;
+        linearise(P, gxr, N, lin);
+        if (act) {
+#pragma unroll
+            for (int i = 0; i < 9; i++) C.J[i] = lin.Iwi[i] * P.dt;
+            C.bv = P.bv;
+            C.F.dc = P.dt * lin.c; C.F.dsn = P.dt * lin.s; C.F.dt = P.dt;
+            cz = lin.c; sz = lin.s;
+        }
+        int bb = 0, ns = 0;
+        for (int c0 = 0; c0 < NCN; c0 += HL) {
+            const int c = c0 + lane;
+            bool st = false;
+            if (c < NCN) {
+            const int k = c / NC;
+            rr[3 * c] = gch[3 * c] - gpc[3 * k]; rr[3 * c + 1] = gch[3 * c + 1] - gpc[3 * k + 1]; rr[3 * c + 2] = gch[3 * c + 2] - gpc[3 * k + 2];
+            const double cf = gct[c];
+            const double lo = P.fz_min * cf, hi = P.fz_max * cf;         // mpc.cpp:344,350
+            if (hi < lo) bb = 1;
+            cfl[c] = cf;
+            st = hi > lo;
+            }
+            // compacted list of stance contacts (order preserved)
+            const unsigned mw = __ballot_sync(kFullMask, st);
+            const unsigned m = HL == 32 ? mw : ((mw >> (half * HL)) & ((1u << (HL & 31)) - 1u));      // the bits of this problem's lanes
+            if (st) stIdx[ns + __popc(m & ((1u << lane) - 1u))] = c;
+            ns += __popc(m);
+        }
+        if (act) { bad_bounds = bb; n_stance = ns; }
+        // free-response error e_k = A^(k+1) x0 - xref_k on the 12 weighted states (mpc.cpp:256-270,369-375)
+        {
+            double x0r[13];
+#pragma unroll
+            for (int i = 0; i < 13; i++) x0r[i] = gx0[i];
+            const double g0 = x0r[12], dt = P.dt;
+            for (int k = lane; k < N; k += HL) {
+                const double kk = (double)(k + 1);
+                const double *xr = gxr + k * NS;
+                double *Ek = E + 12 * k;
+                Ek[0] = x0r[0] + kk * dt * (cz * x0r[6] - sz * x0r[7]) - xr[0];
+                Ek[1] = x0r[1] + kk * dt * (sz * x0r[6] + cz * x0r[7]) - xr[1];
+                Ek[2] = x0r[2] + kk * dt * x0r[8] - xr[2];
+                Ek[3] = x0r[3] + kk * dt * x0r[9] - xr[3];
+                Ek[4] = x0r[4] + kk * dt * x0r[10] - xr[4];
+                Ek[5] = x0r[5] + kk * dt * x0r[11] + (0.5 * kk * (kk - 1.0)) * dt * dt * g0 - xr[5];
+                Ek[6] = x0r[6] - xr[6]; Ek[7] = x0r[7] - xr[7]; Ek[8] = x0r[8] - xr[8];
+                Ek[9] = x0r[9] - xr[9]; Ek[10] = x0r[10] - xr[10]; Ek[11] = x0r[11] + kk * dt * g0 - xr[11];
+            }
+        }
+        __syncwarp();
+        // start point (cold, or from a previous solution)
+        if (act) warm = io.u_warm != nullptr;
+        start_point<LAY, HL>(L, smc, P, lane, act, (act && warm) ? io.u_warm + b * NV : nullptr, io.warm_shift);
+        if (act) {
+            m_ineq = 6.0 * (double)(n_stance > 0 ? n_stance : 1);
+            status = G1MPC_MAX_ITER; it = 0;
+            gap = 0.0; rdmax = 0.0; gscale = 1.0; gap_start = 0.0;
+            lam_init = false; exact = true; frozen = false;
+        }
+        __syncwarp();
+    };
+    if (REFILL) { prologue(have); if (!have) frozen = true; }
+    else prologue(true);
+
+    // ---- outputs: for the half-warps with `fin` (all of them unless REFILL) ------------------------------------
+    auto epilogue = [&](const bool fin) {
+    // A failed factorisation leaves the scratch in solve-phase state, and with two problems per warp the one that stopped
+    // first has had its stage storage reused by the other's later iterations: evaluate w, X, V again from the returned u.
+    if (HL == 16 || REFILL || status == G1MPC_NUMERICAL) {
+        __syncwarp();
+        gradient_sweeps<LAY, HL>(L, sm, smc, P, C, lane);
+    }
+    __syncwarp();
+    // here w = W u, X = state response, gf = grad f(u) are consistent with the returned u
+    {
+        const unsigned bw = __ballot_sync(kFullMask, bad_bounds != 0);
+        bad_bounds = (HL == 32 ? bw : ((bw >> (half * HL)) & ((1u << (HL & 31)) - 1u))) != 0u;
+    }
+    if (fin && bad_bounds && status == G1MPC_SOLVED) status = G1MPC_BAD_BOUNDS;
+    // The slacks are carried by the iteration (ds = -Cb du), not recomputed from u, so after ~25 iterations u can sit
+    // ~1e-9 N outside an active row (measured at N = 40, nc = 8).  Clamp the returned point back into the pyramid:
+    // the change is six orders below the 1e-3 N parity tolerance and makes primal feasibility exact.
+    if (status != G1MPC_NUMERICAL) {
+        for (int i = lane; i < (fin ? n_stance : 0); i += HL) {
+            const int c = stIdx[i];
+            const double cf = cfl[c], lo = P.fz_min * cf, hi = P.fz_max * cf;
+            const double fz = fmin(fmax(u[3 * c + 2], lo), hi), lim = mu * fz;
+            u[3 * c] = fmin(fmax(u[3 * c], -lim), lim);
+            u[3 * c + 1] = fmin(fmax(u[3 * c + 1], -lim), lim);
+            u[3 * c + 2] = fz;
+        }
+    }
+    __syncwarp();                                   // (outside the branch: with two problems per warp `status` differs per half)
+    double *gu = io.u_opt + b * NV;
+    for (int i = lane; i < (fin && valid ? NV : 0); i += HL) gu[i] = u[i];
+    if (io.status && lane == 0 && fin && valid) io.status[b] = status;
+    if (io.iters && lane == 0 && fin && valid) io.iters[b] = it;
+    const double *wv = sm + L.oW, *Xs = sm + L.oXs;
+    if (io.resid) {
+        double obj2[2] = {0.0, 0.0}, pv = 0.0;      // (two accumulators: see wsum2)
+        for (int i = lane, odd = 0; i < NV; i += HL, odd ^= 1) {
+            const double t = 0.5 * sr * u[i] * u[i];
+            if (HL == 16 && odd) obj2[1] += t; else obj2[0] += t;
+        }
+        // 1/2 u'Hu + g'u = 1/2 sr |u|^2 + 1/2 sum sQ (e^2 - E^2),  e = E + X
+        for (int e = lane, odd = 0; e < 12 * N; e += HL, odd ^= 1) {
+            const double t = 0.5 * P.scale * P.q[e % 12] * Xs[e] * (2.0 * E[e] + Xs[e]);
+            if (HL == 16 && odd) obj2[1] += t; else obj2[0] += t;
+        }
+        for (int c = lane; c < NCN; c += HL) {
+            const double fx = u[3 * c], fy = u[3 * c + 1], fz = u[3 * c + 2];
+            const double cf = cfl[c], lo = P.fz_min * cf, hi = fmax(P.fz_max * cf, lo);
+            const double lim = __dmul_rn(mu, fz);                  // the rounded product the clamp above used (no FMA contraction)
+            pv = fmax(pv, fmax(fabs(fx) - lim, fabs(fy) - lim));
+            pv = fmax(pv, fmax(fz - hi, lo - fz));
+        }
+        const double obj = wsum2<HL>(obj2);
+        pv = wmax<HL>(pv);
+        if (lane == 0 && fin && valid) {
+            double *r = io.resid + b * 4;
+            r[0] = gap; r[1] = rdmax; r[2] = fmax(pv, 0.0); r[3] = obj;
+        }
+    }
+    if (io.y_opt) {
+        // multipliers of the reference's 5 rows per contact (OSQP sign: y<0 at a lower bound)
+        double *gy = io.y_opt + b * (5 * NCN);
+        for (int c = lane; c < (fin && valid ? NCN : 0); c += HL) {
+            double y5[5];
+            const double cf = cfl[c];
+            if (P.fz_max * cf > P.fz_min * cf) {
+                const double *l6 = lam + 6 * c;
+                y5[0] = -l6[1]; y5[1] = l6[0]; y5[2] = -l6[3]; y5[3] = l6[2]; y5[4] = l6[4] - l6[5];
+            } else {
+                // swing contact: any sign-feasible multiplier set that balances the gradient
+                const double *vk = sm + L.oV + 6 * (c / NC), *r = rr + 3 * c;      // u = 0 here: grad f = W_c^T v
+                const double g0 = (vk[1] * r[2] - vk[2] * r[1]) + vk[3], g1 = (vk[2] * r[0] - vk[0] * r[2]) + vk[4];
+                const double g2 = (vk[0] * r[1] - vk[1] * r[0]) + vk[5];
+                y5[0] = y5[1] = y5[2] = y5[3] = 0.0;
+                if (-g0 <= 0.0) y5[0] = -g0; else y5[1] = -g0;
+                if (-g1 <= 0.0) y5[2] = -g1; else y5[3] = -g1;
+                y5[4] = -g2 - mu * (y5[0] - y5[1] + y5[2] - y5[3]);
+            }
+#pragma unroll
+            for (int i = 0; i < 5; i++) gy[5 * c + i] = y5[i];
+        }
+    }
+    rollout_rows(io.x_opt + b * (N * NS), io.x_current ? io.x_current + b * NS : nullptr, io.one_rollout ? 1 : N - 1,
+                 sm + L.oVa, sm + L.oXs, P.dt, cz, sz, lane, HL, fin && valid);
+    };
+
+    PH_DECL
+#ifdef G1MPC_PHASE_CLOCKS
+    ph_t[13] = ph_last - ph_k0;                     // prologue: linearise, stage the inputs, start point
+#endif
+    const double exact_gap = 1e7 * P.gap_tol;
     int n_act = n_stance;
 #pragma unroll 1
-    for (it = 0;;) {
+    for (;;) {
         PH(7)
     again:
         n_act = frozen ? 0 : n_stance;
@@ -1187,7 +1296,23 @@ __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtr
             frozen = true;
         }
         if (!frozen && it >= P.max_iter) { status = G1MPC_MAX_ITER; frozen = true; }
-        if (HL == 32 ? frozen : __all_sync(kFullMask, frozen)) break;
+        if (REFILL) {
+            // a half-warp whose problem has stopped: results out, next problem in, while the other half waits at this iteration
+            // boundary; then the top of the iteration runs again for both (for the half in mid-solve it recomputes what it had)
+            const bool fin = frozen && have;
+            if (__any_sync(kFullMask, fin)) {
+                __syncwarp();
+                epilogue(fin);
+                unsigned long long nb = 0;
+                if (fin && lane == 0) nb = next_base + atomicAdd(next, 1ULL);
+                nb = __shfl_sync(kFullMask, nb, half * HL);
+                if (fin) { b = (long long)nb; have = valid = b < B; if (!have) b = B - 1; }
+                __syncwarp();
+                prologue(fin && have);
+                if (__all_sync(kFullMask, !have)) break;
+                goto again;
+            }
+        } else if (HL == 32 ? frozen : __all_sync(kFullMask, frozen)) break;
         n_act = frozen ? 0 : n_stance;
         __syncwarp();
 
@@ -1203,7 +1328,7 @@ __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtr
             bar_sync64(kLatDoneBar);
         }
         if (!fac_ok && !frozen) { status = G1MPC_NUMERICAL; frozen = true; }
-        if (HL == 32 ? frozen : __all_sync(kFullMask, frozen)) break;
+        if (!REFILL && (HL == 32 ? frozen : __all_sync(kFullMask, frozen))) break;      // (REFILL: handled at the next iteration boundary)
         n_act = frozen ? 0 : n_stance;
         PH(3)
         // (4) predictor.  With x = ds/s:  dl = -lam (1 + x), and the largest feasible step is
@@ -1324,89 +1449,7 @@ __device__ __forceinline__ void solve_problem(const DevParams &P, const BatchPtr
         PH(6)
     }
 
-    // ---- outputs ------------------------------------------------------------------------------------
-    // A failed factorisation leaves the scratch in solve-phase state, and with two problems per warp the one that stopped
-    // first has had its stage storage reused by the other's later iterations: evaluate w, X, V again from the returned u.
-    if (HL == 16 || status == G1MPC_NUMERICAL) {
-        __syncwarp();
-        gradient_sweeps<LAY, HL>(L, sm, smc, P, C, lane);
-    }
-    __syncwarp();
-    // here w = W u, X = state response, gf = grad f(u) are consistent with the returned u
-    {
-        const unsigned bw = __ballot_sync(kFullMask, bad_bounds != 0);
-        bad_bounds = (HL == 32 ? bw : ((bw >> (half * HL)) & ((1u << (HL & 31)) - 1u))) != 0u;
-    }
-    if (bad_bounds && status == G1MPC_SOLVED) status = G1MPC_BAD_BOUNDS;
-    // The slacks are carried by the iteration (ds = -Cb du), not recomputed from u, so after ~25 iterations u can sit
-    // ~1e-9 N outside an active row (measured at N = 40, nc = 8).  Clamp the returned point back into the pyramid:
-    // the change is six orders below the 1e-3 N parity tolerance and makes primal feasibility exact.
-    if (status != G1MPC_NUMERICAL) {
-        for (int i = lane; i < n_stance; i += HL) {
-            const int c = stIdx[i];
-            const double cf = cfl[c], lo = P.fz_min * cf, hi = P.fz_max * cf;
-            const double fz = fmin(fmax(u[3 * c + 2], lo), hi), lim = mu * fz;
-            u[3 * c] = fmin(fmax(u[3 * c], -lim), lim);
-            u[3 * c + 1] = fmin(fmax(u[3 * c + 1], -lim), lim);
-            u[3 * c + 2] = fz;
-        }
-    }
-    __syncwarp();                                   // (outside the branch: with two problems per warp `status` differs per half)
-    double *gu = io.u_opt + b * NV;
-    for (int i = lane; i < (valid ? NV : 0); i += HL) gu[i] = u[i];
-    if (io.status && lane == 0 && valid) io.status[b] = status;
-    if (io.iters && lane == 0 && valid) io.iters[b] = it;
-    const double *wv = sm + L.oW, *Xs = sm + L.oXs;
-    if (io.resid) {
-        double obj2[2] = {0.0, 0.0}, pv = 0.0;      // (two accumulators: see wsum2)
-        for (int i = lane, odd = 0; i < NV; i += HL, odd ^= 1) {
-            const double t = 0.5 * sr * u[i] * u[i];
-            if (HL == 16 && odd) obj2[1] += t; else obj2[0] += t;
-        }
-        // 1/2 u'Hu + g'u = 1/2 sr |u|^2 + 1/2 sum sQ (e^2 - E^2),  e = E + X
-        for (int e = lane, odd = 0; e < 12 * N; e += HL, odd ^= 1) {
-            const double t = 0.5 * P.scale * P.q[e % 12] * Xs[e] * (2.0 * E[e] + Xs[e]);
-            if (HL == 16 && odd) obj2[1] += t; else obj2[0] += t;
-        }
-        for (int c = lane; c < NCN; c += HL) {
-            const double fx = u[3 * c], fy = u[3 * c + 1], fz = u[3 * c + 2];
-            const double cf = cfl[c], lo = P.fz_min * cf, hi = fmax(P.fz_max * cf, lo);
-            const double lim = __dmul_rn(mu, fz);                  // the rounded product the clamp above used (no FMA contraction)
-            pv = fmax(pv, fmax(fabs(fx) - lim, fabs(fy) - lim));
-            pv = fmax(pv, fmax(fz - hi, lo - fz));
-        }
-        const double obj = wsum2<HL>(obj2);
-        pv = wmax<HL>(pv);
-        if (lane == 0 && valid) {
-            double *r = io.resid + b * 4;
-            r[0] = gap; r[1] = rdmax; r[2] = fmax(pv, 0.0); r[3] = obj;
-        }
-    }
-    if (io.y_opt) {
-        // multipliers of the reference's 5 rows per contact (OSQP sign: y<0 at a lower bound)
-        double *gy = io.y_opt + b * (5 * NCN);
-        for (int c = lane; c < (valid ? NCN : 0); c += HL) {
-            double y5[5];
-            const double cf = cfl[c];
-            if (P.fz_max * cf > P.fz_min * cf) {
-                const double *l6 = lam + 6 * c;
-                y5[0] = -l6[1]; y5[1] = l6[0]; y5[2] = -l6[3]; y5[3] = l6[2]; y5[4] = l6[4] - l6[5];
-            } else {
-                // swing contact: any sign-feasible multiplier set that balances the gradient
-                const double *vk = sm + L.oV + 6 * (c / NC), *r = rr + 3 * c;      // u = 0 here: grad f = W_c^T v
-                const double g0 = (vk[1] * r[2] - vk[2] * r[1]) + vk[3], g1 = (vk[2] * r[0] - vk[0] * r[2]) + vk[4];
-                const double g2 = (vk[0] * r[1] - vk[1] * r[0]) + vk[5];
-                y5[0] = y5[1] = y5[2] = y5[3] = 0.0;
-                if (-g0 <= 0.0) y5[0] = -g0; else y5[1] = -g0;
-                if (-g1 <= 0.0) y5[2] = -g1; else y5[3] = -g1;
-                y5[4] = -g2 - mu * (y5[0] - y5[1] + y5[2] - y5[3]);
-            }
-#pragma unroll
-            for (int i = 0; i < 5; i++) gy[5 * c + i] = y5[i];
-        }
-    }
-    rollout_rows(io.x_opt + b * (N * NS), io.x_current ? io.x_current + b * NS : nullptr, io.one_rollout ? 1 : N - 1,
-                 sm + L.oVa, sm + L.oXs, P.dt, cz, sz, lane, HL, valid);
+    if (!REFILL) epilogue(true);
 #ifdef G1MPC_PHASE_CLOCKS
     __syncwarp();
     PH(14)                                          // epilogue: outputs + rollout
@@ -1450,6 +1493,23 @@ __global__ void __launch_bounds__(128) srbd_mpc_solve_warp_kernel(const DevParam
             __syncwarp();
         }
     }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Two problems per warp with REFILL (see solve_problem): persistent grid of one-warp CTAs, workspace in shared memory.  The warp no
+// longer lasts as long as the slower of a fixed pair (E[max of two iteration counts] = 14.5 against a mean of 13.6 on config 3), and
+// the launch has no tail of half-empty warps.  `next` counts the problems handed out after the first gridDim.x * 2.
+// ------------------------------------------------------------------------------------------------
+template <class LAY, int HL>
+__global__ void __launch_bounds__(32) srbd_mpc_solve_refill_kernel(const DevParams P, const BatchPtrs io, long long B, const LAY L,
+                                                                    unsigned long long *next)
+{
+    constexpr int PPW = 32 / HL;
+    extern __shared__ __align__(16) double sm_all[];
+    const int lane = threadIdx.x & (HL - 1), half = (threadIdx.x & 31) / HL;
+    double *sm = sm_all + (size_t)half * L.oEnd;
+    solve_problem<LAY, HL, false, true>(P, io, B, L, (long long)blockIdx.x * PPW + half, sm, sm, lane, half, nullptr, next,
+                                        (unsigned long long)gridDim.x * PPW);
 }
 
 // ------------------------------------------------------------------------------------------------

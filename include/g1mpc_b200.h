@@ -69,7 +69,10 @@ typedef struct g1mpc_params {
                                  warps per problem -- up to 2 problems per SM, one problem per warp up to 4 per SM, two per
                                  warp above), 1 = one problem per warp, 2 = two per warp, 3 = latency mode, 4 = latency mode with
                                  two problems per main warp (measured slower than 2, never chosen automatically; 2-4 where
-                                 compiled: horizon <= 16 resp. <= 15, 4 contacts).  Results do not depend on it (bit-identical). */
+                                 compiled: horizon <= 16 resp. <= 15, 4 contacts), 5 = two per warp with refill (persistent grid: a
+                                 half-warp that has finished takes the next problem while its partner goes on; bench shape only;
+                                 measured 5 % slower than 2 on large batches, never chosen automatically).  Results do not depend
+                                 on it (bit-identical). */
     double dual_tol;          /* see G1MPC_SOLVED                             (<=0: default 1e-6)   */
     double warm_margin;       /* warm start: newtons a previous solution is pulled inside every constraint row
                                                                               (<=0: default 0.01 mass |g|) */

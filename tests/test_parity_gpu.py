@@ -466,6 +466,29 @@ def test_two_problems_per_warp_layout_gives_the_same_bits():
     assert int((b[2]["status"] != 0).sum()) == 0
 
 
+def test_two_problems_per_warp_with_refill_gives_the_same_bits():
+    """layout = 5: persistent grid, a half-warp whose problem has stopped writes its results and takes the next problem from the
+    launch's counter while the other half goes on (its per-iteration quantities are recomputed from its untouched iterate at the
+    iteration boundary).  Bit-identical to the plain layout -- several waves, an odd batch, a batch smaller than the grid, warm
+    start falls back to the plain kernel.  (Measured 5 % slower on large batches: never chosen automatically.)"""
+    preset = presets.get_preset("cpp_node")
+    plain, refill = BatchedMPC(preset, device=0, layout=2), BatchedMPC(preset, device=0, layout=5)
+    full = list(inputs.random_batch(preset, 7001, seed=41, device="cuda"))
+    for B in (7001, 1185, 37, 1):
+        ins = [t[:B].contiguous() for t in full]
+        a = plain.update_batch(*ins, x_current=ins[0], want_multipliers=True)
+        for rep in range(2):
+            b = refill.update_batch(*ins, x_current=ins[0], want_multipliers=True)
+            assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1]), B
+            for k in ("status", "iters", "resid", "y"):
+                assert torch.equal(a[2][k], b[2][k]), (B, k)
+    ins = [t[:300].contiguous() for t in full]
+    cold = plain.update_batch(*ins, x_current=ins[0])[0]
+    a = plain.update_batch(*ins, x_current=ins[0], u_warm=cold, warm_shift=0)
+    b = refill.update_batch(*ins, x_current=ins[0], u_warm=cold, warm_shift=0)
+    assert int((b[2]["status"] != 0).sum()) == 0 and torch.equal(a[0], b[0])
+
+
 @pytest.mark.parametrize("pname,N,auto_ppw", [("cpp_node", 12, 2), ("python_default", 7, 2), ("cpp_node", 16, 1)])
 def test_two_problems_per_warp_layout_on_run_time_shapes(pname, N, auto_ppw):
     """Horizons without a compile-time instantiation (the reference takes HORIZON_LENGTH at run time, mpc.py:12) get the two-per-warp
