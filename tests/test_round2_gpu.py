@@ -369,6 +369,11 @@ def test_two_problems_per_warp_from_the_hybrid_workspace_give_the_same_bits(pnam
     host = [t.cpu().numpy() for t in ins]
     uh, xh, ih = auto.update_host(*host, x_current=host[0])
     assert np.array_equal(uh, a[0].cpu().numpy()) and np.array_equal(ih["iters"], a[2]["iters"].cpu().numpy())
+    # warm start (a previous solution shifted by one stage) through the same variants
+    prev = torch.roll(a[0], 1, 0).contiguous()
+    w1 = one.update_batch(*ins, x_current=ins[0], u_warm=prev, warm_shift=1)
+    w2 = auto.update_batch(*ins, x_current=ins[0], u_warm=prev, warm_shift=1)
+    assert torch.equal(w1[0], w2[0]) and torch.equal(w1[2]["iters"], w2[2]["iters"]) and int((w2[2]["status"] != 0).sum()) == 0
 
 
 # --------------------------------------------------------------------------------------------------------------------
