@@ -279,7 +279,7 @@ def test_shape_beyond_shared_memory_runs_from_the_global_workspace(orc):
 def test_no_write_lands_outside_the_output_arrays():
     """compute-sanitizer is closed on this GPU pool, so out-of-bounds writes are looked for with guard bands: every output
     array of the solve, rollout, emit, gait-plan and closed-loop entry points is a window into a larger buffer filled with a
-    sentinel; after the calls (odd batch sizes, both lane layouts, shared and global workspace) the bands are untouched."""
+    sentinel; after the calls (odd batch sizes, every lane layout, shared / global / hybrid workspace) the bands are untouched."""
     SENT = -7.25e301
     def window(*shape, dtype=torch.float64):
         n = int(np.prod(shape))
@@ -290,7 +290,10 @@ def test_no_write_lands_outside_the_output_arrays():
         return bool((buf[:256] == v).all()) and bool((buf[256 + n:] == v).all())
     for preset, kw, B in ((presets.get_preset("cpp_node"), dict(layout=1), 5), (presets.get_preset("cpp_node"), dict(layout=2), 7),
                           (presets.get_preset("cpp_node", horizon=13), dict(workspace=1), 3),
-                          (presets.get_preset("cpp_node", horizon=21, num_contacts=8), dict(workspace=2), 301)):
+                          (presets.get_preset("cpp_node", horizon=21, num_contacts=8), dict(workspace=2), 301),
+                          (presets.get_preset("cpp_node", horizon=21, num_contacts=8), dict(workspace=3), 1187),      # hybrid, > one wave
+                          (presets.get_preset("python_default"), dict(), 1301),          # two per warp from the hybrid workspace (odd batch)
+                          (presets.get_preset("cpp_node"), dict(layout=5), 2371)):       # refill: persistent grid, odd batch
         N, nu = preset["horizon"], 3 * preset["num_contacts"]
         s = BatchedMPC(preset, device=0, **kw)
         ins = list(inputs.random_batch(preset, B, seed=2, device="cuda"))
