@@ -68,8 +68,8 @@ typedef struct g1mpc_params {
     int32_t layout;           /* lane layout of the solve kernel: 0 = chosen per launch (g1mpc_layout_info: latency mode -- two
                                  warps per problem -- up to 2 problems per SM, one problem per warp up to 4 per SM, two per
                                  warp above), 1 = one problem per warp, 2 = two per warp, 3 = latency mode, 4 = latency mode with
-                                 two problems per main warp (measured slower than 2, never chosen automatically; 2-4 where
-                                 compiled: horizon <= 16 resp. <= 15, 4 contacts), 5 = two per warp with refill (persistent grid: a
+                                 two problems per main warp (measured slower than 2, never chosen automatically; horizon 10, 4
+                                 contacts only; 2-3 where compiled: horizon <= 16 resp. <= 15, 4 contacts), 5 = two per warp with refill (persistent grid: a
                                  half-warp that has finished takes the next problem while its partner goes on; bench shape only;
                                  measured 5 % slower than 2 on large batches, never chosen automatically).  Results do not depend
                                  on it (bit-identical). */

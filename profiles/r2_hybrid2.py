@@ -16,7 +16,11 @@ def timed(s, ins, reps=3):
     return a.elapsed_time(b) / reps, out
 for pname, N, nc, Bs in (("cpp_node", 10, 4, (1024, 4096, 65536)), ("python_default", 15, 4, (1024, 4096, 32768)), ("cpp_node", 10, 8, (1024, 4096, 16384)), ("cpp_node", 12, 8, (4096, 16384))):
     pr = presets.get_preset(pname, horizon=N, num_contacts=nc)
-    solvers = {"auto": BatchedMPC(pr, device=0), "hybrid2": BatchedMPC(pr, device=0, workspace=3, layout=2)}
+    solvers = {"auto": BatchedMPC(pr, device=0)}
+    try:
+        solvers["hybrid2"] = BatchedMPC(pr, device=0, workspace=3, layout=2)
+    except RuntimeError as e:      # (the bench-shape instantiation was dropped from the library after this measurement)
+        print(pname, N, nc, "hybrid2:", str(e)[:80]); continue
     print(pname, N, nc, {k: v.kernel_info(1 << 20) for k, v in solvers.items()})
     for B in Bs:
         ins = list(inputs.random_batch(pr, B, seed=11, device="cuda"))
