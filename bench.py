@@ -570,6 +570,25 @@ def extras(solver, preset, dev):
             del ins_h
         sv.close()
     out["config4_horizon_sweep"] = sweep
+    # the reference's OTHER preset (Python class defaults: N = 15, dt 0.04, mu 0.3, full inertia, cost scale 1; mpc.py:12-51) at a
+    # machine-filling batch of the config-3 distribution -- what a caller who swaps the import of g1_mpc/scripts/mpc.py gets in bulk
+    pr = _presets.get_preset("python_default")
+    sv = BatchedMPC(pr, device=dev.index)
+    ins_h = list(inputs.random_batch(pr, 32768, seed=11, device=dev))
+    for _ in range(2):
+        _, _, info_h = sv.update_batch(*ins_h, x_current=ins_h[0], want_resid=False)
+    torch.cuda.synchronize()
+    h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    h0.record()
+    for _ in range(3):
+        sv.update_batch(*ins_h, x_current=ins_h[0], want_resid=False)
+    h1.record(); torch.cuda.synchronize()
+    ms_h = h0.elapsed_time(h1) / 3
+    out["python_default_N15_32768_random"] = {"problems_per_s": 32768 / (ms_h * 1e-3), "ms_per_launch": ms_h,
+                                              "status_counts": torch.bincount(info_h["status"], minlength=5).tolist(),
+                                              "ipm_iters_mean": float(info_h["iters"].double().mean()), "kernel": sv.kernel_info(32768)}
+    del ins_h
+    sv.close()
 
     def timed_call(fn, spin):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

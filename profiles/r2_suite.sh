@@ -13,6 +13,8 @@ print("e2e", d["e2e"]["value"], d["e2e"]["sync"]["value"], d["e2e"]["per_rank"])
 for k, v in ex.items():
     if k.startswith("single") or k.startswith("mpc_"):
         print(k, {a: b for a, b in v.items() if a in ("device_p50", "p50", "wall_p50", "device_p99", "wall_p99", "warm_start_attribute")})
+    elif k == "python_default_N15_32768_random":
+        print(k, round(v["problems_per_s"]), v["status_counts"], v["kernel"]["mode"])
     elif k == "config4_horizon_sweep":
         for a, b in v.items(): print("  ", a, round(b["problems_per_s"]), b["status_counts"], b["kernel"])
     elif k == "next_rows":
